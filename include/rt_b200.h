@@ -1,0 +1,166 @@
+/* rt_b200.h -- C ABI of the B200-native per-pixel render path.
+ *
+ * This is the drop-in boundary for the reference's tracer backend: everything
+ * `OpenCLRaytracer` does against Boost.Compute/OpenCL (OpenCLRaytracer.cpp:13-105)
+ * is reached through these entry points instead.  Plain pointers and sizes only;
+ * no C++/torch types.  The C++ class `CudaRaytracer : public IRaytracer`
+ * (opencl-raytracer_b200/host/CudaRaytracer.hpp) and the ctypes binding
+ * (opencl-raytracer_b200/pyrt) are thin callers of this header.
+ *
+ * All functions return RT_OK (0) or a negative rt_status; rt_last_error() gives
+ * the message of the last failure on the calling thread.  There is NO CPU
+ * fallback: without a CUDA device of compute capability 10.x rt_create fails.
+ *
+ * Reference interface each entry point replaces (file:line under the reference):
+ *   rt_create / rt_destroy   device, context, queue    OpenCLRaytracer.cpp:36-44, 76-78
+ *   rt_upload_scene          objs/lights marshalling   OpenCLRaytracer.cpp:16-24, 47-48, 70-71, 108-146
+ *   rt_set_rays              ray buffer upload         OpenCLRaytracer.cpp:26-33, 49, 72
+ *   rt_set_camera            host ray generation       OpenCL-Raytracer.cpp:18-26, 68-72
+ *   rt_render                Render(): launch + read   OpenCLRaytracer.cpp:80-105
+ *   rt_render_aov / rt_trace (no equivalent: hit ids / t are not exported by the reference;
+ *                             added so that parity of the nearest-hit search can be tested)
+ */
+#ifndef RT_B200_H
+#define RT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_B200_ABI_VERSION 1
+
+typedef struct rt_ctx rt_ctx;
+
+typedef enum rt_status {
+    RT_OK = 0,
+    RT_ERR_INVALID = -1,     /* bad argument / call order                       */
+    RT_ERR_NO_DEVICE = -2,   /* no usable sm_100 device (no CPU fallback)       */
+    RT_ERR_CUDA = -3,        /* CUDA runtime error, see rt_last_error()         */
+    RT_ERR_UNSUPPORTED = -4, /* scene outside the supported domain (non-affine) */
+    RT_ERR_NOMEM = -5
+} rt_status;
+
+/* Kernel semantics selected per render (three stages of one path). */
+typedef enum rt_mode {
+    RT_MODE_HITTEST = 0,          /* hittest_kernel.cl:54-150  -> t in .x, (t,t,t,1) */
+    RT_MODE_SHADE = 1,            /* shade_kernel.cl:180-258   -> lights accumulate  */
+    RT_MODE_SHADE_AND_REFLECT = 2 /* shade_and_reflect_kernel.cl:244-285 (the live kernel) */
+} rt_mode;
+
+/* Nearest-hit search strategy.  All of them return bit-identical hits. */
+typedef enum rt_accel {
+    RT_ACCEL_AUTO = -1,
+    RT_ACCEL_BRUTE = 0, /* every ray x every object, the reference's arithmetic on every pair   */
+    RT_ACCEL_CULL = 1,  /* every ray x every object, conservative bounding-sphere reject first  */
+    RT_ACCEL_BVH = 2    /* bounding volume hierarchy, conservative traversal, exact leaf tests  */
+} rt_accel;
+
+/* Material.hpp:6-11 / cl_Material OpenCLRaytracer.hpp:32-39 (tightly packed here). */
+typedef struct rt_material {
+    float ambient[3];
+    float diffuse[3];
+    float specular[3];
+    float absorption, reflection, transparency, shininess;
+} rt_material;
+
+/* ObjectData.hpp:20-22 / cl_ObjectData OpenCLRaytracer.hpp:41-50.  Matrices are
+ * column-major exactly as glm::value_ptr yields them (m[12..14] = translation).
+ * mvInverseTranspose is not read by any kernel of the path and is not passed. */
+typedef struct rt_object {
+    rt_material mat;
+    float mv[16];
+    float mvInverse[16];
+    uint32_t type; /* 0 = unit sphere, 1 = unit cube [-0.5,0.5]^3 (ObjectData.hpp:9-12) */
+} rt_object;
+
+/* Light.hpp:4-16 / cl_Light OpenCLRaytracer.hpp:52-58. position is view space. */
+typedef struct rt_light {
+    float ambient[3];
+    float diffuse[3];
+    float specular[3];
+    float position[4];
+} rt_light;
+
+/* Ray3D.hpp:5-10 / cl_Ray OpenCLRaytracer.hpp:25-30. */
+typedef struct rt_ray {
+    float start[4];
+    float direction[4];
+} rt_ray;
+
+typedef struct rt_stats {
+    uint64_t rays_primary;   /* rays traced by the last render, by class        */
+    uint64_t rays_shadow;
+    uint64_t rays_reflect;
+    uint64_t pair_tests;     /* ray x object pairs examined (brute/cull) or leaf tests (bvh) */
+    uint64_t exact_tests;    /* pairs that ran the reference's exact arithmetic */
+    uint64_t pixels;         /* pixels rendered by this context (its shard)     */
+    uint64_t hit_pixels;
+    float kernel_ms;         /* device time of all kernels of the last render (CUDA events) */
+    float total_ms;          /* kernels + device->host copy of the last render  */
+    uint32_t kernel_launches;
+    uint32_t accel_used;     /* rt_accel actually used                          */
+    uint32_t pipeline_used;  /* 0 = megakernel, 1 = wavefront                   */
+    uint32_t reserved;
+} rt_stats;
+
+/* Integer options for rt_set_option. */
+typedef enum rt_option {
+    RT_OPT_PIPELINE = 1,   /* -1 auto, 0 megakernel, 1 wavefront */
+    RT_OPT_COUNT_RAYS = 2, /* 1: fill the ray/test counters of rt_stats (small atomics cost) */
+    RT_OPT_BVH_LEAF = 3    /* max objects per BVH leaf */
+} rt_option;
+
+const char* rt_last_error(void);
+int rt_abi_version(void);
+
+/* device < 0 selects the current CUDA device. */
+int rt_create(rt_ctx** out, int device);
+int rt_destroy(rt_ctx* ctx);
+int rt_set_option(rt_ctx* ctx, int option, int64_t value);
+
+/* Repack the AoS scene into the device SoA (and build the BVH lazily). */
+int rt_upload_scene(rt_ctx* ctx, const rt_object* objs, uint32_t n_objs, const rt_light* lights, uint32_t n_lights);
+
+/* Rays: either an explicit host array (any rays, index = output index) ... */
+int rt_set_rays(rt_ctx* ctx, const rt_ray* host_rays, uint64_t n_rays);
+/* ... or the reference's pinhole grid generated on the device, bit-identical to
+ * OpenCL-Raytracer.cpp:18-26,68-72: start (0,0,0,1), dir (ii - W/2, (H - jj) - H/2, zdir, 0),
+ * zdir = -(H/2)/tan(fov/2) computed by the caller in float. */
+int rt_set_camera(rt_ctx* ctx, uint32_t width, uint32_t height, float zdir);
+/* Restrict this context to a shard of the camera frame: row-blocks of
+ * `block_rows` rows dealt round-robin, this context owning blocks b with
+ * b % n_shards == shard.  (1 block, shard 0 of 1) = whole frame. */
+int rt_set_shard(rt_ctx* ctx, uint32_t block_rows, uint32_t shard, uint32_t n_shards);
+
+/* Render into a HOST buffer of n_rays float4 (xyz = unclamped colour, w = 1;
+ * pixels whose primary ray misses are (0,0,0,1), OpenCLRaytracer.cpp:32).
+ * With a shard set, only this shard's rows are written.  Synchronous. */
+int rt_render(rt_ctx* ctx, uint32_t max_bounces, int mode, int accel, float* host_out);
+/* Same, result left in DEVICE memory (dev_out may be a peer-mapped pointer of
+ * another GPU: stores go over NVLink).  dev_out == NULL renders into the
+ * context's own framebuffer.  Returns after the kernels finished. */
+int rt_render_device(rt_ctx* ctx, uint32_t max_bounces, int mode, int accel, float* dev_out);
+/* Device framebuffer of the context (n_rays float4), valid until rays/camera change. */
+int rt_framebuffer(rt_ctx* ctx, float** dev_ptr, uint64_t* n_pixels);
+
+/* Primary-ray nearest hit as AOVs: object index (-1 = miss) and t, host arrays of n_rays. */
+int rt_render_aov(rt_ctx* ctx, int accel, int32_t* host_hit_id, float* host_hit_t);
+/* Nearest hit of arbitrary host rays against the uploaded scene. */
+int rt_trace(rt_ctx* ctx, const rt_ray* host_rays, uint64_t n_rays, int accel, int32_t* host_hit_id, float* host_hit_t);
+
+int rt_get_stats(rt_ctx* ctx, rt_stats* out);
+
+/* Byte-identical device version of PPMExporter.cpp:19-21 quantisation:
+ * min(255, (int)floorf(c * 255.f)) per channel, rgb8 packed, from a host float4 frame. */
+int rt_quantize_rgb8(rt_ctx* ctx, const float* host_rgba, uint64_t n_pixels, int32_t* host_rgb_out);
+
+/* Register-only FFMA loop: measured FP32 peak of this device in TFLOP/s (roofline denominator). */
+int rt_measure_fp32_peak(rt_ctx* ctx, float* tflops, float* sm_mhz_hint);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* RT_B200_H */
