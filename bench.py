@@ -1,0 +1,396 @@
+#!/usr/bin/env python
+"""bench.py -- Mrays/s of the per-pixel render path (primary + shadow + reflection rays).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg5-box|...]
+
+One "step" = one frame of the workload = one IRaytracer::Render().  At N > 1 the frame is sharded by
+row-blocks over the ranks (one process per GPU, torchrun); every rank's kernels store their pixels straight
+into rank 0's framebuffer over NVLink (CUDA IPC peer mapping), rank 0 reads the frame back.
+
+  value     Mrays/s, device-resident: scene, camera and framebuffer already in HBM, kernels only,
+            CUDA events on the launching stream, max over ranks
+  e2e       the same frame through the reference-facing call (rt_render == Render()): launch + readback of the
+            whole frame into pinned host memory inside the timed region.  Scene and camera are uploaded once
+            before (as OpenCLRaytracer's constructor does, OpenCLRaytracer.cpp:70-73), so h2d bytes per step = 0.
+  roofline  the timed kernel against the measured FP32 FFMA peak of this GPU (rt_measure_fp32_peak);
+            MEASURED_PEAKS.json has no FP32 entry, HBM peak is taken from it for the framebuffer traffic.
+  cpu_baseline  the reference's own kernel source compiled for the host (oracle/_ref, "reference") or the C
+            restatement ("port") on all host cores, on a bounded pixel sample of the same frame.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "opencl-raytracer_b200")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+from pyrt import scenes, types  # noqa: E402
+
+METRIC = "Mrays/s (primary+shadow+reflect)"
+
+# flops of the arithmetic each counted unit executes (DESIGN.md "Work per unit")
+FLOPS_FILTER = 17.0   # bounding-sphere filter: 3 sub + 3 (mul,fma,fma) x2 + mul + fma ...
+FLOPS_EXACT = 78.0    # reference arithmetic of one ray x object test as written
+FLOPS_NODE = 62.0     # two inflated slab tests of one BVH node
+FLOPS_SHADE = 100.0   # Phong terms per (hit, light)
+FLOPS_ALGO_PAIR = 54.5  # minimal affine ray x object test
+
+
+def workload(name: str, args):
+    """-> (objs, lights, width, height, max_bounces, mode, label)"""
+    if name == "cfg5-box":
+        o, l = scenes.synthetic_scene(100_000, 4096)
+        return o, l, 7680, 4320, 4, 2, "synthetic 100k boxes + 4096 spheres, 7680x4320, reflection depth 4"
+    if name == "cfg5-small":
+        o, l = scenes.synthetic_scene(100_000, 4096)
+        return o, l, 1920, 1080, 4, 2, "synthetic 100k boxes + 4096 spheres, 1920x1080, reflection depth 4"
+    table = {
+        "cfg1": ("simpleSphere", 2560, 1440, 30, 2),
+        "cfg2": ("multipleSpheres", 1920, 1080, 3, 2),
+        "cfg3": ("roundedCube", 3840, 2160, 30, 2),
+        "cfg3-shade": ("roundedCube", 3840, 2160, 30, 1),
+        "cfg4": ("simpleScene", 3840, 2160, 5, 2),
+        "cfg4-3l": ("simpleScene3L", 3840, 2160, 5, 2),
+    }
+    s, w, h, mb, mode = table[name]
+    o, l = scenes.load_reference_scene(s)
+    return o, l, w, h, mb, mode, "%s.txt %dx%d depth %d mode %d" % (s, w, h, mb, mode)
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU during the timed region (NVML)."""
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index = index
+        self.samples, self.reasons = [], set()
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.ok = False
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {
+            nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+            nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap",
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.05)
+
+    def stop(self):
+        self._stop.set()
+        if self.is_alive():
+            self.join(timeout=2)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def sample_rays(width, height, zdir, n_side=64):
+    """A bounded, frame-covering pixel sample: an n_side x n_side lattice of pixels of the full frame."""
+    jj = np.linspace(0, height - 1, n_side).astype(np.int64)
+    ii = np.linspace(0, width - 1, n_side).astype(np.int64)
+    rows = types.camera_rays(width, height, zdir, rows=jj)
+    return rows.reshape(len(jj), width)[:, ii].reshape(-1).copy()
+
+
+def cpu_arm(objs, lights, rays, max_bounces, mode, steps, warmup, n_ref_rays=None):
+    """The reference's CPU implementation of the path on the host cores: oracle/_ref when it was built,
+    else the C restatement.  Returns (Mrays/s, ms_per_step, kind, cores, ray_count)."""
+    import oracle
+
+    cores = os.cpu_count() or 1
+    if n_ref_rays is None:
+        _, _, _, st = oracle.port_render(mode, max_bounces, objs, lights, rays, nthreads=cores)
+        n_ref_rays = st.rays_primary + st.rays_shadow + st.rays_reflect
+    use_ref = oracle.have_ref()
+    fast = use_ref and oracle.cpu_has_avx2_fma() and os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libsar_ref_fast.so"))
+    kind = "reference" if use_ref else "port"
+
+    def once():
+        if use_ref:
+            oracle.ref_render(mode, max_bounces, objs, lights, rays, nthreads=cores, fast=fast)
+        else:
+            oracle.port_render(mode, max_bounces, objs, lights, rays, nthreads=cores)
+
+    for _ in range(warmup):
+        once()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        once()
+    dt = (time.perf_counter() - t0) / max(steps, 1)
+    build = "-O3 -march=x86-64-v3" if fast else "-O2 -ffp-contract=off"
+    return n_ref_rays / dt / 1e6, dt * 1e3, kind, cores, n_ref_rays, build
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cfg5-box")
+    ap.add_argument("--accel", type=int, default=-1, help="-1 auto, 0 brute (exact on every pair), 1 filter, 2 bvh")
+    ap.add_argument("--block-rows", type=int, default=16)
+    ap.add_argument("--cpu-sample", type=int, default=0, help="side of the pixel lattice of the CPU sample (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-brute-leg", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    objs, lights, W, H, max_bounces, mode, label = workload(args.workload, args)
+    zdir = types.camera_zdir(H)
+    config = {"workload": label, "objects": int(len(objs)), "lights": int(len(lights)), "width": W, "height": H,
+              "max_bounces": max_bounces, "mode": ["hittest", "shade", "shade_and_reflect"][mode]}
+
+    # ------------------------------------------------------------------ reference arm (CPU)
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        side = args.cpu_sample or (48 if len(objs) > 10000 else 512)
+        rays = sample_rays(W, H, zdir, side)
+        v, ms, kind, cores, nrays, build = cpu_arm(objs, lights, rays, max_bounces, mode, args.steps, args.warmup)
+        sample = "%dx%d pixel lattice of the frame (%d rays/step), %s, %d threads" % (side, side, nrays, build, cores)
+        print(json.dumps({
+            "impl": "reference", "metric": METRIC, "value": v, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": config,
+            "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample},
+            "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        }))
+        return
+
+    # ------------------------------------------------------------------ our arm (CUDA)
+    import torch
+    import torch.distributed as dist
+
+    from pyrt import lib
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    lib.load()
+    ctx = lib.Context(local_rank)
+    sampler = ClockSampler(local_rank)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    t_up0 = time.perf_counter()
+    ctx.upload_scene(objs, lights)
+    ctx.set_camera(W, H, zdir)
+    torch.cuda.synchronize()
+    upload_ms = (time.perf_counter() - t_up0) * 1e3
+    if world > 1:
+        ctx.set_shard(args.block_rows, rank, world)
+
+    # framebuffer of the gather root, mapped into every rank (CUDA IPC): kernels store straight into it
+    target = 0
+    if world > 1:
+        handle = [ctx.ipc_export_framebuffer() if rank == 0 else None]
+        dist.broadcast_object_list(handle, src=0)
+        if rank != 0:
+            target = ctx.ipc_open(handle[0])
+
+    # ray counts of the frame (one counted, untimed render)
+    ctx.set_option(lib.OPT_COUNT_RAYS, 1)
+    ctx.render_device(max_bounces, mode, args.accel, target)
+    st = ctx.stats()
+    counts = torch.tensor([st.rays_primary, st.rays_shadow, st.rays_reflect, st.traced_shadow, st.traced_reflect,
+                           st.pair_tests, st.exact_tests, st.node_visits, st.hit_pixels, st.pixels], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.all_reduce(counts)
+    (r_prim, r_shadow, r_refl, t_shadow, t_refl, pair_tests, exact_tests, node_visits, hit_pixels, pixels) = [int(x) for x in counts.tolist()]
+    rays_traced = r_prim + t_shadow + t_refl
+    rays_reference = r_prim + r_shadow + r_refl
+    accel_used = st.accel_used
+    ctx.set_option(lib.OPT_COUNT_RAYS, 0)
+
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        sampler_local = ClockSampler(local_rank)
+        sampler_local.start()
+        dev_ms = 0.0
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            flush.zero_()
+            barrier()
+            dev_ms += fn()
+        barrier()
+        wall_ms = (time.perf_counter() - t0) * 1e3
+        clocks = sampler_local.stop()
+        t = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()) / steps, wall_ms / steps, clocks
+
+    def step_device():
+        ctx.render_device(max_bounces, mode, args.accel, target)
+        return ctx.stats().kernel_ms
+
+    ms_dev, _, clocks = timed(step_device, args.steps, args.warmup)
+    value = rays_traced / (ms_dev * 1e-3) / 1e6
+
+    # e2e: Render() semantics -- launch + readback of the whole frame to pinned host memory on rank 0
+    host = lib.PinnedBuffer((W * H, 4)) if rank == 0 else None
+
+    def step_e2e():
+        t0 = time.perf_counter()
+        if world == 1:
+            ctx.render(max_bounces, mode, args.accel, out=host.array)
+        else:
+            ctx.render_device(max_bounces, mode, args.accel, target)
+            barrier()  # every shard has landed in rank 0's HBM
+            if rank == 0:
+                ctx.readback(host.array)
+        return (time.perf_counter() - t0) * 1e3
+
+    ms_e2e, _, _ = timed(step_e2e, args.steps, args.warmup)
+    e2e_value = rays_traced / (ms_e2e * 1e-3) / 1e6
+
+    # ------------------------------------------------------------------ roofline of the timed kernel
+    peak_tf, peak_mhz = ctx.measure_fp32_peak()
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    kernel_names = {0: "render_mega<brute>", 1: "render_mega<filter>", 2: "render_mega<bvh>"}
+    shades = t_shadow  # one Phong evaluation per traced shadow ray
+    if accel_used == 2:
+        flops = node_visits * FLOPS_NODE + exact_tests * (FLOPS_EXACT + FLOPS_FILTER) + shades * FLOPS_SHADE
+    elif accel_used == 1:
+        flops = pair_tests * FLOPS_FILTER + exact_tests * FLOPS_EXACT + shades * FLOPS_SHADE
+    else:
+        flops = pair_tests * FLOPS_EXACT + shades * FLOPS_SHADE
+    achieved_tf = flops / world / (ms_dev * 1e-3) / 1e12
+    roofline = {
+        "kernel": kernel_names[accel_used], "bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
+        "frac": achieved_tf / peak_tf if peak_tf else None, "traffic": None,
+        "peak_source": "rt_measure_fp32_peak (register-only FFMA loop, this GPU, this run; implies %.0f MHz)" % peak_mhz,
+        "flops_per_launch": flops / world,
+        "hbm": {"framebuffer_bytes_per_launch": pixels * 16 / world, "achieved_gbs": pixels * 16 / world / (ms_dev * 1e-3) / 1e9,
+                "peak_gbs": peaks.get("hbm_gbs")},
+        "note": "BVH traversal is latency/divergence bound; the FP32 fraction is reported for completeness, see roofline_brute"
+        if accel_used == 2 else "",
+    }
+
+    # brute-force leg: the reference's O(rays x objects) search (filter + exact) on a bounded band of the same frame
+    roofline_brute = None
+    if not args.no_brute_leg and rank == 0 and len(objs) > 48:
+        rows = max(8, min(H, int(2.0e13 / (FLOPS_FILTER * len(objs) * W * 6)) // 8 * 8))
+        r0 = (H // 2 - rows // 2) // 8 * 8
+        band = types.camera_rays(W, H, zdir, rows=np.arange(r0, r0 + rows))
+        with lib.Context(local_rank) as c2:
+            c2.upload_scene(objs, lights)
+            c2.set_rays(band)
+            c2.set_option(lib.OPT_COUNT_RAYS, 1)
+            c2.render_device(max_bounces, mode, 1)
+            s2 = c2.stats()
+            c2.set_option(lib.OPT_COUNT_RAYS, 0)
+            best = None
+            for _ in range(3):
+                c2.render_device(max_bounces, mode, 1)
+                k = c2.stats().kernel_ms
+                best = k if best is None else min(best, k)
+            fl = s2.pair_tests * FLOPS_FILTER + s2.exact_tests * FLOPS_EXACT + s2.traced_shadow * FLOPS_SHADE
+            tf = fl / (best * 1e-3) / 1e12
+            roofline_brute = {
+                "kernel": "render_mega<filter>", "bound": "fp32", "sample": "%d rows x %d px band at row %d" % (rows, W, r0),
+                "pair_tests": s2.pair_tests, "ms": best, "achieved": tf, "peak": peak_tf, "unit": "TFLOP/s",
+                "frac": tf / peak_tf if peak_tf else None,
+                "reference_equivalent_tflops": s2.pair_tests * FLOPS_ALGO_PAIR / (best * 1e-3) / 1e12,
+                "mrays_per_s": s2.rays_traced / (best * 1e-3) / 1e6,
+            }
+
+    # ------------------------------------------------------------------ CPU baseline (rank 0, N = 1 only)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        side = args.cpu_sample or (40 if len(objs) > 10000 else 384)
+        rays = sample_rays(W, H, zdir, side)
+        with lib.Context(local_rank) as c3:  # reference ray count of the sample (GPU count == oracle count, tests)
+            c3.upload_scene(objs, lights)
+            c3.set_rays(rays)
+            c3.set_option(lib.OPT_COUNT_RAYS, 1)
+            c3.set_option(lib.OPT_SKIP_DEAD_RAYS, 0)
+            c3.render_device(max_bounces, mode, -1)
+            nref = c3.stats().rays_reference
+        v, ms, kind, cores, nrays, build = cpu_arm(objs, lights, rays, max_bounces, mode, 1, 0, n_ref_rays=nref)
+        cpu = {"value": v, "unit": "Mrays/s", "cores": cores, "kind": kind,
+               "sample": "%dx%d pixel lattice of the frame, %d reference rays, %.1f s, %s" % (side, side, nrays, ms / 1e3, build)}
+
+    if rank == 0:
+        out = {
+            "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": dict(config, accel=["brute", "filter", "bvh"][accel_used], pipeline="megakernel",
+                           sharding="row-blocks of %d rows round-robin over %d ranks, peer stores into rank 0 (CUDA IPC)" % (args.block_rows, world)
+                           if world > 1 else "single GPU",
+                           l2="framebuffer %d MB > L2; 256 MB memset between steps flushes L2 (scene is re-read from HBM each step)" % (W * H * 16 >> 20),
+                           scene_upload_ms=upload_ms),
+            "rays": {"traced": rays_traced, "reference": rays_reference, "primary": r_prim, "shadow_traced": t_shadow,
+                     "shadow_reference": r_shadow, "reflect_traced": t_refl, "reflect_reference": r_refl, "hit_pixels": hit_pixels,
+                     "mrays_reference_equivalent": rays_reference / (ms_dev * 1e-3) / 1e6},
+            "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": W * H * 16,
+                    "note": "rt_render == IRaytracer::Render(): launch + blocking readback; scene/camera resident as in the reference ctor"},
+            "gpu_launches": args.steps * 1,
+            "clocks": clocks,
+            "roofline": roofline,
+        }
+        if roofline_brute:
+            out["roofline_brute"] = roofline_brute
+        if cpu:
+            out["cpu_baseline"] = cpu
+        print(json.dumps(out))
+    if world > 1:
+        if target:
+            ctx.ipc_close(target)
+        dist.barrier()
+        dist.destroy_process_group()
+    ctx.close()
+
+
+if __name__ == "__main__":
+    main()

@@ -90,18 +90,25 @@ typedef struct rt_ray {
 } rt_ray;
 
 typedef struct rt_stats {
-    uint64_t rays_primary;   /* rays traced by the last render, by class        */
+    /* rays the reference kernel traces for the rendered pixels (SURVEY.md 8(d) formula) ...  */
+    uint64_t rays_primary;
     uint64_t rays_shadow;
     uint64_t rays_reflect;
-    uint64_t pair_tests;     /* ray x object pairs examined (brute/cull) or leaf tests (bvh) */
-    uint64_t exact_tests;    /* pairs that ran the reference's exact arithmetic */
-    uint64_t pixels;         /* pixels rendered by this context (its shard)     */
+    /* ... and the shadow / reflection rays this path really traced: with RT_OPT_SKIP_DEAD_RAYS rays whose
+     * result cannot reach the output (SAR:238 last-light-wins, SAR:268 absorption test) are not traced.
+     * Throughput is always computed from rays_primary + traced_shadow + traced_reflect. */
+    uint64_t traced_shadow;
+    uint64_t traced_reflect;
+    uint64_t pair_tests;     /* ray x object pairs examined by the brute-force searches      */
+    uint64_t exact_tests;    /* pairs that ran the reference's exact arithmetic              */
+    uint64_t node_visits;    /* BVH inner nodes visited                                      */
+    uint64_t pixels;         /* pixels rendered by this context (its shard)                  */
     uint64_t hit_pixels;
-    float kernel_ms;         /* device time of all kernels of the last render (CUDA events) */
-    float total_ms;          /* kernels + device->host copy of the last render  */
+    float kernel_ms;         /* device time of all kernels of the last render (CUDA events)  */
+    float total_ms;          /* kernels + device->host copy of the last render               */
     uint32_t kernel_launches;
-    uint32_t accel_used;     /* rt_accel actually used                          */
-    uint32_t pipeline_used;  /* 0 = megakernel, 1 = wavefront                   */
+    uint32_t accel_used;     /* rt_accel actually used                                       */
+    uint32_t pipeline_used;  /* 0 = megakernel, 1 = wavefront                                */
     uint32_t reserved;
 } rt_stats;
 
@@ -109,7 +116,8 @@ typedef struct rt_stats {
 typedef enum rt_option {
     RT_OPT_PIPELINE = 1,   /* -1 auto, 0 megakernel, 1 wavefront */
     RT_OPT_COUNT_RAYS = 2, /* 1: fill the ray/test counters of rt_stats (small atomics cost) */
-    RT_OPT_BVH_LEAF = 3    /* max objects per BVH leaf */
+    RT_OPT_BVH_LEAF = 3,   /* max objects per BVH leaf (1..16) */
+    RT_OPT_SKIP_DEAD_RAYS = 4 /* 1 (default): do not trace rays whose result is dead; 0: trace every ray the reference traces */
 } rt_option;
 
 const char* rt_last_error(void);
@@ -145,6 +153,10 @@ int rt_render_device(rt_ctx* ctx, uint32_t max_bounces, int mode, int accel, flo
 /* Device framebuffer of the context (n_rays float4), valid until rays/camera change. */
 int rt_framebuffer(rt_ctx* ctx, float** dev_ptr, uint64_t* n_pixels);
 
+/* Copy the context's whole device framebuffer (all n_rays float4, including rows other ranks stored into
+ * it through rt_ipc_open) to host memory.  Synchronous. */
+int rt_readback(rt_ctx* ctx, float* host_out);
+
 /* Primary-ray nearest hit as AOVs: object index (-1 = miss) and t, host arrays of n_rays. */
 int rt_render_aov(rt_ctx* ctx, int accel, int32_t* host_hit_id, float* host_hit_t);
 /* Nearest hit of arbitrary host rays against the uploaded scene. */
@@ -155,6 +167,19 @@ int rt_get_stats(rt_ctx* ctx, rt_stats* out);
 /* Byte-identical device version of PPMExporter.cpp:19-21 quantisation:
  * min(255, (int)floorf(c * 255.f)) per channel, rgb8 packed, from a host float4 frame. */
 int rt_quantize_rgb8(rt_ctx* ctx, const float* host_rgba, uint64_t n_pixels, int32_t* host_rgb_out);
+
+/* Multi-GPU, one process per GPU: the gather root exports its device framebuffer as a
+ * 64-byte CUDA IPC handle; every other rank opens it and passes the mapped pointer to rt_render_device,
+ * so its kernels store their shard's pixels straight into the root's HBM over NVLink (no separate
+ * collective).  The reference has no multi-device path (OpenCLRaytracer.cpp:36-44 picks one device). */
+int rt_ipc_export_framebuffer(rt_ctx* ctx, void* handle_64_bytes);
+int rt_ipc_open(rt_ctx* ctx, const void* handle_64_bytes, void** dev_ptr);
+int rt_ipc_close(rt_ctx* ctx, void* dev_ptr);
+
+/* Pinned host memory for render targets (cudaHostAlloc); rt_render accepts any host pointer,
+ * a pinned one makes the readback a single DMA. */
+int rt_host_alloc(void** out, uint64_t bytes);
+int rt_host_free(void* p);
 
 /* Register-only FFMA loop: measured FP32 peak of this device in TFLOP/s (roofline denominator). */
 int rt_measure_fp32_peak(rt_ctx* ctx, float* tflops, float* sm_mhz_hint);

@@ -1,0 +1,612 @@
+// rt_api.cu -- the extern "C" layer of include/rt_b200.h: device/context, scene upload, launch, readback.
+// This is what OpenCLRaytracer does against Boost.Compute (OpenCLRaytracer.cpp:13-105), on the CUDA runtime.
+// No CPU fallback: without an sm_100 device rt_create fails.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "../../include/rt_b200.h"
+#include "rt_kernels.cuh"
+#include "rt_scene.hpp"
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const std::string& msg) {
+    g_last_error = msg;
+    return code;
+}
+
+#define RT_CUDA(call)                                                                                          \
+    do {                                                                                                       \
+        cudaError_t e_ = (call);                                                                               \
+        if (e_ != cudaSuccess)                                                                                 \
+            return fail(RT_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));                      \
+    } while (0)
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    cudaError_t ensure(size_t count) {
+        if (count <= n && p) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        n = 0;
+        cudaError_t e = cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T));
+        if (e == cudaSuccess) n = std::max<size_t>(count, 1);
+        return e;
+    }
+    cudaError_t upload(const std::vector<T>& v, cudaStream_t s) {
+        cudaError_t e = ensure(v.size());
+        if (e != cudaSuccess || v.empty()) return e;
+        return cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, s);
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        n = 0;
+    }
+};
+
+}  // namespace
+
+struct rt_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
+
+    // host copy of the AoS scene (kept so that the bounds can be rebuilt when the ray-origin bound grows)
+    std::vector<rt_object> objs;
+    std::vector<rt_light> lights;
+    bool have_scene = false, scene_dirty = true;
+    rt::HostScene hs;
+    DevBuf<rt::F4> d_minv, d_mv, d_mat, d_lights;
+    DevBuf<rt::CullRec> d_cull, d_leaf_cull;
+    DevBuf<rt::BvhNode> d_nodes;
+    DevBuf<rt::BvhNodeF> d_nodef;
+    DevBuf<uint32_t> d_leaf_obj;
+    rt::Scene scene;
+
+    // rays / camera
+    bool use_camera = false, have_rays = false;
+    uint32_t width = 0, height = 0;
+    float zdir = 0.f;
+    DevBuf<rt::Ray> d_rays;
+    uint64_t n_rays = 0;
+    float omax_user = 0.f;
+    uint32_t block_rows = 1, shard = 0, n_shards = 1;
+
+    DevBuf<float4> d_fb;
+    DevBuf<int32_t> d_hit_id;
+    DevBuf<float> d_hit_t;
+    DevBuf<rt::Counters> d_counters;
+    DevBuf<float> d_sink;
+
+    // options
+    int opt_pipeline = -1, opt_count = 0, opt_leaf = 4, opt_skip_dead = 1;
+
+    rt_stats stats;
+};
+
+namespace {
+
+uint32_t shard_rows(const rt_ctx* c) {
+    if (!c->use_camera) return 0;
+    const uint32_t br = c->block_rows;
+    const uint32_t n_blocks = (c->height + br - 1) / br;
+    uint32_t rows = 0;
+    for (uint32_t b = c->shard; b < n_blocks; b += c->n_shards) rows += std::min(br, c->height - b * br);
+    return rows;
+}
+
+uint32_t shard_local_rows(const rt_ctx* c) {  // rows of the local image incl. the ragged last block
+    if (!c->use_camera) return 0;
+    const uint32_t br = c->block_rows;
+    const uint32_t n_blocks = (c->height + br - 1) / br;
+    uint32_t owned = 0;
+    for (uint32_t b = c->shard; b < n_blocks; b += c->n_shards) ++owned;
+    return owned * br;
+}
+
+int sync_scene(rt_ctx* c) {
+    if (!c->have_scene) return fail(RT_ERR_INVALID, "rt_upload_scene has not been called");
+    const float need_omax = c->use_camera ? 0.f : c->omax_user;
+    if (!c->scene_dirty && need_omax <= c->hs.omax) return RT_OK;
+    std::string err;
+    const int rc = rt::build_scene(c->objs.data(), (uint32_t)c->objs.size(), c->lights.data(), (uint32_t)c->lights.size(),
+                                   c->omax_user, c->opt_leaf, c->hs, err);
+    if (rc != RT_OK) return fail(rc, err);
+    RT_CUDA(c->d_minv.upload(c->hs.minv, c->stream));
+    RT_CUDA(c->d_mv.upload(c->hs.mv, c->stream));
+    RT_CUDA(c->d_mat.upload(c->hs.mat, c->stream));
+    RT_CUDA(c->d_lights.upload(c->hs.lights, c->stream));
+    RT_CUDA(c->d_cull.upload(c->hs.cull, c->stream));
+    RT_CUDA(c->d_leaf_cull.upload(c->hs.leaf_cull, c->stream));
+    RT_CUDA(c->d_nodes.upload(c->hs.nodes, c->stream));
+    RT_CUDA(c->d_nodef.upload(c->hs.nodef, c->stream));
+    RT_CUDA(c->d_leaf_obj.upload(c->hs.leaf_obj, c->stream));
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    rt::Scene& s = c->scene;
+    s.minv = reinterpret_cast<const float4*>(c->d_minv.p);
+    s.mv = reinterpret_cast<const float4*>(c->d_mv.p);
+    s.mat = reinterpret_cast<const float4*>(c->d_mat.p);
+    s.cull = c->d_cull.p;
+    s.nodes = c->d_nodes.p;
+    s.nodef = c->d_nodef.p;
+    s.leaf_obj = c->d_leaf_obj.p;
+    s.leaf_cull = c->d_leaf_cull.p;
+    s.lights = reinterpret_cast<const rt::Light*>(c->d_lights.p);
+    s.n_objs = c->hs.n_objs;
+    s.n_lights = c->hs.n_lights;
+    s.n_nodes = (uint32_t)c->hs.nodes.size();
+    s.root = c->hs.root;
+    c->scene_dirty = false;
+    return RT_OK;
+}
+
+int pick_accel(const rt_ctx* c, int accel) {
+    if (accel == RT_ACCEL_AUTO) {
+        const size_t m = c->objs.size();
+        if (m <= 4) return RT_ACCEL_BRUTE;
+        if (m <= 48) return RT_ACCEL_CULL;
+        return RT_ACCEL_BVH;
+    }
+    return accel;
+}
+
+int check_render_args(rt_ctx* c, int mode, int accel) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    if (mode < RT_MODE_HITTEST || mode > RT_MODE_SHADE_AND_REFLECT) return fail(RT_ERR_INVALID, "bad mode");
+    if (accel < RT_ACCEL_AUTO || accel > RT_ACCEL_BVH) return fail(RT_ERR_INVALID, "bad accel");
+    if (!c->use_camera && !c->have_rays) return fail(RT_ERR_INVALID, "neither rt_set_rays nor rt_set_camera was called");
+    return RT_OK;
+}
+
+uint64_t n_pixels(const rt_ctx* c) { return c->use_camera ? (uint64_t)c->width * c->height : c->n_rays; }
+
+void fill_frame_desc(rt_ctx* c, rt::Frame& fr, uint32_t max_bounces, int mode, float4* out) {
+    memset(&fr, 0, sizeof fr);
+    fr.rays = c->use_camera ? nullptr : c->d_rays.p;
+    fr.width = c->width;
+    fr.height = c->height;
+    fr.zdir = c->zdir;
+    fr.block_rows = c->use_camera ? c->block_rows : 1;
+    fr.shard = c->use_camera ? c->shard : 0;
+    fr.n_shards = c->use_camera ? c->n_shards : 1;
+    fr.local_rows = shard_local_rows(c);
+    fr.n_local = c->use_camera ? (uint64_t)shard_rows(c) * c->width : c->n_rays;
+    fr.max_bounces = max_bounces;
+    fr.mode = mode;
+    fr.skip_dead = c->opt_skip_dead;
+    fr.out = out;
+    fr.counters = c->opt_count ? c->d_counters.p : nullptr;
+}
+
+int collect_stats(rt_ctx* c, int accel, uint64_t pixels, uint32_t launches) {
+    rt_stats& st = c->stats;
+    memset(&st, 0, sizeof st);
+    st.pixels = pixels;
+    st.kernel_launches = launches;
+    st.accel_used = (uint32_t)accel;
+    st.pipeline_used = 0;
+    if (c->opt_count) {
+        rt::Counters h;
+        RT_CUDA(cudaMemcpyAsync(&h, c->d_counters.p, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+        RT_CUDA(cudaStreamSynchronize(c->stream));
+        st.rays_primary = h.ref_primary;
+        st.rays_shadow = h.ref_shadow;
+        st.rays_reflect = h.ref_reflect;
+        st.traced_shadow = h.traced_shadow;
+        st.traced_reflect = h.traced_reflect;
+        st.pair_tests = h.pair_tests;
+        st.exact_tests = h.exact_tests;
+        st.node_visits = h.node_visits;
+        st.hit_pixels = h.hit_pixels;
+    }
+    return RT_OK;
+}
+
+// kernels of one render on c->stream, bracketed by ev0/ev1
+int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float4* out, int* accel_used) {
+    int rc = sync_scene(c);
+    if (rc != RT_OK) return rc;
+    accel = pick_accel(c, accel);
+    *accel_used = accel;
+    rt::Frame fr;
+    fill_frame_desc(c, fr, max_bounces, mode, out);
+    if (c->opt_count) {
+        RT_CUDA(c->d_counters.ensure(1));
+        RT_CUDA(cudaMemsetAsync(c->d_counters.p, 0, sizeof(rt::Counters), c->stream));
+        fr.counters = c->d_counters.p;
+    }
+    RT_CUDA(cudaEventRecord(c->ev0, c->stream));
+    RT_CUDA(rt::launch_megakernel(c->scene, fr, accel, false, c->stream));
+    RT_CUDA(cudaEventRecord(c->ev1, c->stream));
+    return RT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* rt_last_error(void) { return g_last_error.c_str(); }
+int rt_abi_version(void) { return RT_B200_ABI_VERSION; }
+
+int rt_create(rt_ctx** out, int device) {
+    if (!out) return fail(RT_ERR_INVALID, "null out pointer");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return fail(RT_ERR_NO_DEVICE, std::string("no CUDA device (there is no CPU fallback): ") + cudaGetErrorString(e));
+    if (device < 0) {
+        if (cudaGetDevice(&device) != cudaSuccess) device = 0;
+    }
+    if (device >= n) return fail(RT_ERR_NO_DEVICE, "device index out of range");
+    cudaDeviceProp prop;
+    RT_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return fail(RT_ERR_NO_DEVICE, std::string("device '") + prop.name + "' is not compute capability 10.x; this library holds sm_100a code only");
+    RT_CUDA(cudaSetDevice(device));
+    rt_ctx* c = new rt_ctx();
+    c->device = device;
+    memset(&c->stats, 0, sizeof c->stats);
+    memset(&c->scene, 0, sizeof c->scene);
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&c->ev0) != cudaSuccess ||
+        cudaEventCreate(&c->ev1) != cudaSuccess || cudaEventCreate(&c->ev2) != cudaSuccess) {
+        delete c;
+        return fail(RT_ERR_CUDA, "stream/event creation failed");
+    }
+    *out = c;
+    return RT_OK;
+}
+
+int rt_destroy(rt_ctx* c) {
+    if (!c) return RT_OK;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    c->d_minv.release(); c->d_mv.release(); c->d_mat.release(); c->d_lights.release();
+    c->d_cull.release(); c->d_leaf_cull.release(); c->d_nodes.release(); c->d_nodef.release(); c->d_leaf_obj.release();
+    c->d_rays.release(); c->d_fb.release(); c->d_hit_id.release(); c->d_hit_t.release(); c->d_counters.release();
+    c->d_sink.release();
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->ev2) cudaEventDestroy(c->ev2);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+    return RT_OK;
+}
+
+int rt_set_option(rt_ctx* c, int option, int64_t value) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    switch (option) {
+        case RT_OPT_PIPELINE: c->opt_pipeline = (int)value; return RT_OK;
+        case RT_OPT_COUNT_RAYS: c->opt_count = value ? 1 : 0; return RT_OK;
+        case RT_OPT_BVH_LEAF:
+            if (value < 1 || value > 16) return fail(RT_ERR_INVALID, "leaf size must be 1..16");
+            c->opt_leaf = (int)value;
+            c->scene_dirty = true;
+            return RT_OK;
+        case RT_OPT_SKIP_DEAD_RAYS: c->opt_skip_dead = value ? 1 : 0; return RT_OK;
+        default: return fail(RT_ERR_INVALID, "unknown option");
+    }
+}
+
+int rt_upload_scene(rt_ctx* c, const rt_object* objs, uint32_t n_objs, const rt_light* lights, uint32_t n_lights) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    if ((n_objs && !objs) || (n_lights && !lights)) return fail(RT_ERR_INVALID, "null scene arrays");
+    RT_CUDA(cudaSetDevice(c->device));
+    c->objs.assign(objs, objs + n_objs);
+    c->lights.assign(lights, lights + n_lights);
+    c->have_scene = true;
+    c->scene_dirty = true;
+    return sync_scene(c);
+}
+
+int rt_set_rays(rt_ctx* c, const rt_ray* host_rays, uint64_t n) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    if (n && !host_rays) return fail(RT_ERR_INVALID, "null rays");
+    RT_CUDA(cudaSetDevice(c->device));
+    double omax2 = 0.0;
+    for (uint64_t i = 0; i < n; ++i) {
+        const float* s = host_rays[i].start;
+        const float* d = host_rays[i].direction;
+        if (!(fabsf(s[3] - 1.f) <= 1e-4f) || d[3] != 0.f)
+            return fail(RT_ERR_UNSUPPORTED, "ray " + std::to_string(i) + ": start.w must be 1 and direction.w 0 (Ray3D.hpp:9)");
+        const double o2 = (double)s[0] * s[0] + (double)s[1] * s[1] + (double)s[2] * s[2];
+        if (!(o2 < 1e30)) return fail(RT_ERR_UNSUPPORTED, "ray " + std::to_string(i) + ": non-finite origin");
+        omax2 = std::max(omax2, o2);
+    }
+    RT_CUDA(c->d_rays.ensure(n));
+    if (n) RT_CUDA(cudaMemcpyAsync(c->d_rays.p, host_rays, n * sizeof(rt_ray), cudaMemcpyHostToDevice, c->stream));
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    c->n_rays = n;
+    c->omax_user = (float)sqrt(omax2);
+    c->have_rays = true;
+    c->use_camera = false;
+    RT_CUDA(c->d_fb.ensure(n));
+    return RT_OK;
+}
+
+int rt_set_camera(rt_ctx* c, uint32_t width, uint32_t height, float zdir) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    if (width == 0 || height == 0 || !(zdir == zdir)) return fail(RT_ERR_INVALID, "bad camera");
+    if ((uint64_t)width * height >= (1ull << 40)) return fail(RT_ERR_INVALID, "frame too large");
+    RT_CUDA(cudaSetDevice(c->device));
+    c->width = width;
+    c->height = height;
+    c->zdir = zdir;
+    c->use_camera = true;
+    RT_CUDA(c->d_fb.ensure((uint64_t)width * height));
+    return RT_OK;
+}
+
+int rt_set_shard(rt_ctx* c, uint32_t block_rows, uint32_t shard, uint32_t n_shards) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    if (block_rows == 0 || n_shards == 0 || shard >= n_shards) return fail(RT_ERR_INVALID, "bad shard");
+    c->block_rows = block_rows;
+    c->shard = shard;
+    c->n_shards = n_shards;
+    return RT_OK;
+}
+
+int rt_render_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float* dev_out) {
+    int rc = check_render_args(c, mode, accel);
+    if (rc != RT_OK) return rc;
+    RT_CUDA(cudaSetDevice(c->device));
+    int used = 0;
+    float4* out = dev_out ? reinterpret_cast<float4*>(dev_out) : c->d_fb.p;
+    rc = render_on_device(c, max_bounces, mode, accel, out, &used);
+    if (rc != RT_OK) return rc;
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    rc = collect_stats(c, used, c->use_camera ? (uint64_t)shard_rows(c) * c->width : c->n_rays, 1);
+    if (rc != RT_OK) return rc;
+    float ms = 0.f;
+    RT_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    c->stats.kernel_ms = ms;
+    c->stats.total_ms = ms;
+    return RT_OK;
+}
+
+int rt_render(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float* host_out) {
+    int rc = check_render_args(c, mode, accel);
+    if (rc != RT_OK) return rc;
+    if (!host_out) return fail(RT_ERR_INVALID, "null output buffer");
+    RT_CUDA(cudaSetDevice(c->device));
+    int used = 0;
+    rc = render_on_device(c, max_bounces, mode, accel, c->d_fb.p, &used);
+    if (rc != RT_OK) return rc;
+    // readback: the shard's row-blocks (or everything)
+    uint64_t pixels;
+    if (c->use_camera && c->n_shards > 1) {
+        const uint32_t br = c->block_rows, nb = (c->height + br - 1) / br;
+        pixels = 0;
+        for (uint32_t b = c->shard; b < nb; b += c->n_shards) {
+            const uint64_t first = (uint64_t)b * br * c->width;
+            const uint64_t cnt = (uint64_t)std::min(br, c->height - b * br) * c->width;
+            RT_CUDA(cudaMemcpyAsync(host_out + 4 * first, c->d_fb.p + first, cnt * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+            pixels += cnt;
+        }
+    } else {
+        pixels = n_pixels(c);
+        if (pixels) RT_CUDA(cudaMemcpyAsync(host_out, c->d_fb.p, pixels * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+    }
+    RT_CUDA(cudaEventRecord(c->ev2, c->stream));
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    rc = collect_stats(c, used, pixels, 1);
+    if (rc != RT_OK) return rc;
+    float ms = 0.f, ms2 = 0.f;
+    RT_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    RT_CUDA(cudaEventElapsedTime(&ms2, c->ev0, c->ev2));
+    c->stats.kernel_ms = ms;
+    c->stats.total_ms = ms2;
+    return RT_OK;
+}
+
+int rt_framebuffer(rt_ctx* c, float** dev_ptr, uint64_t* n) {
+    if (!c || !dev_ptr) return fail(RT_ERR_INVALID, "null argument");
+    if (!c->use_camera && !c->have_rays) return fail(RT_ERR_INVALID, "no rays / camera set");
+    *dev_ptr = reinterpret_cast<float*>(c->d_fb.p);
+    if (n) *n = n_pixels(c);
+    return RT_OK;
+}
+
+int rt_readback(rt_ctx* c, float* host_out) {
+    if (!c || !host_out) return fail(RT_ERR_INVALID, "null argument");
+    if (!c->use_camera && !c->have_rays) return fail(RT_ERR_INVALID, "no rays / camera set");
+    RT_CUDA(cudaSetDevice(c->device));
+    const uint64_t n = n_pixels(c);
+    if (n) RT_CUDA(cudaMemcpyAsync(host_out, c->d_fb.p, n * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+int rt_render_aov(rt_ctx* c, int accel, int32_t* host_hit_id, float* host_hit_t) {
+    int rc = check_render_args(c, RT_MODE_HITTEST, accel);
+    if (rc != RT_OK) return rc;
+    if (!host_hit_id || !host_hit_t) return fail(RT_ERR_INVALID, "null output buffer");
+    RT_CUDA(cudaSetDevice(c->device));
+    rc = sync_scene(c);
+    if (rc != RT_OK) return rc;
+    accel = pick_accel(c, accel);
+    const uint64_t n = n_pixels(c);
+    RT_CUDA(c->d_hit_id.ensure(n));
+    RT_CUDA(c->d_hit_t.ensure(n));
+    rt::Frame fr;
+    fill_frame_desc(c, fr, 0, RT_MODE_HITTEST, c->d_fb.p);
+    fr.hit_id = c->d_hit_id.p;
+    fr.hit_t = c->d_hit_t.p;
+    if (c->opt_count) {
+        RT_CUDA(c->d_counters.ensure(1));
+        RT_CUDA(cudaMemsetAsync(c->d_counters.p, 0, sizeof(rt::Counters), c->stream));
+        fr.counters = c->d_counters.p;
+    }
+    if (c->use_camera && c->n_shards > 1) {  // rows of other shards read as "miss"
+        RT_CUDA(cudaMemsetAsync(c->d_hit_id.p, 0xff, n * sizeof(int32_t), c->stream));
+        RT_CUDA(cudaMemsetAsync(c->d_hit_t.p, 0, n * sizeof(float), c->stream));
+    }
+    RT_CUDA(cudaEventRecord(c->ev0, c->stream));
+    RT_CUDA(rt::launch_megakernel(c->scene, fr, accel, true, c->stream));
+    RT_CUDA(cudaEventRecord(c->ev1, c->stream));
+    if (n) {
+        RT_CUDA(cudaMemcpyAsync(host_hit_id, c->d_hit_id.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+        RT_CUDA(cudaMemcpyAsync(host_hit_t, c->d_hit_t.p, n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    }
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    rc = collect_stats(c, accel, n, 1);
+    if (rc != RT_OK) return rc;
+    float ms = 0.f;
+    RT_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    c->stats.kernel_ms = c->stats.total_ms = ms;
+    return RT_OK;
+}
+
+int rt_trace(rt_ctx* c, const rt_ray* host_rays, uint64_t n, int accel, int32_t* host_hit_id, float* host_hit_t) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    if (accel < RT_ACCEL_AUTO || accel > RT_ACCEL_BVH) return fail(RT_ERR_INVALID, "bad accel");
+    if (n && (!host_rays || !host_hit_id || !host_hit_t)) return fail(RT_ERR_INVALID, "null argument");
+    RT_CUDA(cudaSetDevice(c->device));
+    double omax2 = 0.0;
+    for (uint64_t i = 0; i < n; ++i) {
+        const float* s = host_rays[i].start;
+        if (!(fabsf(s[3] - 1.f) <= 1e-4f) || host_rays[i].direction[3] != 0.f)
+            return fail(RT_ERR_UNSUPPORTED, "ray " + std::to_string(i) + ": start.w must be 1 and direction.w 0 (Ray3D.hpp:9)");
+        omax2 = std::max(omax2, (double)s[0] * s[0] + (double)s[1] * s[1] + (double)s[2] * s[2]);
+    }
+    if (!(omax2 < 1e30)) return fail(RT_ERR_UNSUPPORTED, "non-finite ray origin");
+    const bool was_camera = c->use_camera;
+    const float saved = c->omax_user;
+    c->omax_user = std::max(c->omax_user, (float)sqrt(omax2));
+    c->use_camera = false;  // make sync_scene honour omax_user
+    int rc = sync_scene(c);
+    c->use_camera = was_camera;
+    if (rc != RT_OK) {
+        c->omax_user = saved;
+        return rc;
+    }
+    accel = pick_accel(c, accel);
+    DevBuf<rt::Ray> rays;
+    DevBuf<int32_t> ids;
+    DevBuf<float> ts;
+    cudaError_t e = rays.ensure(n);
+    if (e == cudaSuccess) e = ids.ensure(n);
+    if (e == cudaSuccess) e = ts.ensure(n);
+    if (e == cudaSuccess && n) e = cudaMemcpyAsync(rays.p, host_rays, n * sizeof(rt_ray), cudaMemcpyHostToDevice, c->stream);
+    rt::Counters* ctr = nullptr;
+    if (e == cudaSuccess && c->opt_count) {
+        e = c->d_counters.ensure(1);
+        if (e == cudaSuccess) e = cudaMemsetAsync(c->d_counters.p, 0, sizeof(rt::Counters), c->stream);
+        ctr = c->d_counters.p;
+    }
+    if (e == cudaSuccess) e = cudaEventRecord(c->ev0, c->stream);
+    if (e == cudaSuccess) e = rt::launch_trace(c->scene, rays.p, n, accel, ids.p, ts.p, ctr, c->stream);
+    if (e == cudaSuccess) e = cudaEventRecord(c->ev1, c->stream);
+    if (e == cudaSuccess && n) e = cudaMemcpyAsync(host_hit_id, ids.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess && n) e = cudaMemcpyAsync(host_hit_t, ts.p, n * sizeof(float), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    rays.release();
+    ids.release();
+    ts.release();
+    if (e != cudaSuccess) return fail(RT_ERR_CUDA, std::string("rt_trace: ") + cudaGetErrorString(e));
+    rc = collect_stats(c, accel, n, 1);
+    if (rc != RT_OK) return rc;
+    float ms = 0.f;
+    RT_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    c->stats.kernel_ms = c->stats.total_ms = ms;
+    return RT_OK;
+}
+
+int rt_get_stats(rt_ctx* c, rt_stats* out) {
+    if (!c || !out) return fail(RT_ERR_INVALID, "null argument");
+    *out = c->stats;
+    return RT_OK;
+}
+
+int rt_quantize_rgb8(rt_ctx* c, const float* host_rgba, uint64_t n, int32_t* host_rgb_out) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    if (n && (!host_rgba || !host_rgb_out)) return fail(RT_ERR_INVALID, "null argument");
+    if (n == 0) return RT_OK;
+    RT_CUDA(cudaSetDevice(c->device));
+    DevBuf<float4> in;
+    DevBuf<int32_t> outb;
+    cudaError_t e = in.ensure(n);
+    if (e == cudaSuccess) e = outb.ensure(3 * n);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(in.p, host_rgba, n * sizeof(float4), cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) e = rt::launch_quantize(in.p, n, outb.p, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(host_rgb_out, outb.p, 3 * n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    in.release();
+    outb.release();
+    if (e != cudaSuccess) return fail(RT_ERR_CUDA, std::string("rt_quantize_rgb8: ") + cudaGetErrorString(e));
+    return RT_OK;
+}
+
+int rt_measure_fp32_peak(rt_ctx* c, float* tflops, float* sm_mhz_hint) {
+    if (!c || !tflops) return fail(RT_ERR_INVALID, "null argument");
+    RT_CUDA(cudaSetDevice(c->device));
+    cudaDeviceProp prop;
+    RT_CUDA(cudaGetDeviceProperties(&prop, c->device));
+    RT_CUDA(c->d_sink.ensure(1));
+    const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 4096;
+    float best = 0.f;
+    for (int rep = 0; rep < 5; ++rep) {
+        RT_CUDA(cudaEventRecord(c->ev0, c->stream));
+        RT_CUDA(rt::launch_fp32_peak(c->d_sink.p, iters, blocks, threads, c->stream));
+        RT_CUDA(cudaEventRecord(c->ev1, c->stream));
+        RT_CUDA(cudaStreamSynchronize(c->stream));
+        float ms = 0.f;
+        RT_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+        const double flops = 2.0 * 8.0 * 16.0 * (double)iters * (double)blocks * threads;
+        if (rep > 0 && ms > 0.f) best = std::max(best, (float)(flops / (ms * 1e-3) / 1e12));
+    }
+    *tflops = best;
+    if (sm_mhz_hint) *sm_mhz_hint = best > 0.f ? (float)(best * 1e12 / (2.0 * 128.0 * prop.multiProcessorCount) / 1e6) : 0.f;
+    return RT_OK;
+}
+
+int rt_ipc_export_framebuffer(rt_ctx* c, void* handle) {
+    if (!c || !handle) return fail(RT_ERR_INVALID, "null argument");
+    if (!c->d_fb.p) return fail(RT_ERR_INVALID, "no framebuffer yet: call rt_set_camera / rt_set_rays first");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    RT_CUDA(cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    RT_CUDA(cudaIpcGetMemHandle(&h, c->d_fb.p));
+    memcpy(handle, &h, sizeof h);
+    return RT_OK;
+}
+
+int rt_ipc_open(rt_ctx* c, const void* handle, void** dev_ptr) {
+    if (!c || !handle || !dev_ptr) return fail(RT_ERR_INVALID, "null argument");
+    RT_CUDA(cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof h);
+    RT_CUDA(cudaIpcOpenMemHandle(dev_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return RT_OK;
+}
+
+int rt_ipc_close(rt_ctx* c, void* dev_ptr) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    RT_CUDA(cudaSetDevice(c->device));
+    if (dev_ptr) RT_CUDA(cudaIpcCloseMemHandle(dev_ptr));
+    return RT_OK;
+}
+
+int rt_host_alloc(void** out, uint64_t bytes) {
+    if (!out) return fail(RT_ERR_INVALID, "null argument");
+    RT_CUDA(cudaHostAlloc(out, std::max<uint64_t>(bytes, 1), cudaHostAllocPortable));
+    return RT_OK;
+}
+
+int rt_host_free(void* p) {
+    if (p) RT_CUDA(cudaFreeHost(p));
+    return RT_OK;
+}
+
+}  // extern "C"

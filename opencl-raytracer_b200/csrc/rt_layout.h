@@ -1,0 +1,27 @@
+// rt_layout.h -- byte layouts shared by the host scene builder (rt_scene.cpp) and the
+// device code (rt_device.cuh).  Plain structs, no CUDA types.
+#pragma once
+#include <stdint.h>
+
+namespace rt {
+
+struct CullRec {       // 32 B, two 128-bit loads
+    float cx, cy, cz;  // view-space centre of the bounding sphere
+    float r2;          // padded squared radius
+    float h;           // 1 - g (cone term): reject iff h*|oc|^2 - (oc.u)^2 > r2
+    float cc;          // |c|^2
+    float e0;          // h*cc - r2: common-origin (o = 0) form, reject iff e0 > (c.u)^2
+    uint32_t type;     // 0 sphere, 1 box, other: never hit (the kernels' switch has no default)
+};
+
+struct BvhNode {  // 64 B: both children's boxes
+    float lo0[3], hi0[3];
+    float lo1[3], hi1[3];
+    int32_t c0, c1;  // >= 0: inner node index; < 0: leaf, ~c = (first << 4) | (count - 1)
+    float a0, a1;    // static inflation of each child box: pad + f * r_far
+};
+struct BvhNodeF {  // cone coefficient per child; inflation = a + f * |ray origin|
+    float f0, f1;
+};
+
+}  // namespace rt

@@ -1,0 +1,482 @@
+// rt_scene.cpp -- host side of rt_upload_scene: AoS -> SoA repack (replaces the cl_* marshalling of
+// OpenCLRaytracer.cpp:16-24,108-146), conservative per-object bounds, BVH build.
+//
+// Why the bounds need care.  The reference decides hit / miss in binary32 with the arithmetic of
+// shade_and_reflect_kernel.cl:78-144, and that arithmetic is *noisy*: for a sphere the discriminant
+// B*B - 4*A*C cancels catastrophically when the ray origin is far from the object in object-space
+// units (|s| >> 1), so the silhouette the reference actually renders differs from the geometric one
+// by up to ~15 u |s|^2 in squared object-space radius (u = 2^-24; derivation in DESIGN.md).  The CUDA
+// path reproduces that arithmetic bit for bit (ex:: in rt_device.cuh), but it only runs it on pairs
+// that survive a cheap conservative filter, so every bound produced here must contain the *noisy*
+// object, not just the geometric one:
+//
+//      fuzzy squared radius (object space)   rho^2 <= 1 + K u |s|^2,          |s| <= |oc| / sigma_min
+//      => view space, any direction          extent <= sigma_max * rho
+//      => bounding sphere test               p^2 <= R^2 + g |oc|^2,           g = K u (sigma_max/sigma_min)^2
+//      => box inflation                      + sqrt(g) * |oc|,                |oc| <= |o| + r_far
+//
+// plus static pads for the rounding of the transform itself.  K = 32 is twice the first-order worst case.
+// tests/test_bounds.py checks on adversarial scenes that no exact hit is ever filtered.
+#include "rt_scene.hpp"
+
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+#include <numeric>
+
+namespace rt {
+namespace {
+
+const double U = 5.9604644775390625e-08;  // 2^-24
+const double K_FUZZ = 32.0;
+
+struct M3 {
+    double a[3][3];
+};
+
+bool inverse3(const M3& m, M3& out) {
+    const double (*a)[3] = m.a;
+    const double c00 = a[1][1] * a[2][2] - a[1][2] * a[2][1];
+    const double c01 = a[1][2] * a[2][0] - a[1][0] * a[2][2];
+    const double c02 = a[1][0] * a[2][1] - a[1][1] * a[2][0];
+    const double det = a[0][0] * c00 + a[0][1] * c01 + a[0][2] * c02;
+    if (!(fabs(det) > 0.0) || !std::isfinite(det)) return false;
+    const double id = 1.0 / det;
+    out.a[0][0] = c00 * id;
+    out.a[1][0] = c01 * id;
+    out.a[2][0] = c02 * id;
+    out.a[0][1] = (a[0][2] * a[2][1] - a[0][1] * a[2][2]) * id;
+    out.a[1][1] = (a[0][0] * a[2][2] - a[0][2] * a[2][0]) * id;
+    out.a[2][1] = (a[0][1] * a[2][0] - a[0][0] * a[2][1]) * id;
+    out.a[0][2] = (a[0][1] * a[1][2] - a[0][2] * a[1][1]) * id;
+    out.a[1][2] = (a[0][2] * a[1][0] - a[0][0] * a[1][2]) * id;
+    out.a[2][2] = (a[0][0] * a[1][1] - a[0][1] * a[1][0]) * id;
+    return true;
+}
+
+// Extreme singular values of a 3x3 matrix: sqrt of the eigenvalues of M^T M (cyclic Jacobi).
+void singular_range(const M3& m, double& smin, double& smax) {
+    double s[3][3];
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) {
+            s[i][j] = 0;
+            for (int k = 0; k < 3; ++k) s[i][j] += m.a[k][i] * m.a[k][j];
+        }
+    for (int sweep = 0; sweep < 32; ++sweep) {
+        const double off = fabs(s[0][1]) + fabs(s[0][2]) + fabs(s[1][2]);
+        if (off < 1e-300 || off < 1e-18 * (fabs(s[0][0]) + fabs(s[1][1]) + fabs(s[2][2]))) break;
+        for (int p = 0; p < 2; ++p)
+            for (int q = p + 1; q < 3; ++q) {
+                if (s[p][q] == 0.0) continue;
+                const double theta = (s[q][q] - s[p][p]) / (2.0 * s[p][q]);
+                const double t = (theta >= 0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+                const double c = 1.0 / sqrt(t * t + 1.0), sn = t * c;
+                for (int k = 0; k < 3; ++k) {  // S <- S * J
+                    const double skp = s[k][p], skq = s[k][q];
+                    s[k][p] = c * skp - sn * skq;
+                    s[k][q] = sn * skp + c * skq;
+                }
+                for (int k = 0; k < 3; ++k) {  // S <- J^T * S
+                    const double spk = s[p][k], sqk = s[q][k];
+                    s[p][k] = c * spk - sn * sqk;
+                    s[q][k] = sn * spk + c * sqk;
+                }
+            }
+    }
+    const double e0 = std::max(s[0][0], 0.0), e1 = std::max(s[1][1], 0.0), e2 = std::max(s[2][2], 0.0);
+    smax = sqrt(std::max(e0, std::max(e1, e2)));
+    smin = sqrt(std::min(e0, std::min(e1, e2)));
+}
+
+float up(double v) {  // round to float, then one ulp outward (towards +inf)
+    float f = (float)v;
+    if ((double)f < v) f = nextafterf(f, INFINITY);
+    return nextafterf(f, INFINITY);
+}
+float down(double v) {
+    float f = (float)v;
+    if ((double)f > v) f = nextafterf(f, -INFINITY);
+    return nextafterf(f, -INFINITY);
+}
+
+struct ObjBound {
+    double c[3];     // centre
+    double half[3];  // padded half extents of the AABB
+    double R;        // padded bounding-sphere radius
+    double g;        // cone coefficient on |oc|^2
+    double f;        // sqrt(g)
+};
+
+struct BuildNode {
+    double lo[3], hi[3];
+    double f;
+    int left = -1, right = -1;  // BuildNode indices
+    uint32_t first = 0, count = 0;
+    int depth = 0;
+};
+
+struct Builder {
+    const std::vector<ObjBound>& ob;
+    std::vector<uint32_t> idx;
+    std::vector<BuildNode> bn;
+    int leaf_size;
+    uint32_t max_depth = 0;
+
+    Builder(const std::vector<ObjBound>& o, int ls) : ob(o), idx(o.size()), leaf_size(ls) { std::iota(idx.begin(), idx.end(), 0u); }
+
+    void bounds(uint32_t first, uint32_t count, BuildNode& n) const {
+        for (int a = 0; a < 3; ++a) {
+            n.lo[a] = INFINITY;
+            n.hi[a] = -INFINITY;
+        }
+        n.f = 0;
+        for (uint32_t i = first; i < first + count; ++i) {
+            const ObjBound& b = ob[idx[i]];
+            for (int a = 0; a < 3; ++a) {
+                n.lo[a] = std::min(n.lo[a], b.c[a] - b.half[a]);
+                n.hi[a] = std::max(n.hi[a], b.c[a] + b.half[a]);
+            }
+            n.f = std::max(n.f, b.f);
+        }
+    }
+
+    static double area(const double* lo, const double* hi) {
+        const double x = hi[0] - lo[0], y = hi[1] - lo[1], z = hi[2] - lo[2];
+        return 2.0 * (x * y + y * z + z * x);
+    }
+
+    int build(uint32_t first, uint32_t count, int depth) {
+        const int me = (int)bn.size();
+        bn.emplace_back();
+        {
+            BuildNode n;
+            bounds(first, count, n);
+            n.first = first;
+            n.count = count;
+            n.depth = depth;
+            bn[me] = n;
+        }
+        max_depth = std::max<uint32_t>(max_depth, (uint32_t)depth);
+        if (count <= (uint32_t)leaf_size) return me;
+
+        // binned SAH over centroids
+        double clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        for (uint32_t i = first; i < first + count; ++i)
+            for (int a = 0; a < 3; ++a) {
+                clo[a] = std::min(clo[a], ob[idx[i]].c[a]);
+                chi[a] = std::max(chi[a], ob[idx[i]].c[a]);
+            }
+        const int NB = 16;
+        int best_axis = -1, best_bin = -1;
+        double best_cost = INFINITY;
+        for (int a = 0; a < 3; ++a) {
+            const double ext = chi[a] - clo[a];
+            if (!(ext > 0)) continue;
+            struct Bin {
+                double lo[3], hi[3];
+                uint32_t n;
+            } bins[NB];
+            for (int b = 0; b < NB; ++b) {
+                bins[b].n = 0;
+                for (int k = 0; k < 3; ++k) {
+                    bins[b].lo[k] = INFINITY;
+                    bins[b].hi[k] = -INFINITY;
+                }
+            }
+            const double scale = NB / ext;
+            for (uint32_t i = first; i < first + count; ++i) {
+                const ObjBound& o = ob[idx[i]];
+                int b = (int)((o.c[a] - clo[a]) * scale);
+                b = std::min(std::max(b, 0), NB - 1);
+                bins[b].n++;
+                for (int k = 0; k < 3; ++k) {
+                    bins[b].lo[k] = std::min(bins[b].lo[k], o.c[k] - o.half[k]);
+                    bins[b].hi[k] = std::max(bins[b].hi[k], o.c[k] + o.half[k]);
+                }
+            }
+            double rl[NB][3], rh[NB][3];
+            uint32_t rn[NB];
+            double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+            uint32_t n = 0;
+            for (int b = NB - 1; b > 0; --b) {
+                for (int k = 0; k < 3; ++k) {
+                    lo[k] = std::min(lo[k], bins[b].lo[k]);
+                    hi[k] = std::max(hi[k], bins[b].hi[k]);
+                    rl[b][k] = lo[k];
+                    rh[b][k] = hi[k];
+                }
+                n += bins[b].n;
+                rn[b] = n;
+            }
+            for (int k = 0; k < 3; ++k) {
+                lo[k] = INFINITY;
+                hi[k] = -INFINITY;
+            }
+            n = 0;
+            for (int b = 0; b < NB - 1; ++b) {
+                for (int k = 0; k < 3; ++k) {
+                    lo[k] = std::min(lo[k], bins[b].lo[k]);
+                    hi[k] = std::max(hi[k], bins[b].hi[k]);
+                }
+                n += bins[b].n;
+                if (n == 0 || rn[b + 1] == 0) continue;
+                const double cost = area(lo, hi) * n + area(rl[b + 1], rh[b + 1]) * rn[b + 1];
+                if (cost < best_cost) {
+                    best_cost = cost;
+                    best_axis = a;
+                    best_bin = b;
+                }
+            }
+        }
+        uint32_t mid;
+        if (best_axis < 0 || depth >= 32) {  // depth cap: median splits from here on keep the tree below RT_BVH_STACK
+            mid = first + count / 2;  // (also when all centroids coincide)
+        } else {
+            const double ext = chi[best_axis] - clo[best_axis];
+            const double scale = NB / ext;
+            const int a = best_axis;
+            auto it = std::partition(idx.begin() + first, idx.begin() + first + count, [&](uint32_t id) {
+                int b = (int)((ob[id].c[a] - clo[a]) * scale);
+                b = std::min(std::max(b, 0), NB - 1);
+                return b <= best_bin;
+            });
+            mid = (uint32_t)(it - idx.begin());
+            if (mid == first || mid == first + count) mid = first + count / 2;
+        }
+        const int l = build(first, mid - first, depth + 1);
+        const int r = build(mid, first + count - mid, depth + 1);
+        bn[me].left = l;
+        bn[me].right = r;
+        return me;
+    }
+};
+
+}  // namespace
+
+int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, uint32_t n_lights, float omax_user,
+                int leaf_size, HostScene& out, std::string& err) {
+    out = HostScene();
+    out.n_objs = n_objs;
+    out.n_lights = n_lights;
+    if ((n_objs && !objs) || (n_lights && !lights)) {
+        err = "null scene arrays";
+        return RT_ERR_INVALID;
+    }
+    if (n_objs >= (1u << 27)) {
+        err = "too many objects";
+        return RT_ERR_INVALID;
+    }
+    leaf_size = std::min(std::max(leaf_size, 1), 16);
+
+    out.minv.resize(4 * (size_t)n_objs);
+    out.mv.resize(4 * (size_t)n_objs);
+    out.mat.resize(3 * (size_t)n_objs);
+    out.cull.resize(n_objs);
+    out.lights.resize(4 * (size_t)n_lights);
+
+    for (uint32_t i = 0; i < n_lights; ++i) {
+        const rt_light& l = lights[i];
+        out.lights[4 * i + 0] = F4{l.ambient[0], l.ambient[1], l.ambient[2], 0.f};
+        out.lights[4 * i + 1] = F4{l.diffuse[0], l.diffuse[1], l.diffuse[2], 0.f};
+        out.lights[4 * i + 2] = F4{l.specular[0], l.specular[1], l.specular[2], 0.f};
+        out.lights[4 * i + 3] = F4{l.position[0], l.position[1], l.position[2], l.position[3]};
+    }
+
+    // ---- pass 1: geometry of every object in double precision
+    struct Geo {
+        double c[3], ext[3], R, smin, smax, wdev;
+    };
+    std::vector<Geo> geo(n_objs);
+    double r0 = 0.0, wdev_max = 0.0;
+    for (uint32_t i = 0; i < n_objs; ++i) {
+        const rt_object& o = objs[i];
+        for (int k = 0; k < 16; ++k)
+            if (!std::isfinite(o.mv[k]) || !std::isfinite(o.mvInverse[k])) {
+                err = "object " + std::to_string(i) + ": non-finite matrix";
+                return RT_ERR_UNSUPPORTED;
+            }
+        for (int c = 0; c < 4; ++c) {
+            out.minv[4 * (size_t)i + c] = F4{o.mvInverse[4 * c], o.mvInverse[4 * c + 1], o.mvInverse[4 * c + 2], o.mvInverse[4 * c + 3]};
+            out.mv[4 * (size_t)i + c] = F4{o.mv[4 * c], o.mv[4 * c + 1], o.mv[4 * c + 2], o.mv[4 * c + 3]};
+        }
+        out.mat[3 * (size_t)i + 0] = F4{o.mat.ambient[0], o.mat.ambient[1], o.mat.ambient[2], o.mat.absorption};
+        out.mat[3 * (size_t)i + 1] = F4{o.mat.diffuse[0], o.mat.diffuse[1], o.mat.diffuse[2], o.mat.shininess};
+        out.mat[3 * (size_t)i + 2] = F4{o.mat.specular[0], o.mat.specular[1], o.mat.specular[2], 0.f};
+
+        // affine check: bottom rows (0,0,0,1) up to rounding of glm::inverse
+        const float* mi = o.mvInverse;
+        const float* mv = o.mv;
+        const double brow = fabs(mi[3]) + fabs(mi[7]) + fabs(mi[11]) + fabs(mv[3]) + fabs(mv[7]) + fabs(mv[11]);
+        const double wd = std::max(fabs((double)mi[15] - 1.0), fabs((double)mv[15] - 1.0));
+        if (brow > 0.0 || wd > 1e-4) {
+            err = "object " + std::to_string(i) + ": projective (non-affine) matrices are outside the supported domain";
+            return RT_ERR_UNSUPPORTED;
+        }
+        Geo& g = geo[i];
+        g.wdev = wd;
+        wdev_max = std::max(wdev_max, wd);
+        M3 A, F;
+        for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 3; ++c) A.a[r][c] = mi[4 * c + r];
+        if (o.type > 1u) {  // never hit: keep a degenerate record far away
+            g.c[0] = g.c[1] = g.c[2] = 0;
+            g.ext[0] = g.ext[1] = g.ext[2] = 0;
+            g.R = 0;
+            g.smin = g.smax = 1;
+            continue;
+        }
+        if (!inverse3(A, F)) {
+            err = "object " + std::to_string(i) + ": singular mvInverse";
+            return RT_ERR_UNSUPPORTED;
+        }
+        for (int r = 0; r < 3; ++r) g.c[r] = -(F.a[r][0] * mi[12] + F.a[r][1] * mi[13] + F.a[r][2] * mi[14]);
+        singular_range(F, g.smin, g.smax);
+        if (!(g.smin > 0) || !std::isfinite(g.smax)) {
+            err = "object " + std::to_string(i) + ": degenerate transform";
+            return RT_ERR_UNSUPPORTED;
+        }
+        if (o.type == 0u) {
+            for (int r = 0; r < 3; ++r) g.ext[r] = sqrt(F.a[r][0] * F.a[r][0] + F.a[r][1] * F.a[r][1] + F.a[r][2] * F.a[r][2]);
+            g.R = g.smax;
+        } else {
+            for (int r = 0; r < 3; ++r) g.ext[r] = 0.5 * (fabs(F.a[r][0]) + fabs(F.a[r][1]) + fabs(F.a[r][2]));
+            double rmax = 0;
+            for (int sy = -1; sy <= 1; sy += 2)
+                for (int sz = -1; sz <= 1; sz += 2) {
+                    double v2 = 0;
+                    for (int r = 0; r < 3; ++r) {
+                        const double v = 0.5 * (F.a[r][0] + sy * F.a[r][1] + sz * F.a[r][2]);
+                        v2 += v * v;
+                    }
+                    rmax = std::max(rmax, sqrt(v2));
+                }
+            g.R = rmax;
+        }
+        const double cn = sqrt(g.c[0] * g.c[0] + g.c[1] * g.c[1] + g.c[2] * g.c[2]);
+        r0 = std::max(r0, cn + g.R);
+    }
+    // Ray origins: the camera (0), caller rays (omax_user) and points on object surfaces + skin.
+    const double omax = std::max(1.05 * r0 + 1.0, (double)omax_user * 1.0001 + 1e-3);
+    out.omax = (float)omax;
+    out.scene_radius = (float)r0;
+
+    // ---- pass 2: padded bounds
+    std::vector<ObjBound> ob(n_objs);
+    std::vector<uint32_t> live;
+    live.reserve(n_objs);
+    for (uint32_t i = 0; i < n_objs; ++i) {
+        const Geo& g = geo[i];
+        CullRec& cr = out.cull[i];
+        cr.type = objs[i].type;
+        if (objs[i].type > 1u) {
+            cr.cx = cr.cy = cr.cz = 0.f;
+            cr.r2 = -1.f;  // h*|oc|^2 - dt^2 >= ... never <= -1 unless NaN
+            cr.h = 1.f;
+            cr.cc = 0.f;
+            cr.e0 = 1.f;
+            continue;
+        }
+        const double ratio = g.smax / g.smin;
+        const double gg = K_FUZZ * U * ratio * ratio + 24.0 * U;
+        if (gg > 0.25) {
+            err = "object " + std::to_string(i) + ": anisotropy too extreme for conservative bounds";
+            return RT_ERR_UNSUPPORTED;
+        }
+        const double cn = sqrt(g.c[0] * g.c[0] + g.c[1] * g.c[1] + g.c[2] * g.c[2]);
+        // rounding of s = mvInverse * (o, w): 4 products / 3 sums of magnitude <= (|o| + |c|) / sigma_min each,
+        // plus the drift of w away from 1 (mvInverse[15] != 1 after glm::inverse), mapped back to view space.
+        const double pad = ratio * (omax + cn) * (32.0 * U + 40.0 * wdev_max) + 1e-6 * g.R;
+        ObjBound& b = ob[i];
+        for (int a = 0; a < 3; ++a) {
+            b.c[a] = g.c[a];
+            b.half[a] = g.ext[a] * (1.0 + 1e-6) + pad;
+        }
+        b.R = g.R * (1.0 + 1e-6) + pad;
+        b.g = gg;
+        b.f = sqrt(gg);
+        cr.cx = (float)g.c[0];
+        cr.cy = (float)g.c[1];
+        cr.cz = (float)g.c[2];
+        // centre rounding to float moves the sphere by <= u*|c|: add it to the radius
+        const double Rf = b.R + 2.0 * U * cn;
+        cr.r2 = up(Rf * Rf);
+        cr.h = down(1.0 - gg);
+        const double ccf = (double)cr.cx * cr.cx + (double)cr.cy * cr.cy + (double)cr.cz * cr.cz;
+        cr.cc = (float)ccf;
+        cr.e0 = down((double)cr.h * ccf * (1.0 - 8.0 * U) - (double)cr.r2);
+        live.push_back(i);
+    }
+
+    // ---- BVH over the live objects
+    out.root = 0;
+    if (live.empty()) {
+        out.root = ~0;  // empty leaf; never dereferenced because n_objs == 0 or count handled below
+        BvhNode n;
+        memset(&n, 0, sizeof n);
+        out.nodes.push_back(n);
+        out.nodef.push_back(BvhNodeF{0.f, 0.f});
+        out.leaf_obj.push_back(0);
+        CullRec dead;
+        memset(&dead, 0, sizeof dead);
+        dead.r2 = -1.f;
+        dead.h = 1.f;
+        dead.type = 2u;
+        out.leaf_cull.push_back(dead);
+        return RT_OK;
+    }
+    std::vector<ObjBound> lob(live.size());
+    for (size_t i = 0; i < live.size(); ++i) lob[i] = ob[live[i]];
+    Builder bld(lob, leaf_size);
+    bld.bn.reserve(2 * live.size());
+    const int root = bld.build(0, (uint32_t)live.size(), 0);
+    out.bvh_depth = bld.max_depth;
+
+    out.leaf_obj.resize(live.size());
+    out.leaf_cull.resize(live.size());
+    for (size_t i = 0; i < live.size(); ++i) {
+        out.leaf_obj[i] = live[bld.idx[i]];
+        out.leaf_cull[i] = out.cull[out.leaf_obj[i]];
+    }
+    // flatten: inner BuildNodes get consecutive indices in DFS order
+    std::vector<int32_t> inner_index(bld.bn.size(), -1);
+    int32_t n_inner = 0;
+    for (size_t i = 0; i < bld.bn.size(); ++i)
+        if (bld.bn[i].left >= 0) inner_index[i] = n_inner++;
+    out.nodes.resize(std::max(n_inner, 1));
+    out.nodef.resize(std::max(n_inner, 1));
+    memset(out.nodes.data(), 0, out.nodes.size() * sizeof(BvhNode));
+    auto ref_of = [&](int bi) -> int32_t {
+        const BuildNode& n = bld.bn[bi];
+        if (n.left >= 0) return inner_index[bi];
+        return ~(int32_t)((n.first << 4) | (n.count - 1));
+    };
+    auto child = [&](int bi, float* lo, float* hi, float& a, float& f) {
+        const BuildNode& n = bld.bn[bi];
+        double rf2 = 0;
+        for (int k = 0; k < 3; ++k) {
+            lo[k] = down(n.lo[k]);
+            hi[k] = up(n.hi[k]);
+            const double m = std::max(fabs(n.lo[k]), fabs(n.hi[k]));
+            rf2 += m * m;
+        }
+        const double rfar = sqrt(rf2);
+        f = up(n.f);
+        // slab arithmetic of cv::box_may_hit: (lo - o) rounds with error <= u * max(|lo|, |o|)
+        a = up(8.0 * U * (omax + rfar) + (double)f * rfar * (1.0 + 1e-6));
+    };
+    for (size_t i = 0; i < bld.bn.size(); ++i) {
+        const BuildNode& n = bld.bn[i];
+        if (n.left < 0) continue;
+        BvhNode& d = out.nodes[inner_index[i]];
+        BvhNodeF& df = out.nodef[inner_index[i]];
+        child(n.left, d.lo0, d.hi0, d.a0, df.f0);
+        child(n.right, d.lo1, d.hi1, d.a1, df.f1);
+        d.c0 = ref_of(n.left);
+        d.c1 = ref_of(n.right);
+    }
+    out.root = ref_of(root);
+    return RT_OK;
+}
+
+}  // namespace rt

@@ -1,0 +1,42 @@
+// rt_scene.hpp -- host-side repacking of the AoS scene (rt_object / rt_light, the layout of
+// cl_ObjectData / cl_Light in OpenCLRaytracer.hpp:41-58) into the device SoA, the conservative
+// bounds of every object and the BVH over them.
+#pragma once
+
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/rt_b200.h"
+#include "rt_layout.h"
+
+namespace rt {
+
+struct F4 {
+    float x, y, z, w;
+};
+
+struct HostScene {
+    std::vector<F4> minv;  // 4 per object (columns of mvInverse)
+    std::vector<F4> mv;    // 4 per object
+    std::vector<F4> mat;   // 3 per object
+    std::vector<CullRec> cull;
+    std::vector<BvhNode> nodes;
+    std::vector<BvhNodeF> nodef;
+    std::vector<uint32_t> leaf_obj;
+    std::vector<CullRec> leaf_cull;
+    std::vector<F4> lights;  // 4 per light
+    uint32_t n_objs = 0, n_lights = 0;
+    int32_t root = 0;      // child-style reference
+    float omax = 0.f;      // bound on |ray origin| the pads were computed for
+    float scene_radius = 0.f;
+    uint32_t bvh_depth = 0;
+};
+
+// Returns RT_OK or RT_ERR_UNSUPPORTED / RT_ERR_INVALID with a message in err.
+// omax_user: largest |origin| of caller-supplied rays (0 for the pinhole camera).
+int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, uint32_t n_lights, float omax_user,
+                int leaf_size, HostScene& out, std::string& err);
+
+}  // namespace rt

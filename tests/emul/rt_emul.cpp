@@ -1,0 +1,115 @@
+// TEST INFRASTRUCTURE -- not part of the product path.
+//
+// Host emulation of the CUDA path's device code: the same headers the kernels are made of, compiled for the
+// CPU through cuda_shim.h, driven one pixel at a time.  Used by the CPU-only tests to check filters, BVH and
+// the per-pixel state machine against the oracle before GPU time is spent.  Never loaded by the product.
+#include "cuda_shim.h"
+
+#include <string>
+#include <thread>
+#include <vector>
+#include <atomic>
+
+#include "../../opencl-raytracer_b200/csrc/rt_pixel.cuh"
+#include "../../opencl-raytracer_b200/csrc/rt_scene.hpp"
+
+namespace {
+
+void bind(const rt::HostScene& hs, rt::Scene& s) {
+    memset(&s, 0, sizeof s);
+    s.minv = reinterpret_cast<const float4*>(hs.minv.data());
+    s.mv = reinterpret_cast<const float4*>(hs.mv.data());
+    s.mat = reinterpret_cast<const float4*>(hs.mat.data());
+    s.cull = hs.cull.data();
+    s.nodes = hs.nodes.data();
+    s.nodef = hs.nodef.data();
+    s.leaf_obj = hs.leaf_obj.data();
+    s.leaf_cull = hs.leaf_cull.data();
+    s.lights = reinterpret_cast<const rt::Light*>(hs.lights.data());
+    s.n_objs = hs.n_objs;
+    s.n_lights = hs.n_lights;
+    s.n_nodes = (uint32_t)hs.nodes.size();
+    s.root = hs.root;
+}
+
+template <int ACCEL>
+void run(const rt::Scene& sc, const rt::Frame& fr, uint64_t n, int nthreads, rt::Counters* total) {
+    if (nthreads <= 0) nthreads = (int)std::thread::hardware_concurrency();
+    if (nthreads < 1) nthreads = 1;
+    std::atomic<uint64_t> next{0};
+    std::vector<rt::LocalCounters> lcs(nthreads);
+    auto worker = [&](int t) {
+        for (;;) {
+            const uint64_t b = next.fetch_add(256);
+            if (b >= n) return;
+            const uint64_t e = b + 256 < n ? b + 256 : n;
+            for (uint64_t i = b; i < e; ++i) {
+                rt::Ray ray;
+                ray.s = reinterpret_cast<const float4*>(fr.rays + i)[0];
+                ray.d = reinterpret_cast<const float4*>(fr.rays + i)[1];
+                rt::render_pixel<ACCEL, true>(sc, fr, ray, i, false, lcs[t]);
+            }
+        }
+    };
+    std::vector<std::thread> pool;
+    for (int t = 0; t < nthreads; ++t) pool.emplace_back(worker, t);
+    for (auto& t : pool) t.join();
+    memset(total, 0, sizeof *total);
+    for (auto& l : lcs) {
+        total->ref_primary += l.ref_primary;
+        total->ref_shadow += l.ref_shadow;
+        total->ref_reflect += l.ref_reflect;
+        total->traced_shadow += l.traced_shadow;
+        total->traced_reflect += l.traced_reflect;
+        total->pair_tests += l.pair_tests;
+        total->exact_tests += l.exact_tests;
+        total->node_visits += l.node_visits;
+        total->hit_pixels += l.hit_pixels;
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+// counters_out: 9 x uint64 in the order of rt::Counters.  Returns rt_status; message via emul_last_error().
+static thread_local std::string g_err;
+const char* emul_last_error(void) { return g_err.c_str(); }
+
+int emul_render(const rt_object* objs, uint32_t n_objs, const rt_light* lights, uint32_t n_lights, const rt_ray* rays,
+                uint64_t n_rays, uint32_t max_bounces, int mode, int accel, int skip_dead, int leaf, float omax_user,
+                float* out_rgba, int32_t* hit_id, float* hit_t, uint64_t* counters_out, int nthreads) {
+    rt::HostScene hs;
+    const int rc = rt::build_scene(objs, n_objs, lights, n_lights, omax_user, leaf, hs, g_err);
+    if (rc != RT_OK) return rc;
+    rt::Scene sc;
+    bind(hs, sc);
+    rt::Frame fr;
+    memset(&fr, 0, sizeof fr);
+    fr.rays = reinterpret_cast<const rt::Ray*>(rays);
+    fr.n_local = n_rays;
+    fr.max_bounces = max_bounces;
+    fr.mode = mode;
+    fr.skip_dead = skip_dead;
+    fr.out = reinterpret_cast<float4*>(out_rgba);
+    fr.hit_id = hit_id;
+    fr.hit_t = hit_t;
+    rt::Counters total;
+    if (accel == 0) run<0>(sc, fr, n_rays, nthreads, &total);
+    else if (accel == 1) run<1>(sc, fr, n_rays, nthreads, &total);
+    else run<2>(sc, fr, n_rays, nthreads, &total);
+    if (counters_out) memcpy(counters_out, &total, sizeof total);
+    return RT_OK;
+}
+
+// BVH facts for the host-logic tests
+int emul_bvh_info(const rt_object* objs, uint32_t n_objs, int leaf, uint32_t* n_nodes, uint32_t* depth, float* omax) {
+    rt::HostScene hs;
+    const int rc = rt::build_scene(objs, n_objs, nullptr, 0, 0.f, leaf, hs, g_err);
+    if (rc != RT_OK) return rc;
+    *n_nodes = (uint32_t)hs.nodes.size();
+    *depth = hs.bvh_depth;
+    *omax = hs.omax;
+    return RT_OK;
+}
+}

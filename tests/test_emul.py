@@ -1,0 +1,147 @@
+"""CPU tier: the CUDA path's device code (rt_device.cuh / rt_pixel.cuh / rt_scene.cpp) compiled for the host
+(tests/emul) against the oracle.  This checks, without a GPU, that the conservative filters and the BVH never
+lose a hit the reference arithmetic would find, and that the per-pixel state machine -- including the
+dead-ray skipping -- is output-identical to the reference kernel."""
+import numpy as np
+import pytest
+
+import emul
+from helpers import frame_rays, random_rays
+from pyrt import scenes as S
+from pyrt import types as T
+
+
+def _scene(name):
+    return S.kat2_scene() if name == "kat2" else S.load_reference_scene(name)
+
+
+@pytest.mark.parametrize("name", list(S.REFERENCE_SCENES) + ["simpleScene3L", "kat2"])
+@pytest.mark.parametrize("accel", [0, 1, 2])
+def test_device_code_bit_exact_on_reference_scenes(oracle_mod, name, accel):
+    objs, lights = _scene(name)
+    _, rays = frame_rays(128, 72)
+    for mode in (0, 1, 2):
+        ref, hid, ht, st = oracle_mod.port_render(mode, 30, objs, lights, rays)
+        for skip_dead in (0, 1):
+            out, eid, et, c = emul.render(objs, lights, rays, 30, mode, accel, skip_dead)
+            assert np.array_equal(eid, hid) and np.array_equal(et, ht)
+            assert np.array_equal(out, ref)
+            assert (c["ref_primary"], c["ref_shadow"], c["ref_reflect"]) == (st.rays_primary, st.rays_shadow, st.rays_reflect)
+            assert c["traced_shadow"] <= c["ref_shadow"] and c["traced_reflect"] <= c["ref_reflect"]
+            if not skip_dead and mode == 2:
+                assert c["traced_shadow"] == c["ref_shadow"] and c["traced_reflect"] == c["ref_reflect"]
+
+
+@pytest.mark.parametrize("second_type", [T.BOX, T.SPHERE])
+def test_bvh_and_cull_equal_brute_force_synthetic(oracle_mod, second_type):
+    objs, lights = S.synthetic_scene(3000, 300, second_type=second_type)
+    _, rays = frame_rays(96, 54)
+    ref, hid, ht, st = oracle_mod.port_render(2, 4, objs, lights, rays)
+    assert st.rays_reflect > st.hit_pixels  # reflective materials are exercised
+    for accel in (1, 2):
+        out, eid, et, c = emul.render(objs, lights, rays, 4, 2, accel, 1)
+        assert np.array_equal(eid, hid) and np.array_equal(et, ht) and np.array_equal(out, ref)
+    for leaf in (1, 2, 8, 16):
+        out, eid, et, c = emul.render(objs, lights, rays, 4, 2, 2, 1, leaf=leaf)
+        assert np.array_equal(eid, hid) and np.array_equal(out, ref)
+
+
+def test_filters_never_drop_a_noisy_hit(oracle_mod):
+    """Adversarial for the bounds: tiny, strongly anisotropic spheres very far from the ray origins, where the
+    reference's discriminant is dominated by rounding noise (rt_scene.cpp header)."""
+    rng = np.random.Generator(np.random.PCG64(7))
+    n = 400
+    objs, _ = S.synthetic_scene(n, 0, seed=11, second_type=T.SPHERE)
+    # shrink every object by 20x about its centre: mv' = mv * S(1/20), mvInverse' = S(20) * mvInverse
+    mv = objs["mv"].reshape(n, 4, 4).copy()
+    mi = objs["mvInverse"].reshape(n, 4, 4).copy()
+    mv[:, :3, :] *= np.float32(1 / 16.0)     # columns 0..2 of mv
+    mi[:, :, :3] *= np.float32(16.0)         # rows 0..2 of mvInverse (incl. translation)
+    objs["mv"], objs["mvInverse"] = mv.reshape(n, 16), mi.reshape(n, 16)
+    # rays aimed at (jittered) object centres from far away, arbitrary direction length
+    centre = mv[:, 3, :3]
+    k = 6000
+    pick = rng.integers(0, n, k)
+    o = (rng.normal(size=(k, 3)) * 150.0).astype(np.float32)
+    tgt = centre[pick] + (rng.normal(size=(k, 3)) * 0.03).astype(np.float32)
+    rays = np.zeros(k, dtype=T.RAY_DTYPE)
+    rays["start"][:, :3] = o
+    rays["start"][:, 3] = 1.0
+    rays["direction"][:, :3] = (tgt - o) * rng.uniform(0.5, 30.0, size=(k, 1)).astype(np.float32)
+    hid, ht = oracle_mod.port_trace(objs, rays)
+    assert (hid >= 0).sum() > k // 10
+    lights = np.zeros(0, dtype=T.LIGHT_DTYPE)
+    for accel in (1, 2):
+        _, eid, et, _ = emul.render(objs, lights, rays, 0, 0, accel, 1)
+        assert np.array_equal(eid, hid) and np.array_equal(et, ht)
+
+
+def test_random_rays_nearest_hit(oracle_mod):
+    objs, _ = S.synthetic_scene(2000, 400)
+    rays = random_rays(5000, 3)
+    hid, ht = oracle_mod.port_trace(objs, rays)
+    lights = np.zeros(0, dtype=T.LIGHT_DTYPE)
+    for accel in (0, 1, 2):
+        _, eid, et, _ = emul.render(objs, lights, rays, 0, 0, accel, 1)
+        assert np.array_equal(eid, hid) and np.array_equal(et, ht)
+
+
+def test_tie_rules_coincident_objects(oracle_mod):
+    """Exact ties: duplicated spheres (highest index wins) and duplicated boxes (lowest index wins), SAR:108,147."""
+    base, lights = S.kat2_scene()
+    objs = np.concatenate([base[[0]], base[[1]], base[[0]], base[[1]], base[[2]], base[[2]]])
+    _, rays = frame_rays(160, 90)
+    ref, hid, ht, _ = oracle_mod.port_render(2, 4, objs, lights, rays)
+    assert set(np.unique(hid)) == {-1, 0, 3, 5}
+    for accel in (0, 1, 2):
+        out, eid, et, _ = emul.render(objs, lights, rays, 4, 2, accel, 1, leaf=1)
+        assert np.array_equal(eid, hid) and np.array_equal(out, ref)
+
+
+def test_degenerate_inputs(oracle_mod):
+    objs, lights = S.kat2_scene()
+    _, rays = frame_rays(64, 36)
+    # no lights: shade() returns black, reflection still runs
+    nol = lights[:0]
+    ref, hid, *_ = oracle_mod.port_render(2, 4, objs, nol, rays)
+    for accel in (0, 1, 2):
+        out, eid, *_ = emul.render(objs, nol, rays, 4, 2, accel, 1)
+        assert np.array_equal(out, ref) and np.array_equal(eid, hid)
+    # no objects: every pixel keeps {0,0,0,1}
+    out, eid, *_ = emul.render(objs[:0], lights, rays, 4, 2, 2, 1)
+    assert np.all(out == np.array([0, 0, 0, 1], dtype=np.float32)) and np.all(eid == -1)
+    # axis-parallel rays (direction component exactly 0 -> the copysign branch of the slab test, SAR:36-43),
+    # origins inside a box / inside a sphere, unknown primitive type (skipped by the kernels' switch)
+    r = np.zeros(7, dtype=T.RAY_DTYPE)
+    r["start"][:, 3] = 1.0
+    r["start"][:, :3] = [(0, 0, 0), (0, 0, 0), (1, 1, 0), (0, 0, -10), (3, 2, -7), (5, 0, -10), (0, 5, -10)]
+    r["direction"][:, :3] = [(0, 0, -1), (0, 0, 1), (0, 0, -3), (0, 1, 0), (1, 0, 0), (-1, 0, 0), (0, -2, 0)]
+    weird = objs.copy()
+    weird = np.concatenate([weird, weird[[1]]])
+    weird[3]["type"] = 7
+    hid, ht = oracle_mod.port_trace(weird, r)
+    assert (hid >= 0).sum() >= 5 and not (hid == 3).any()
+    for accel in (0, 1, 2):
+        _, eid, et, _ = emul.render(weird, lights, r, 0, 0, accel, 1)
+        assert np.array_equal(eid, hid) and np.array_equal(et, ht)
+    # max_bounces 0 and 1 exercise the uint wrap of `bounces` (SAR:258,268,281)
+    _, rays = frame_rays(96, 54)
+    for mb in (0, 1, 2):
+        ref, *_ = oracle_mod.port_render(2, mb, objs, lights, rays)
+        for sd in (0, 1):
+            out, *_ = emul.render(objs, lights, rays, mb, 2, 2, sd)
+            assert np.array_equal(out, ref)
+
+
+def test_unsupported_scenes_are_rejected():
+    objs, lights = S.kat2_scene()
+    _, rays = frame_rays(8, 8)
+    bad = objs.copy()
+    bad[0]["mvInverse"][3] = 0.25  # projective row
+    with pytest.raises(RuntimeError):
+        emul.render(bad, lights, rays)
+    bad = objs.copy()
+    bad[1]["mvInverse"][:] = 0
+    bad[1]["mvInverse"][15] = 1
+    with pytest.raises(RuntimeError):
+        emul.render(bad, lights, rays)

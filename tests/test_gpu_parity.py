@@ -1,0 +1,200 @@
+"""GPU tier: the CUDA path through the C ABI (ctypes -> librt_b200.so) against the oracle on the same inputs.
+
+Bar (BASELINE.json north_star / SURVEY.md 8(d)): hit ids bit-exact; t and colours |d| <= 1e-4 * max(1,|ref|)
+(FP32; the only non-bit-exact operation on the CUDA side is powf), PPM <= 1 LSB per channel; missed pixels
+exactly (0,0,0,1).  Full-size frames are checked through size-independent properties (BVH == filter == brute
+force, sharded == unsharded, checksums) because the CPU oracle cannot finish them."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from helpers import assert_colours_close, frame_rays, random_rays
+from pyrt import scenes as S
+from pyrt import types as T
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+ALL_SCENES = list(S.REFERENCE_SCENES) + ["simpleScene3L", "kat2"]
+
+
+def _scene(name):
+    return S.kat2_scene() if name == "kat2" else S.load_reference_scene(name)
+
+
+@pytest.mark.parametrize("name", ALL_SCENES)
+def test_reference_scenes_all_modes_all_searches(rt, ctx, oracle_mod, name):
+    objs, lights = _scene(name)
+    W, H = 320, 180
+    z, rays = frame_rays(W, H)
+    ctx.set_option(rt.OPT_COUNT_RAYS, 1)
+    ctx.upload_scene(objs, lights)
+    ctx.set_camera(W, H, z)
+    for mode in (0, 1, 2):
+        ref, hid, ht, st = oracle_mod.port_render(mode, 30, objs, lights, rays)
+        for accel in (0, 1, 2, -1):
+            out = ctx.render(30, mode, accel)
+            assert_colours_close(out, ref)
+            assert np.array_equal(out[hid < 0], ref[hid < 0])
+            s = ctx.stats()
+            assert (s.rays_primary, s.rays_shadow, s.rays_reflect) == (st.rays_primary, st.rays_shadow, st.rays_reflect)
+            assert s.hit_pixels == st.hit_pixels and s.pixels == W * H
+            gid, gt = ctx.render_aov(accel)
+            assert np.array_equal(gid, hid) and np.array_equal(gt, ht)
+
+
+def test_camera_rays_equal_host_rays(rt, ctx, oracle_mod):
+    """Device ray generation is bit-identical to main()'s loop (OpenCL-Raytracer.cpp:68-72)."""
+    objs, lights = S.load_reference_scene("roundedCube")
+    W, H = 200, 120
+    z, rays = frame_rays(W, H)
+    ctx.upload_scene(objs, lights)
+    ctx.set_camera(W, H, z)
+    a = ctx.render(30, 2, 1).copy()
+    ctx.set_rays(rays)
+    b = ctx.render(30, 2, 1)
+    assert np.array_equal(a, b)
+
+
+def test_golden_vectors(rt, ctx):
+    kat = json.load(open(os.path.join(HERE, "golden", "kat.json")))
+    for case in kat["cases"]:
+        objs, lights = _scene(case["scene"])
+        W, H = case["width"], case["height"]
+        z = T.camera_zdir(H)
+        ctx.set_option(rt.OPT_COUNT_RAYS, 1)
+        ctx.set_option(rt.OPT_SKIP_DEAD_RAYS, 0)
+        ctx.upload_scene(objs, lights)
+        ctx.set_camera(W, H, z)
+        out = ctx.render(case["max_bounces"], case["mode"], -1)
+        for px in case["pixels"]:
+            got = out[px["jj"] * W + px["ii"], :3]
+            ref = np.asarray(px["rgb"], dtype=np.float32)
+            assert np.all(np.abs(got - ref) <= 1e-4 * np.maximum(1, np.abs(ref))), (case["name"], px, got)
+        if "sum_rgb" in case:
+            assert np.allclose(out[:, :3].astype(np.float64).sum(axis=0), case["sum_rgb"], rtol=1e-6)
+            s = ctx.stats()
+            assert [s.rays_primary, s.rays_shadow, s.rays_reflect] == case["rays"]
+            assert [s.rays_primary, s.traced_shadow, s.traced_reflect] == case["rays"]  # nothing skipped
+        ctx.set_option(rt.OPT_SKIP_DEAD_RAYS, 1)
+
+
+@pytest.mark.parametrize("second_type", [T.BOX, T.SPHERE])
+def test_synthetic_scene_against_oracle(rt, ctx, oracle_mod, second_type):
+    objs, lights = S.synthetic_scene(6000, 500, second_type=second_type)
+    W, H = 160, 90
+    z, rays = frame_rays(W, H)
+    ref, hid, ht, st = oracle_mod.port_render(2, 4, objs, lights, rays)
+    ctx.set_option(rt.OPT_COUNT_RAYS, 1)
+    ctx.upload_scene(objs, lights)
+    ctx.set_camera(W, H, z)
+    for accel in (0, 1, 2):
+        for skip in (0, 1):
+            ctx.set_option(rt.OPT_SKIP_DEAD_RAYS, skip)
+            out = ctx.render(4, 2, accel)
+            assert_colours_close(out, ref)
+            s = ctx.stats()
+            assert (s.rays_primary, s.rays_shadow, s.rays_reflect) == (st.rays_primary, st.rays_shadow, st.rays_reflect)
+            if not skip:
+                assert (s.traced_shadow, s.traced_reflect) == (st.rays_shadow, st.rays_reflect)
+        gid, gt = ctx.render_aov(accel)
+        assert np.array_equal(gid, hid) and np.array_equal(gt, ht)
+
+
+def test_trace_random_rays(rt, ctx, oracle_mod):
+    objs, lights = S.synthetic_scene(4000, 600)
+    rays = random_rays(20000, 5)
+    hid, ht = oracle_mod.port_trace(objs, rays)
+    ctx.upload_scene(objs, lights)
+    for accel in (0, 1, 2):
+        gid, gt = ctx.trace(rays, accel)
+        assert np.array_equal(gid, hid) and np.array_equal(gt, ht)
+
+
+def test_full_size_scene_bvh_equals_filter(rt, ctx):
+    """cfg5 geometry (100k boxes + 4096 spheres) on a 512x288 frame: BVH == bounding-sphere filter, bit for bit
+    (ids, t, colours); plus a band of exact brute force."""
+    objs, lights = S.synthetic_scene()
+    W, H = 512, 288
+    z = T.camera_zdir(H)
+    ctx.upload_scene(objs, lights)
+    ctx.set_camera(W, H, z)
+    a = ctx.render(4, 2, 2).copy()
+    ida, ta = ctx.render_aov(2)
+    b = ctx.render(4, 2, 1)
+    idb, tb = ctx.render_aov(1)
+    assert np.array_equal(ida, idb) and np.array_equal(ta, tb) and np.array_equal(a, b)
+    assert (ida >= 0).mean() > 0.5
+    rays = T.camera_rays(W, H, z, rows=[100, 101, 200])
+    idc, tc = ctx.trace(rays, 0)
+    sel = np.r_[100 * W:102 * W, 200 * W:201 * W]
+    assert np.array_equal(idc, ida[sel]) and np.array_equal(tc, ta[sel])
+
+
+def test_sharded_render_equals_whole_frame(rt, oracle_mod):
+    objs, lights = S.synthetic_scene(3000, 300)
+    W, H = 192, 100  # 100 rows: ragged last row-block
+    z = T.camera_zdir(H)
+    with rt.Context(0) as c:
+        c.upload_scene(objs, lights)
+        c.set_camera(W, H, z)
+        whole = c.render(4, 2, 2).copy()
+    for n_shards, block_rows in ((2, 8), (3, 16), (8, 32)):
+        frame = np.full((W * H, 4), -7.0, dtype=np.float32)
+        total = 0
+        for s in range(n_shards):
+            with rt.Context(0) as c:
+                c.upload_scene(objs, lights)
+                c.set_camera(W, H, z)
+                c.set_shard(block_rows, s, n_shards)
+                c.render(4, 2, 2, out=frame)
+                total += c.stats().pixels
+        assert total == W * H
+        assert np.array_equal(frame, whole)
+
+
+def test_quantize_is_byte_identical_to_ppm_rule(rt, ctx):
+    rng = np.random.Generator(np.random.PCG64(1))
+    rgba = rng.uniform(-0.2, 1.3, size=(50000, 4)).astype(np.float32)
+    rgba[:8, :3] = [[0, 1, 0.5], [1 / 255, 2 / 255, 254 / 255], [0.999999, 1.000001, 0.00392156], [76 / 255] * 3,
+                    [0.3, 0.375826597, 0.536895216], [255.5 / 255, 3, -1], [1e-9, 0.99607843, 0.99607844], [0.5, 0.25, 0.75]]
+    assert np.array_equal(ctx.quantize_rgb8(rgba), T.quantize_ppm(rgba))
+
+
+def test_edge_cases(rt, ctx, oracle_mod):
+    objs, lights = S.kat2_scene()
+    z, rays = frame_rays(70, 37)  # neither dimension a multiple of the tile
+    ctx.upload_scene(objs, lights[:0])  # zero lights
+    ctx.set_camera(70, 37, z)
+    ref, *_ = oracle_mod.port_render(2, 4, objs, lights[:0], rays)
+    assert_colours_close(ctx.render(4, 2, 2), ref)
+    ctx.upload_scene(objs[:0], lights)  # zero objects
+    out = ctx.render(4, 2, -1)
+    assert np.all(out == np.array([0, 0, 0, 1], dtype=np.float32))
+    ctx.upload_scene(objs, lights)
+    for mb in (0, 1, 2):  # uint wrap of `bounces`
+        ref, *_ = oracle_mod.port_render(2, mb, objs, lights, rays)
+        assert_colours_close(ctx.render(mb, 2, 1), ref)
+    ctx.set_rays(rays[:0])  # empty ray set
+    assert ctx.render(4, 2, 1).shape == (0, 4)
+    ctx.set_rays(rays[:33])  # ragged: not a multiple of the warp
+    ref, *_ = oracle_mod.port_render(2, 4, objs, lights, rays[:33])
+    assert_colours_close(ctx.render(4, 2, 2), ref)
+
+
+def test_errors_are_reported_not_hidden(rt, ctx):
+    objs, lights = S.kat2_scene()
+    with pytest.raises(rt.RtError):
+        ctx.render(4, 2, 1)  # nothing uploaded
+    bad = objs.copy()
+    bad[0]["mvInverse"][7] = 0.5
+    with pytest.raises(rt.RtError) as e:
+        ctx.upload_scene(bad, lights)
+    assert e.value.code == -4
+    ctx.upload_scene(objs, lights)
+    with pytest.raises(rt.RtError):
+        ctx.render(4, 2, 1)  # no rays / camera
+    ctx.set_camera(16, 16, -10.0)
+    with pytest.raises(rt.RtError):
+        ctx.render(4, 9, 1)  # bad mode
