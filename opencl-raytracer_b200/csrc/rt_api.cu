@@ -13,6 +13,7 @@
 #include "../../include/rt_b200.h"
 #include "rt_kernels.cuh"
 #include "rt_scene.hpp"
+#include "rt_wavefront.cuh"
 
 namespace {
 
@@ -88,6 +89,15 @@ struct rt_ctx {
     DevBuf<float> d_hit_t;
     DevBuf<rt::Counters> d_counters;
     DevBuf<float> d_sink;
+
+    // wavefront pipeline buffers (allocated on first use)
+    DevBuf<float4> w_acc, w_refl, w_P, w_Nm, w_Rc, w_qs[2], w_qd[2];
+    DevBuf<uint32_t> w_out, w_qpath[2], w_counts;
+    DevBuf<float> w_res_t;
+    DevBuf<int32_t> w_res_id;
+    int sm_count = 148;
+    int last_pipeline = 0;
+    uint32_t last_launches = 1;
 
     // options
     int opt_pipeline = -1, opt_count = 0, opt_leaf = 4, opt_skip_dead = 1;
@@ -193,9 +203,9 @@ int collect_stats(rt_ctx* c, int accel, uint64_t pixels, uint32_t launches) {
     rt_stats& st = c->stats;
     memset(&st, 0, sizeof st);
     st.pixels = pixels;
-    st.kernel_launches = launches;
+    st.kernel_launches = c->last_launches ? c->last_launches : launches;
     st.accel_used = (uint32_t)accel;
-    st.pipeline_used = 0;
+    st.pipeline_used = (uint32_t)c->last_pipeline;
     if (c->opt_count) {
         rt::Counters h;
         RT_CUDA(cudaMemcpyAsync(&h, c->d_counters.p, sizeof h, cudaMemcpyDeviceToHost, c->stream));
@@ -213,21 +223,85 @@ int collect_stats(rt_ctx* c, int accel, uint64_t pixels, uint32_t launches) {
     return RT_OK;
 }
 
+// 0 megakernel, 1 wavefront.  The wavefront always skips dead rays, so asking for every reference ray
+// (RT_OPT_SKIP_DEAD_RAYS = 0) selects the megakernel; tiny scenes are launch-bound and stay on the megakernel too.
+int pick_pipeline(const rt_ctx* c, int accel) {
+    if (!c->opt_skip_dead) return 0;
+    if (c->opt_pipeline == 0 || c->opt_pipeline == 1) return c->opt_pipeline;
+    return (accel != RT_ACCEL_BRUTE && c->objs.size() > 48) ? 1 : 0;
+}
+
+int ensure_wave_buffers(rt_ctx* c, uint64_t capacity, uint32_t gens, rt::WaveBuffers& wb) {
+    if (capacity >= (1ull << 31)) return fail(RT_ERR_INVALID, "too many rays for one wavefront context");
+    RT_CUDA(c->w_acc.ensure(capacity));
+    RT_CUDA(c->w_refl.ensure(capacity));
+    RT_CUDA(c->w_P.ensure(capacity));
+    RT_CUDA(c->w_Nm.ensure(capacity));
+    RT_CUDA(c->w_Rc.ensure(capacity));
+    RT_CUDA(c->w_out.ensure(capacity));
+    for (int i = 0; i < 2; ++i) {
+        RT_CUDA(c->w_qs[i].ensure(capacity));
+        RT_CUDA(c->w_qd[i].ensure(capacity));
+        RT_CUDA(c->w_qpath[i].ensure(capacity));
+    }
+    RT_CUDA(c->w_res_t.ensure(capacity));
+    RT_CUDA(c->w_res_id.ensure(capacity));
+    RT_CUDA(c->w_counts.ensure(2 * (size_t)(gens + 2)));
+    wb.pa.acc = c->w_acc.p;
+    wb.pa.refl = c->w_refl.p;
+    wb.pa.P = c->w_P.p;
+    wb.pa.Nm = c->w_Nm.p;
+    wb.pa.Rc = c->w_Rc.p;
+    wb.pa.out = c->w_out.p;
+    for (int i = 0; i < 2; ++i) {
+        wb.q[i].s = c->w_qs[i].p;
+        wb.q[i].d = c->w_qd[i].p;
+        wb.q[i].path = c->w_qpath[i].p;
+    }
+    wb.res_t = c->w_res_t.p;
+    wb.res_id = c->w_res_id.p;
+    wb.counts = c->w_counts.p;
+    wb.n_counts = (uint32_t)(c->w_counts.n / 2);
+    wb.capacity = capacity;
+    return RT_OK;
+}
+
 // kernels of one render on c->stream, bracketed by ev0/ev1
-int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float4* out, int* accel_used) {
+int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float4* out, int* accel_used, bool aov_only = false) {
     int rc = sync_scene(c);
     if (rc != RT_OK) return rc;
     accel = pick_accel(c, accel);
     *accel_used = accel;
     rt::Frame fr;
     fill_frame_desc(c, fr, max_bounces, mode, out);
+    if (aov_only) {
+        fr.hit_id = c->d_hit_id.p;
+        fr.hit_t = c->d_hit_t.p;
+    }
     if (c->opt_count) {
         RT_CUDA(c->d_counters.ensure(1));
         RT_CUDA(cudaMemsetAsync(c->d_counters.p, 0, sizeof(rt::Counters), c->stream));
         fr.counters = c->d_counters.p;
     }
+    const int pipeline = pick_pipeline(c, accel);
+    c->last_pipeline = pipeline;
+    c->last_launches = 1;
+    if (pipeline == 1 && fr.n_local > 0) {
+        uint32_t gens = rt::wave_max_generations(max_bounces, c->scene.n_lights, mode);
+        if (gens > 4096) return fail(RT_ERR_INVALID, "max_bounces x lights too large for the wavefront pipeline; use RT_OPT_PIPELINE 0");
+        rt::WaveBuffers wb;
+        // camera tiles may include a ragged edge; capacity counts real pixels only
+        rc = ensure_wave_buffers(c, fr.n_local, gens, wb);
+        if (rc != RT_OK) return rc;
+        RT_CUDA(cudaEventRecord(c->ev0, c->stream));
+        uint32_t nl = 0;
+        RT_CUDA(rt::wave_render(c->scene, fr, wb, accel, (uint32_t)c->opt_leaf, c->sm_count, &nl, c->stream));
+        c->last_launches = nl;
+        RT_CUDA(cudaEventRecord(c->ev1, c->stream));
+        return RT_OK;
+    }
     RT_CUDA(cudaEventRecord(c->ev0, c->stream));
-    RT_CUDA(rt::launch_megakernel(c->scene, fr, accel, false, c->stream));
+    RT_CUDA(rt::launch_megakernel(c->scene, fr, accel, aov_only, c->stream));
     RT_CUDA(cudaEventRecord(c->ev1, c->stream));
     return RT_OK;
 }
@@ -257,6 +331,7 @@ int rt_create(rt_ctx** out, int device) {
     RT_CUDA(cudaSetDevice(device));
     rt_ctx* c = new rt_ctx();
     c->device = device;
+    c->sm_count = prop.multiProcessorCount;
     memset(&c->stats, 0, sizeof c->stats);
     memset(&c->scene, 0, sizeof c->scene);
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&c->ev0) != cudaSuccess ||
@@ -276,6 +351,9 @@ int rt_destroy(rt_ctx* c) {
     c->d_cull.release(); c->d_leaf_cull.release(); c->d_nodes.release(); c->d_nodef.release(); c->d_leaf_obj.release();
     c->d_rays.release(); c->d_fb.release(); c->d_hit_id.release(); c->d_hit_t.release(); c->d_counters.release();
     c->d_sink.release();
+    c->w_acc.release(); c->w_refl.release(); c->w_P.release(); c->w_Nm.release(); c->w_Rc.release(); c->w_out.release();
+    for (int i = 0; i < 2; ++i) { c->w_qs[i].release(); c->w_qd[i].release(); c->w_qpath[i].release(); }
+    c->w_res_t.release(); c->w_res_id.release(); c->w_counts.release();
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->ev2) cudaEventDestroy(c->ev2);
@@ -433,28 +511,15 @@ int rt_render_aov(rt_ctx* c, int accel, int32_t* host_hit_id, float* host_hit_t)
     if (rc != RT_OK) return rc;
     if (!host_hit_id || !host_hit_t) return fail(RT_ERR_INVALID, "null output buffer");
     RT_CUDA(cudaSetDevice(c->device));
-    rc = sync_scene(c);
-    if (rc != RT_OK) return rc;
-    accel = pick_accel(c, accel);
     const uint64_t n = n_pixels(c);
     RT_CUDA(c->d_hit_id.ensure(n));
     RT_CUDA(c->d_hit_t.ensure(n));
-    rt::Frame fr;
-    fill_frame_desc(c, fr, 0, RT_MODE_HITTEST, c->d_fb.p);
-    fr.hit_id = c->d_hit_id.p;
-    fr.hit_t = c->d_hit_t.p;
-    if (c->opt_count) {
-        RT_CUDA(c->d_counters.ensure(1));
-        RT_CUDA(cudaMemsetAsync(c->d_counters.p, 0, sizeof(rt::Counters), c->stream));
-        fr.counters = c->d_counters.p;
-    }
     if (c->use_camera && c->n_shards > 1) {  // rows of other shards read as "miss"
         RT_CUDA(cudaMemsetAsync(c->d_hit_id.p, 0xff, n * sizeof(int32_t), c->stream));
         RT_CUDA(cudaMemsetAsync(c->d_hit_t.p, 0, n * sizeof(float), c->stream));
     }
-    RT_CUDA(cudaEventRecord(c->ev0, c->stream));
-    RT_CUDA(rt::launch_megakernel(c->scene, fr, accel, true, c->stream));
-    RT_CUDA(cudaEventRecord(c->ev1, c->stream));
+    rc = render_on_device(c, 0, RT_MODE_HITTEST, accel, c->d_fb.p, &accel, true);
+    if (rc != RT_OK) return rc;
     if (n) {
         RT_CUDA(cudaMemcpyAsync(host_hit_id, c->d_hit_id.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
         RT_CUDA(cudaMemcpyAsync(host_hit_t, c->d_hit_t.p, n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));

@@ -25,6 +25,9 @@ def lib():
         _lib.emul_render.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, C.c_uint32,
                                      C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.c_int]
+        _lib.emul_render_wave.restype = C.c_int
+        _lib.emul_render_wave.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, C.c_uint32,
+                                          C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib.emul_bvh_info.restype = C.c_int
         _lib.emul_bvh_info.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
     return _lib
@@ -49,3 +52,20 @@ def render(objs, lights, rays, max_bounces=30, mode=2, accel=2, skip_dead=1, lea
     if rc != 0:
         raise RuntimeError("emul_render: %d %s" % (rc, lib().emul_last_error().decode()))
     return out, hid, ht, dict(zip(COUNTER_FIELDS, (int(x) for x in ctr)))
+
+
+def render_wave(objs, lights, rays, max_bounces=30, mode=2, accel=2, leaf=4):
+    """The wavefront state machine (rt_wave.cuh) on the host; returns (rgba, counters, generations)."""
+    objs = np.ascontiguousarray(objs)
+    lights = np.ascontiguousarray(lights)
+    rays = np.ascontiguousarray(rays)
+    n = rays.shape[0]
+    out = np.empty((n, 4), dtype=np.float32)
+    ctr = np.zeros(len(COUNTER_FIELDS), dtype=np.uint64)
+    gens = C.c_uint32(0)
+    omax = float(np.sqrt((rays["start"][:, :3].astype(np.float64) ** 2).sum(axis=1).max())) if n else 0.0
+    rc = lib().emul_render_wave(_ptr(objs), len(objs), _ptr(lights), len(lights), _ptr(rays), n, max_bounces, mode, accel,
+                                leaf, omax, _ptr(out), _ptr(ctr), C.byref(gens))
+    if rc != 0:
+        raise RuntimeError("emul_render_wave: %d %s" % (rc, lib().emul_last_error().decode()))
+    return out, dict(zip(COUNTER_FIELDS, (int(x) for x in ctr))), gens.value

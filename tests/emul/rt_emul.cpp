@@ -11,7 +11,15 @@
 #include <atomic>
 
 #include "../../opencl-raytracer_b200/csrc/rt_pixel.cuh"
+#include "../../opencl-raytracer_b200/csrc/rt_wave.cuh"
 #include "../../opencl-raytracer_b200/csrc/rt_scene.hpp"
+
+// same formula as rt::wave_max_generations (rt_wavefront.cu, a CUDA translation unit)
+static uint32_t rt_wave_max_generations_host(uint32_t max_bounces, uint32_t n_lights, int mode) {
+    if (mode == 0) return 1;
+    if (mode == 1) return 1 + n_lights;
+    return 1u + n_lights + max_bounces * (1u + n_lights);
+}
 
 namespace {
 
@@ -99,6 +107,80 @@ int emul_render(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
     else if (accel == 1) run<1>(sc, fr, n_rays, nthreads, &total);
     else run<2>(sc, fr, n_rays, nthreads, &total);
     if (counters_out) memcpy(counters_out, &total, sizeof total);
+    return RT_OK;
+}
+
+// The wavefront pipeline's state machine (rt_wave.cuh) driven generation by generation on the host: queues,
+// path state and compaction as in rt_wavefront.cu, the trace step done per ray with the functions above.
+int emul_render_wave(const rt_object* objs, uint32_t n_objs, const rt_light* lights, uint32_t n_lights, const rt_ray* rays,
+                     uint64_t n_rays, uint32_t max_bounces, int mode, int accel, int leaf, float omax_user, float* out_rgba,
+                     uint64_t* counters_out, uint32_t* generations_out) {
+    rt::HostScene hs;
+    const int rc = rt::build_scene(objs, n_objs, lights, n_lights, omax_user, leaf, hs, g_err);
+    if (rc != RT_OK) return rc;
+    rt::Scene sc;
+    bind(hs, sc);
+    const size_t n = (size_t)n_rays;
+    std::vector<float4> acc(n), refl(n), P(n), Nm(n), Rc(n), qs[2], qd[2];
+    std::vector<uint32_t> outi(n), qp[2];
+    rt::PathArrays pa{acc.data(), refl.data(), P.data(), Nm.data(), Rc.data(), outi.data()};
+    for (int i = 0; i < 2; ++i) {
+        qs[i].resize(n);
+        qd[i].resize(n);
+        qp[i].resize(n);
+    }
+    for (size_t i = 0; i < n; ++i) {
+        qs[0][i] = reinterpret_cast<const float4*>(rays + i)[0];
+        qd[0][i] = reinterpret_cast<const float4*>(rays + i)[1];
+        qp[0][i] = (uint32_t)i;
+        outi[i] = (uint32_t)i;
+        reinterpret_cast<float4*>(out_rgba)[i] = make_float4(-1.f, -1.f, -1.f, -1.f);
+    }
+    rt::WaveParams wp{max_bounces, mode};
+    rt::LocalCounters lc;
+    size_t cnt = n;
+    uint32_t g = 0;
+    while (cnt > 0) {
+        const int a = g & 1, b = (g + 1) & 1;
+        size_t nout = 0;
+        for (size_t i = 0; i < cnt; ++i) {
+            rt::Ray ray{qs[a][i], qd[a][i]};
+            const uint32_t pb = qp[a][i];
+            rt::Hit h;
+            unsigned long long ne = 0, nn = 0;
+            if (accel == 0) h = rt::trace_brute(sc, ray, &ne);
+            else if (accel == 1) h = rt::trace_cull(sc, ray, &ne);
+            else if (pb & RT_TASK_ANYHIT) h = rt::trace_bvh<true>(sc, ray, 1.f, &ne, &nn);
+            else h = rt::trace_bvh<false>(sc, ray, RT_MAX_FLOAT, &ne, &nn);
+            lc.exact_tests += ne;
+            lc.node_visits += nn;
+            rt::StepOut o;
+            const uint32_t p = pb & ~RT_TASK_ANYHIT;
+            rt::wave::step<true>(sc, wp, pa, p, g == 0, ray, h, o, lc);
+            if (o.emit) {
+                qs[b][nout] = o.ray.s;
+                qd[b][nout] = o.ray.d;
+                qp[b][nout] = p | (o.anyhit ? RT_TASK_ANYHIT : 0u);
+                ++nout;
+            }
+            if (o.write) reinterpret_cast<float4*>(out_rgba)[outi[p]] = o.px;
+        }
+        cnt = nout;
+        ++g;
+    }
+    if (generations_out) *generations_out = g;
+    if (g > rt_wave_max_generations_host(max_bounces, n_lights, mode)) {
+        g_err = "more generations than wave_max_generations allows";
+        return RT_ERR_INVALID;
+    }
+    if (counters_out) {
+        rt::Counters total;
+        memset(&total, 0, sizeof total);
+        total.ref_primary = lc.ref_primary; total.ref_shadow = lc.ref_shadow; total.ref_reflect = lc.ref_reflect;
+        total.traced_shadow = lc.traced_shadow; total.traced_reflect = lc.traced_reflect; total.pair_tests = lc.pair_tests;
+        total.exact_tests = lc.exact_tests; total.node_visits = lc.node_visits; total.hit_pixels = lc.hit_pixels;
+        memcpy(counters_out, &total, sizeof total);
+    }
     return RT_OK;
 }
 

@@ -145,3 +145,30 @@ def test_unsupported_scenes_are_rejected():
     bad[1]["mvInverse"][15] = 1
     with pytest.raises(RuntimeError):
         emul.render(bad, lights, rays)
+
+
+@pytest.mark.parametrize("name", list(S.REFERENCE_SCENES) + ["simpleScene3L", "kat2"])
+def test_wavefront_state_machine_bit_exact(oracle_mod, name):
+    """rt_wave.cuh (one ray in flight per path, queues, backward light walk) == the reference work-item."""
+    objs, lights = _scene(name)
+    _, rays = frame_rays(128, 72)
+    for mode in (0, 1, 2):
+        for mb in ((30, 0, 1, 2) if mode == 2 else (30,)):
+            ref, hid, ht, st = oracle_mod.port_render(mode, mb, objs, lights, rays)
+            out, c, gens = emul.render_wave(objs, lights, rays, mb, mode, 2)
+            assert np.array_equal(out, ref)
+            assert (c["ref_primary"], c["ref_shadow"], c["ref_reflect"]) == (st.rays_primary, st.rays_shadow, st.rays_reflect)
+            assert c["hit_pixels"] == st.hit_pixels
+
+
+def test_wavefront_state_machine_synthetic(oracle_mod):
+    objs, lights = S.synthetic_scene(2500, 300, n_lights=3)
+    _, rays = frame_rays(96, 54)
+    for mode in (1, 2):
+        ref, *_ = oracle_mod.port_render(mode, 4, objs, lights, rays)
+        for accel in (1, 2):
+            out, c, gens = emul.render_wave(objs, lights, rays, 4, mode, accel)
+            assert np.array_equal(out, ref)
+    out, c, gens = emul.render_wave(objs, lights[:0], rays, 4, 2, 2)
+    ref, *_ = oracle_mod.port_render(2, 4, objs, lights[:0], rays)
+    assert np.array_equal(out, ref)

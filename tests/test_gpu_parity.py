@@ -44,6 +44,63 @@ def test_reference_scenes_all_modes_all_searches(rt, ctx, oracle_mod, name):
             assert np.array_equal(gid, hid) and np.array_equal(gt, ht)
 
 
+@pytest.mark.parametrize("name", ALL_SCENES + ["synthetic"])
+def test_wavefront_pipeline_equals_megakernel_and_oracle(rt, ctx, oracle_mod, name):
+    """The wavefront pipeline (ray queues + ballot compaction, rt_wavefront.cu) gives the same bits as the
+    megakernel on the GPU and the oracle's ids / t / ray counts, for every mode and both accelerated searches."""
+    if name == "synthetic":
+        objs, lights = S.synthetic_scene(5000, 500, n_lights=3)
+        W, H, mb = 200, 112, 4
+    else:
+        objs, lights = _scene(name)
+        W, H, mb = 320, 180, 30
+    z, rays = frame_rays(W, H)
+    ctx.set_option(rt.OPT_COUNT_RAYS, 1)
+    ctx.upload_scene(objs, lights)
+    ctx.set_camera(W, H, z)
+    for mode in (0, 1, 2):
+        ref, hid, ht, st = oracle_mod.port_render(mode, mb, objs, lights, rays)
+        ctx.set_option(rt.OPT_PIPELINE, 0)
+        mega = ctx.render(mb, mode, 2).copy()
+        sm = ctx.stats().as_dict()
+        for accel in (1, 2):
+            ctx.set_option(rt.OPT_PIPELINE, 1)
+            out = ctx.render(mb, mode, accel)
+            s = ctx.stats()
+            assert s.pipeline_used == 1
+            assert np.array_equal(out, mega)
+            assert_colours_close(out, ref)
+            assert (s.rays_primary, s.rays_shadow, s.rays_reflect) == (st.rays_primary, st.rays_shadow, st.rays_reflect)
+            assert (s.traced_shadow, s.traced_reflect, s.hit_pixels) == (sm["traced_shadow"], sm["traced_reflect"], sm["hit_pixels"])
+            gid, gt = ctx.render_aov(accel)
+            assert np.array_equal(gid, hid) and np.array_equal(gt, ht)
+    ctx.set_option(rt.OPT_PIPELINE, -1)
+
+
+def test_wavefront_ragged_and_sharded(rt, oracle_mod):
+    objs, lights = S.synthetic_scene(3000, 300)
+    W, H = 131, 77
+    z, rays = frame_rays(W, H)
+    ref, *_ = oracle_mod.port_render(2, 4, objs, lights, rays)
+    frame = np.full((W * H, 4), -7.0, dtype=np.float32)
+    for s in range(3):
+        with rt.Context(0) as c:
+            c.set_option(rt.OPT_PIPELINE, 1)
+            c.upload_scene(objs, lights)
+            c.set_camera(W, H, z)
+            c.set_shard(8, s, 3)
+            c.render(4, 2, 2, out=frame)
+            assert c.stats().pipeline_used == 1
+    assert_colours_close(frame, ref)
+    with rt.Context(0) as c:
+        c.set_option(rt.OPT_PIPELINE, 1)
+        c.upload_scene(objs, lights)
+        c.set_rays(rays[:1000])
+        assert_colours_close(c.render(4, 2, 2), ref[:1000])
+        c.set_rays(rays[:0])
+        assert c.render(4, 2, 2).shape == (0, 4)
+
+
 def test_camera_rays_equal_host_rays(rt, ctx, oracle_mod):
     """Device ray generation is bit-identical to main()'s loop (OpenCL-Raytracer.cpp:68-72)."""
     objs, lights = S.load_reference_scene("roundedCube")
