@@ -53,6 +53,9 @@ def workload(name: str, args):
     if name == "cfg5-small":
         o, l = scenes.synthetic_scene(100_000, 4096)
         return o, l, 1920, 1080, 4, 2, "synthetic 100k boxes + 4096 spheres, 1920x1080, reflection depth 4"
+    if name == "cfg5-tiny":
+        o, l = scenes.synthetic_scene(100_000, 4096)
+        return o, l, 640, 360, 4, 2, "synthetic 100k boxes + 4096 spheres, 640x360, reflection depth 4"
     table = {
         "cfg1": ("simpleSphere", 2560, 1440, 30, 2),
         "cfg2": ("multipleSpheres", 1920, 1080, 3, 2),
@@ -240,6 +243,8 @@ def main():
     rays_traced = r_prim + t_shadow + t_refl
     rays_reference = r_prim + r_shadow + r_refl
     accel_used = st.accel_used
+    pipeline_used = st.pipeline_used
+    launches_per_step = st.kernel_launches
     ctx.set_option(lib.OPT_COUNT_RAYS, 0)
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
@@ -295,7 +300,8 @@ def main():
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
-    kernel_names = {0: "render_mega<brute>", 1: "render_mega<filter>", 2: "render_mega<bvh>"}
+    kernel_names = ({0: "wave_trace_brute", 1: "wave_trace_filter", 2: "wave_trace_bvh"} if pipeline_used == 1 else
+                    {0: "render_mega<brute>", 1: "render_mega<filter>", 2: "render_mega<bvh>"})
     shades = t_shadow  # one Phong evaluation per traced shadow ray
     if accel_used == 2:
         flops = node_visits * FLOPS_NODE + exact_tests * (FLOPS_EXACT + FLOPS_FILTER) + shades * FLOPS_SHADE
@@ -336,7 +342,7 @@ def main():
             fl = s2.pair_tests * FLOPS_FILTER + s2.exact_tests * FLOPS_EXACT + s2.traced_shadow * FLOPS_SHADE
             tf = fl / (best * 1e-3) / 1e12
             roofline_brute = {
-                "kernel": "render_mega<filter>", "bound": "fp32", "sample": "%d rows x %d px band at row %d" % (rows, W, r0),
+                "kernel": "wave_trace_filter" if s2.pipeline_used == 1 else "render_mega<filter>", "bound": "fp32", "sample": "%d rows x %d px band at row %d" % (rows, W, r0),
                 "pair_tests": s2.pair_tests, "ms": best, "achieved": tf, "peak": peak_tf, "unit": "TFLOP/s",
                 "frac": tf / peak_tf if peak_tf else None,
                 "reference_equivalent_tflops": s2.pair_tests * FLOPS_ALGO_PAIR / (best * 1e-3) / 1e12,
@@ -364,7 +370,7 @@ def main():
             "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": dict(config, accel=["brute", "filter", "bvh"][accel_used], pipeline="megakernel",
+            "config": dict(config, accel=["brute", "filter", "bvh"][accel_used], pipeline=["megakernel", "wavefront"][pipeline_used],
                            sharding="row-blocks of %d rows round-robin over %d ranks, peer stores into rank 0 (CUDA IPC)" % (args.block_rows, world)
                            if world > 1 else "single GPU",
                            l2="framebuffer %d MB > L2; 256 MB memset between steps flushes L2 (scene is re-read from HBM each step)" % (W * H * 16 >> 20),
@@ -375,7 +381,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": 0,
                     "d2h_bytes_per_step": W * H * 16,
                     "note": "rt_render == IRaytracer::Render(): launch + blocking readback; scene/camera resident as in the reference ctor"},
-            "gpu_launches": args.steps * 1,
+            "gpu_launches": args.steps * launches_per_step,
             "clocks": clocks,
             "roofline": roofline,
         }

@@ -157,6 +157,7 @@ int sync_scene(rt_ctx* c) {
     s.n_lights = c->hs.n_lights;
     s.n_nodes = (uint32_t)c->hs.nodes.size();
     s.root = c->hs.root;
+    s.root_f = c->hs.f_global;
     c->scene_dirty = false;
     return RT_OK;
 }

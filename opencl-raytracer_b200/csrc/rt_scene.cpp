@@ -476,6 +476,7 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
         d.c1 = ref_of(n.right);
     }
     out.root = ref_of(root);
+    out.f_global = up(bld.bn[root].f);
     return RT_OK;
 }
 

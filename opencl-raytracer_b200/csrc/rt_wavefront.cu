@@ -105,27 +105,29 @@ __global__ void __launch_bounds__(kBlock) wave_gen(const Frame fr, const TaskQue
 // ------------------------------------------------------------------------------------------------ trace: BVH
 constexpr int kPendCap = 8;
 
-struct LaneRay {  // what a lane keeps in registers for its ray
-    float ox, oy, oz, ux, uy, uz, idx, idy, idz, onorm;
-};
-
-__device__ __forceinline__ bool node_box(const LaneRay& k, float lx, float ly, float lz, float hx, float hy, float hz, float infl,
-                                         float tlimit, float& tnear) {
-    const float ax = (lx - k.ox) * k.idx, bx = (hx - k.ox) * k.idx;
-    const float ay = (ly - k.oy) * k.idy, by = (hy - k.oy) * k.idy;
-    const float az = (lz - k.oz) * k.idz, bz = (hz - k.oz) * k.idz;
-    const float nx = fmaf(-infl, fabsf(k.idx), fminf(ax, bx)), fx = fmaf(infl, fabsf(k.idx), fmaxf(ax, bx));
-    const float ny = fmaf(-infl, fabsf(k.idy), fminf(ay, by)), fy = fmaf(infl, fabsf(k.idy), fmaxf(ay, by));
-    const float nz = fmaf(-infl, fabsf(k.idz), fminf(az, bz)), fz = fmaf(infl, fabsf(k.idz), fmaxf(az, bz));
-    const float tn = fmaxf(fmaxf(nx, ny), nz);
-    const float tf = fminf(fminf(fx, fy), fz);
-    tnear = tn;
-    const float slack = 1e-5f * fmaxf(fabsf(tn), fabsf(tf));
-    return !(tn - slack > fminf(tf, tlimit)) && !(tf + slack < 0.f);
+// The reference arithmetic for one (ray, object) pair, kept out of line: it is long (two 4x4 transforms,
+// IEEE divides and a square root) and rare, and inlining it into the hot loops thrashes the instruction cache.
+__device__ __noinline__ void exact_pair_call(const Scene& sc, const float4 s, const float4 d, uint32_t obj, uint32_t type,
+                                             Hit& best, uint32_t& btype) {
+    Ray r;
+    r.s = s;
+    r.d = d;
+    exact_pair(sc, r, obj, type, best, btype);
 }
 
+// Persistent warps.  Every lane owns one ray of the queue and is in one of four states:
+//   T  traversing (stands on an inner node)           S  traversing, but its candidate buffer is nearly full
+//   F  traversal finished, candidates still queued    I  idle (no ray)
+// A node step tests the two child boxes; a child that is a leaf is not visited -- its objects go straight into
+// the lane's candidate buffer (shared memory) -- so the traversal loop consists of node steps only.  The warp
+// then schedules whole-warp rounds of the three activities so that each runs with most lanes taking part:
+//   node steps   while >= 20 lanes are in T (or nothing else is worth doing)
+//   exact tests  when >= 16 lanes have a candidate queued, a lane is in S, or nobody can traverse
+//   refill       when >= 8 lanes are idle (or nobody is traversing) and the queue is not exhausted
+// Deferring exact tests never changes the result: every queued candidate is tested before its ray retires, and
+// pruning against the best t found so far only ever skips nodes that cannot contain a better hit.
 template <bool COUNT>
-__global__ void __launch_bounds__(kBlock, 2) wave_trace_bvh(const Scene sc, const TaskQueue q, const uint32_t* __restrict__ n_ptr,
+__global__ void __launch_bounds__(kBlock, 3) wave_trace_bvh(const Scene sc, const TaskQueue q, const uint32_t* __restrict__ n_ptr,
                                                             uint32_t* __restrict__ fetch, float* __restrict__ res_t,
                                                             int32_t* __restrict__ res_id, const uint32_t leaf_max, Counters* ctr) {
     const uint32_t n = *n_ptr;
@@ -134,11 +136,9 @@ __global__ void __launch_bounds__(kBlock, 2) wave_trace_bvh(const Scene sc, cons
     const unsigned lane = threadIdx.x & 31u, tid = threadIdx.x;
     LocalCounters lc;
 
-    bool have = false, tdone = false;
-    uint32_t task = 0, path_bits = 0;
-    LaneRay k;
-    k.ox = k.oy = k.oz = k.ux = k.uy = k.uz = k.idx = k.idy = k.idz = k.onorm = 0.f;
-    float tcap = RT_MAX_FLOAT;
+    bool have = false, tdone = false, anyhit = false;
+    uint32_t task = 0;
+    float ox = 0.f, oy = 0.f, oz = 0.f, idx = 0.f, idy = 0.f, idz = 0.f, onorm = 0.f;
     Hit best;
     best.t = RT_MAX_FLOAT;
     best.id = -1;
@@ -147,121 +147,137 @@ __global__ void __launch_bounds__(kBlock, 2) wave_trace_bvh(const Scene sc, cons
     int sp = 0, npend = 0;
     int32_t stack[RT_BVH_STACK];
     bool exhausted = false;
-    const float4* lcull = reinterpret_cast<const float4*>(sc.leaf_cull);
-    const int must_level = kPendCap - (int)min(leaf_max, (uint32_t)kPendCap);
+    const int stall_level = kPendCap - 2 * (int)min(leaf_max, (uint32_t)(kPendCap / 2));
+    const float fglob = sc.root_f;
 
     for (;;) {
-        // A. idle lanes fetch the next rays of the queue
-        const unsigned idle = __ballot_sync(kFull, !have);
-        if (idle && !exhausted) {
-            uint32_t base = 0;
-            if (lane == 0) base = atomicAdd(fetch, (uint32_t)__popc(idle));
-            base = __shfl_sync(kFull, base, 0);
-            if (!have) {
-                const uint32_t i = base + (uint32_t)__popc(idle & lanemask_lt());
-                if (i < n) {
-                    task = i;
-                    const float4 s = q.s[i], d = q.d[i];
-                    path_bits = q.path[i];
-                    Ray r;
-                    r.s = s;
-                    r.d = d;
-                    const cv::RayK rk = cv::prepare(r);
-                    k.ox = rk.ox; k.oy = rk.oy; k.oz = rk.oz;
-                    k.ux = rk.ux; k.uy = rk.uy; k.uz = rk.uz;
-                    k.idx = rk.idx; k.idy = rk.idy; k.idz = rk.idz;
-                    k.onorm = rk.onorm;
-                    tcap = (path_bits & RT_TASK_ANYHIT) ? 1.f : RT_MAX_FLOAT;
-                    best.t = RT_MAX_FLOAT;
-                    best.id = -1;
-                    btype = 0;
-                    cur = sc.root;
-                    sp = 0;
-                    npend = 0;
-                    tdone = sc.n_objs == 0u;
-                    have = true;
-                }
-            }
-            if (base + (uint32_t)__popc(idle) >= n) exhausted = true;
-        }
-        if (!__any_sync(kFull, have)) break;
-
-        // B. inner nodes until this lane stands on a leaf (or runs out of nodes)
-        while (have && !tdone && cur >= 0) {
-            const float4* np = reinterpret_cast<const float4*>(sc.nodes + cur);
-            const float4 q0 = __ldg(np + 0), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
-            const float2 ff = __ldg(reinterpret_cast<const float2*>(sc.nodef + cur));
-            if (COUNT) lc.node_visits++;
-            const float tlimit = fminf(best.t, tcap);
-            float tn0, tn1;
-            const bool h0 = node_box(k, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, fmaf(ff.x, k.onorm, q3.z), tlimit, tn0);
-            const bool h1 = node_box(k, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, fmaf(ff.y, k.onorm, q3.w), tlimit, tn1);
-            const int32_t c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
-            if (h0 && h1) {
-                const bool first0 = tn0 <= tn1;
-                cur = first0 ? c0 : c1;
-                stack[sp++] = first0 ? c1 : c0;
-            } else if (h0) {
-                cur = c0;
-            } else if (h1) {
-                cur = c1;
-            } else if (sp > 0) {
-                cur = stack[--sp];
-            } else {
-                tdone = true;
-            }
-        }
-
-        // C. leaf: bounding-sphere filter, survivors are queued for the exact test
-        if (have && !tdone && cur < 0) {
-            const uint32_t code = (uint32_t)(~cur);
-            const uint32_t first = code >> 4, cnt = (code & 15u) + 1u;
-            for (uint32_t i = 0; i < cnt; ++i) {
-                const float4 a = __ldg(lcull + 2 * (size_t)(first + i));
-                const float h = __ldg(&sc.leaf_cull[first + i].h);
-                const float x = a.x - k.ox, y = a.y - k.oy, z = a.z - k.oz;
-                const float oc2 = fmaf(z, z, fmaf(y, y, x * x));
-                const float dt = fmaf(z, k.uz, fmaf(y, k.uy, x * k.ux));
-                if (!(fmaf(-dt, dt, oc2 * h) > a.w)) {
-                    if (npend == kPendCap) {  // overflow (only with leaves larger than the buffer): test in place
-                        Ray r;
-                        r.s = q.s[task];
-                        r.d = q.d[task];
-                        exact_pair(sc, r, __ldg(sc.leaf_obj + first + i), __ldg(&sc.leaf_cull[first + i].type), best, btype);
-                        if (COUNT) lc.exact_tests++;
-                    } else {
-                        pend[npend++][tid] = first + i;
+        // ---- refill
+        {
+            const unsigned idle = __ballot_sync(kFull, !have);
+            const unsigned trav = __ballot_sync(kFull, have && !tdone);
+            if (idle && !exhausted && (__popc(idle) >= 8 || trav == 0u)) {
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(fetch, (uint32_t)__popc(idle));
+                base = __shfl_sync(kFull, base, 0);
+                if (!have) {
+                    const uint32_t i = base + (uint32_t)__popc(idle & lanemask_lt());
+                    if (i < n) {
+                        task = i;
+                        const float4 s = q.s[i], d = q.d[i];
+                        anyhit = (q.path[i] & RT_TASK_ANYHIT) != 0u;
+                        ox = s.x; oy = s.y; oz = s.z;
+                        // conservative use only: approximate reciprocals are well inside the 1e-5 slack
+                        idx = fabsf(d.x) < 1e-30f ? copysignf(1e30f, d.x) : __fdividef(1.f, d.x);
+                        idy = fabsf(d.y) < 1e-30f ? copysignf(1e30f, d.y) : __fdividef(1.f, d.y);
+                        idz = fabsf(d.z) < 1e-30f ? copysignf(1e30f, d.z) : __fdividef(1.f, d.z);
+                        onorm = sqrtf(fmaf(oz, oz, fmaf(oy, oy, ox * ox))) * 1.000001f;
+                        best.t = RT_MAX_FLOAT;
+                        best.id = -1;
+                        btype = 0;
+                        cur = sc.root;
+                        sp = 0;
+                        npend = 0;
+                        tdone = false;
+                        have = true;
+                        if (cur < 0) {  // the whole scene is one leaf (tiny scenes): test its objects in place
+                            const uint32_t code = (uint32_t)(~cur);
+                            const uint32_t first = code >> 4, cnt = sc.n_objs ? (code & 15u) + 1u : 0u;
+                            for (uint32_t j = 0; j < cnt; ++j) {
+                                exact_pair_call(sc, s, d, __ldg(sc.leaf_obj + first + j), __ldg(&sc.leaf_cull[first + j].type), best, btype);
+                                if (COUNT) lc.exact_tests++;
+                            }
+                            tdone = true;
+                        }
                     }
                 }
+                if (base + (uint32_t)__popc(idle) >= n) exhausted = true;
             }
-            if (sp > 0)
-                cur = stack[--sp];
-            else
-                tdone = true;
+            if (!__any_sync(kFull, have)) break;
         }
 
-        // D. exact tests, run when enough lanes have one queued (or a lane cannot go on without)
+        // ---- node steps
+        for (;;) {
+            const bool go = have && !tdone && npend <= stall_level;
+            const unsigned T = __ballot_sync(kFull, go);
+            if (T == 0u) break;
+            if (__popc(T) < 20) {
+                const unsigned P = __ballot_sync(kFull, have && npend > 0);
+                if (__popc(P) >= 16) break;
+                if (__any_sync(kFull, have && !tdone && npend > stall_level)) break;
+                if (!exhausted && __popc(__ballot_sync(kFull, !have || (tdone && npend == 0))) >= 8) break;
+                if (__popc(__ballot_sync(kFull, have && tdone && npend > 0)) >= 12) break;
+            }
+            if (go) {
+                const float4* np = reinterpret_cast<const float4*>(sc.nodes + cur);
+                const float4 q0 = __ldg(np + 0), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
+                if (COUNT) lc.node_visits++;
+                const float tlimit = anyhit ? fminf(best.t, 1.f) : best.t;
+                const float infl0 = fmaf(fglob, onorm, q3.z), infl1 = fmaf(fglob, onorm, q3.w);
+                const float aix = fabsf(idx), aiy = fabsf(idy), aiz = fabsf(idz);
+                // child 0: lo (q0.x q0.y q0.z) hi (q0.w q1.x q1.y); child 1: lo (q1.z q1.w q2.x) hi (q2.y q2.z q2.w)
+                float ax = (q0.x - ox) * idx, bx = (q0.w - ox) * idx;
+                float ay = (q0.y - oy) * idy, by = (q1.x - oy) * idy;
+                float az = (q0.z - oz) * idz, bz = (q1.y - oz) * idz;
+                float tn0 = fmaxf(fmaxf(fmaf(-infl0, aix, fminf(ax, bx)), fmaf(-infl0, aiy, fminf(ay, by))), fmaf(-infl0, aiz, fminf(az, bz)));
+                float tf0 = fminf(fminf(fmaf(infl0, aix, fmaxf(ax, bx)), fmaf(infl0, aiy, fmaxf(ay, by))), fmaf(infl0, aiz, fmaxf(az, bz)));
+                ax = (q1.z - ox) * idx; bx = (q2.y - ox) * idx;
+                ay = (q1.w - oy) * idy; by = (q2.z - oy) * idy;
+                az = (q2.x - oz) * idz; bz = (q2.w - oz) * idz;
+                float tn1 = fmaxf(fmaxf(fmaf(-infl1, aix, fminf(ax, bx)), fmaf(-infl1, aiy, fminf(ay, by))), fmaf(-infl1, aiz, fminf(az, bz)));
+                float tf1 = fminf(fminf(fmaf(infl1, aix, fmaxf(ax, bx)), fmaf(infl1, aiy, fmaxf(ay, by))), fmaf(infl1, aiz, fmaxf(az, bz)));
+                const float s0 = 1e-5f * fmaxf(fabsf(tn0), fabsf(tf0)), s1 = 1e-5f * fmaxf(fabsf(tn1), fabsf(tf1));
+                bool h0 = !(tn0 - s0 > fminf(tf0, tlimit)) && !(tf0 + s0 < 0.f);
+                bool h1 = !(tn1 - s1 > fminf(tf1, tlimit)) && !(tf1 + s1 < 0.f);
+                const int32_t c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
+                if (h0 && c0 < 0) {  // leaf child: its objects become candidates
+                    const uint32_t code = (uint32_t)(~c0);
+                    const uint32_t first = code >> 4, cnt = (code & 15u) + 1u;
+                    for (uint32_t j = 0; j < cnt; ++j) pend[npend++][tid] = first + j;
+                    h0 = false;
+                }
+                if (h1 && c1 < 0) {
+                    const uint32_t code = (uint32_t)(~c1);
+                    const uint32_t first = code >> 4, cnt = (code & 15u) + 1u;
+                    for (uint32_t j = 0; j < cnt; ++j) pend[npend++][tid] = first + j;
+                    h1 = false;
+                }
+                if (h0 && h1) {
+                    const bool first0 = tn0 <= tn1;
+                    cur = first0 ? c0 : c1;
+                    stack[sp++] = first0 ? c1 : c0;
+                } else if (h0) {
+                    cur = c0;
+                } else if (h1) {
+                    cur = c1;
+                } else if (sp > 0) {
+                    cur = stack[--sp];
+                } else {
+                    tdone = true;
+                }
+            }
+        }
+
+        // ---- exact tests
         for (;;) {
             const bool has = have && npend > 0;
-            const unsigned hasp = __ballot_sync(kFull, has);
-            if (hasp == 0u) break;
-            const unsigned must = __ballot_sync(kFull, has && (tdone || npend > must_level));
-            if (must == 0u && __popc(hasp) < 16) break;
+            const unsigned P = __ballot_sync(kFull, has);
+            if (P == 0u) break;
+            const unsigned T = __ballot_sync(kFull, have && !tdone && npend <= stall_level);
+            const bool stalled = __any_sync(kFull, have && !tdone && npend > stall_level);
+            const int nF = __popc(__ballot_sync(kFull, has && tdone));
+            if (!(__popc(P) >= 16 || stalled || T == 0u || nF >= 12)) break;
             if (has) {
                 const uint32_t slot = pend[--npend][tid];
-                Ray r;
-                r.s = q.s[task];
-                r.d = q.d[task];
-                exact_pair(sc, r, __ldg(sc.leaf_obj + slot), __ldg(&sc.leaf_cull[slot].type), best, btype);
+                exact_pair_call(sc, q.s[task], q.d[task], __ldg(sc.leaf_obj + slot), __ldg(&sc.leaf_cull[slot].type), best, btype);
                 if (COUNT) lc.exact_tests++;
-                if ((path_bits & RT_TASK_ANYHIT) && best.t < tcap) {  // shadow ray decided (SAR:229)
+                if (anyhit && best.t < 1.f) {  // the shadow ray is decided (SAR:229)
                     tdone = true;
                     npend = 0;
                 }
             }
         }
 
-        // E. retire finished rays
+        // ---- retire
         if (have && tdone && npend == 0) {
             res_t[task] = best.id >= 0 ? best.t : RT_MAX_FLOAT;
             res_id[task] = best.id;
@@ -295,81 +311,117 @@ __global__ void __launch_bounds__(kBlock) wave_trace_brute(const Scene sc, const
 
 // N-body layout: RPT rays per thread in registers, the filter records of a tile of objects in shared memory
 // (every lane of a warp reads the same record: one broadcast wavefront per load), survivors run the exact test.
-constexpr int kFilterTile = 1024;  // objects per tile: 1024 x 32 B = 32 KB
+//
+// Per pair the filter evaluates  h*|c-o|^2 - ((c-o).u)^2 > r2  in expanded form, 1 FADD + 1 FMUL + 7 FFMA:
+//     dt  = c.u - o.u                 3 FFMA   (o.u per ray)
+//     oc2 = |c|^2 + |o|^2 - 2 c.o     1 FADD + 3 FFMA   (|c|^2 per object, |o|^2 and -2o per ray)
+//     lhs = h*oc2 - dt*dt             1 FMUL + 1 FFMA
+// The expanded form cancels when |c|, |o| >> |c-o|; its rounding error is below 42 u (|c|^2 + |o|^2), which is
+// added to the accept side (kExpandPad on r2 per object and on |o|^2 per ray) so the filter stays conservative.
+constexpr int kFilterTile = 1024;          // objects per tile
+constexpr float kExpandPad = 3.8147e-06f;  // 64 u
+
+struct FilterRec {  // 24 B per object in shared memory: one LDS.128 + one LDS.64, both warp-broadcast
+    float4 a;       // cx, cy, cz, |c|^2
+    float2 b;       // r2 + pad, h
+};
+
+__device__ __noinline__ void filter_exact(const Scene& sc, const TaskQueue& q, uint32_t ray_idx, uint32_t obj, float* bt, int32_t* bi) {
+    Hit best;
+    best.t = *bt;
+    best.id = *bi;
+    const uint32_t btype0 = best.id >= 0 ? __ldg(&sc.cull[best.id].type) : 0u;
+    uint32_t btype = btype0;
+    Ray r;
+    r.s = q.s[ray_idx];
+    r.d = q.d[ray_idx];
+    exact_pair(sc, r, obj, __ldg(&sc.cull[obj].type), best, btype);
+    *bt = best.t;
+    *bi = best.id;
+}
 
 template <int RPT, bool COUNT>
-__global__ void __launch_bounds__(kBlock) wave_trace_filter(const Scene sc, const TaskQueue q, const uint32_t* __restrict__ n_ptr,
-                                                            float* __restrict__ res_t, int32_t* __restrict__ res_id, Counters* ctr) {
+__global__ void __launch_bounds__(kBlock, 2) wave_trace_filter(const Scene sc, const TaskQueue q, const uint32_t* __restrict__ n_ptr,
+                                                               const uint32_t n_min, const uint32_t n_max, float* __restrict__ res_t,
+                                                               int32_t* __restrict__ res_id, Counters* ctr) {
     const uint32_t n = *n_ptr;
-    if (n == 0u) return;
-    __shared__ float4 tileA[kFilterTile];  // cx, cy, cz, r2
-    __shared__ float tileH[kFilterTile];   // h
+    if (n == 0u || n < n_min || n >= n_max) return;  // the other instantiation handles this queue size
+    __shared__ float4 tA[kFilterTile];
+    __shared__ float2 tB[kFilterTile];
+    __shared__ float best_t[RPT][kBlock];
+    __shared__ int32_t best_i[RPT][kBlock];
     LocalCounters lc;
     const uint32_t M = sc.n_objs;
     const float4* cull4 = reinterpret_cast<const float4*>(sc.cull);
     const uint32_t per_block = kBlock * RPT;
     const uint32_t n_groups = (n + per_block - 1) / per_block;
+    const uint32_t tid = threadIdx.x;
 
     for (uint32_t g = blockIdx.x; g < n_groups; g += gridDim.x) {
-        float ox[RPT], oy[RPT], oz[RPT], ux[RPT], uy[RPT], uz[RPT];
-        Hit best[RPT];
-        uint32_t btype[RPT];
-        uint32_t idx[RPT];
+        float ux[RPT], uy[RPT], uz[RPT], px[RPT], py[RPT], pz[RPT], nq[RPT], oo[RPT];
+        const uint32_t base = g * per_block + tid;  // ray r of this thread: base + r * kBlock (coalesced loads)
 #pragma unroll
         for (int r = 0; r < RPT; ++r) {
-            // consecutive lanes take consecutive rays: coalesced loads, and neighbours stay neighbours
-            idx[r] = g * per_block + r * kBlock + threadIdx.x;
-            best[r].t = RT_MAX_FLOAT;
-            best[r].id = -1;
-            btype[r] = 0;
-            if (idx[r] < n) {
+            const uint32_t i = base + r * kBlock;
+            best_t[r][tid] = RT_MAX_FLOAT;
+            best_i[r][tid] = -1;
+            if (i < n) {
                 Ray ry;
-                ry.s = q.s[idx[r]];
-                ry.d = q.d[idx[r]];
+                ry.s = q.s[i];
+                ry.d = q.d[i];
                 const cv::RayK rk = cv::prepare(ry);
-                ox[r] = rk.ox; oy[r] = rk.oy; oz[r] = rk.oz;
                 ux[r] = rk.ux; uy[r] = rk.uy; uz[r] = rk.uz;
-            } else {  // padding lane: a ray that passes every filter test as "miss" cheaply
-                ox[r] = oy[r] = oz[r] = 0.f;
-                ux[r] = uy[r] = uz[r] = 0.f;
+                px[r] = -2.f * rk.ox; py[r] = -2.f * rk.oy; pz[r] = -2.f * rk.oz;
+                nq[r] = -(rk.ox * rk.ux + rk.oy * rk.uy + rk.oz * rk.uz);
+                const float o2 = rk.ox * rk.ox + rk.oy * rk.oy + rk.oz * rk.oz;
+                oo[r] = o2 - 2.f * kExpandPad * o2;
+            } else {  // padding: u = 0, o = 0 -> lhs = h*|c|^2, rejected unless the object sits on the origin
+                ux[r] = uy[r] = uz[r] = px[r] = py[r] = pz[r] = nq[r] = oo[r] = 0.f;
             }
         }
         for (uint32_t t0 = 0; t0 < M; t0 += kFilterTile) {
             const uint32_t cnt = min((uint32_t)kFilterTile, M - t0);
             __syncthreads();
-            for (uint32_t j = threadIdx.x; j < cnt; j += kBlock) {
-                tileA[j] = __ldg(cull4 + 2 * (size_t)(t0 + j));
-                tileH[j] = __ldg(&sc.cull[t0 + j].h);
+            for (uint32_t j = tid; j < cnt; j += kBlock) {
+                const float4 a = __ldg(cull4 + 2 * (size_t)(t0 + j));       // cx cy cz r2
+                const float4 b = __ldg(cull4 + 2 * (size_t)(t0 + j) + 1);   // h cc e0 type
+                tA[j] = make_float4(a.x, a.y, a.z, b.y);
+                tB[j] = make_float2(a.w < 0.f ? a.w : fmaf(kExpandPad, b.y, a.w), b.x);  // r2 < 0 marks "never hit"
             }
             __syncthreads();
-#pragma unroll 4
+#pragma unroll 2
             for (uint32_t j = 0; j < cnt; ++j) {
-                const float4 a = tileA[j];
-                const float h = tileH[j];
+                const float4 a = tA[j];
+                const float2 b = tB[j];
+                bool pass[RPT];
+                bool any = false;
 #pragma unroll
                 for (int r = 0; r < RPT; ++r) {
-                    const float x = a.x - ox[r], y = a.y - oy[r], z = a.z - oz[r];
-                    const float oc2 = fmaf(z, z, fmaf(y, y, x * x));
-                    const float dt = fmaf(z, uz[r], fmaf(y, uy[r], x * ux[r]));
-                    if (!(fmaf(-dt, dt, oc2 * h) > a.w)) {
-                        if (idx[r] < n) {
-                            Ray ry;
-                            ry.s = q.s[idx[r]];
-                            ry.d = q.d[idx[r]];
-                            exact_pair(sc, ry, t0 + j, __ldg(&sc.cull[t0 + j].type), best[r], btype[r]);
+                    const float dt = fmaf(a.x, ux[r], fmaf(a.y, uy[r], fmaf(a.z, uz[r], nq[r])));
+                    const float oc2 = fmaf(a.x, px[r], fmaf(a.y, py[r], fmaf(a.z, pz[r], a.w + oo[r])));
+                    pass[r] = !(fmaf(-dt, dt, oc2 * b.y) > b.x);
+                    any |= pass[r];
+                }
+                if (any) {
+#pragma unroll
+                    for (int r = 0; r < RPT; ++r)
+                        if (pass[r] && base + r * kBlock < n) {
+                            filter_exact(sc, q, base + r * kBlock, t0 + j, &best_t[r][tid], &best_i[r][tid]);
                             if (COUNT) lc.exact_tests++;
                         }
-                    }
                 }
             }
         }
 #pragma unroll
-        for (int r = 0; r < RPT; ++r)
-            if (idx[r] < n) {
+        for (int r = 0; r < RPT; ++r) {
+            const uint32_t i = base + r * kBlock;
+            if (i < n) {
                 if (COUNT) lc.pair_tests += M;
-                res_t[idx[r]] = best[r].id >= 0 ? best[r].t : RT_MAX_FLOAT;
-                res_id[idx[r]] = best[r].id;
+                const int32_t id = best_i[r][tid];
+                res_t[i] = id >= 0 ? best_t[r][tid] : RT_MAX_FLOAT;
+                res_id[i] = id;
             }
+        }
     }
     if (COUNT) flush_local(lc, ctr);
 }
@@ -450,7 +502,7 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
     WaveParams wp;
     wp.max_bounces = fr.max_bounces;
     wp.mode = fr.mode;
-    const unsigned pgrid = (unsigned)sm_count * 2u;    // persistent trace: 2 CTAs of 8 warps per SM
+    const unsigned pgrid = (unsigned)sm_count * 3u;    // persistent trace: 3 CTAs of 8 warps per SM
     const unsigned sgrid = (unsigned)sm_count * 8u;    // grid-stride kernels
     const bool count = fr.counters != nullptr;
     for (uint32_t g = 0; g < gens; ++g) {
@@ -462,10 +514,17 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
             else
                 wave_trace_bvh<false><<<pgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, fetch + g, wb.res_t, wb.res_id, leaf_max, fr.counters);
         } else if (accel == 1) {
-            if (count)
-                wave_trace_filter<4, true><<<sgrid / 4, kBlock, 0, stream>>>(sc, qin, qcount + g, wb.res_t, wb.res_id, fr.counters);
-            else
-                wave_trace_filter<4, false><<<sgrid / 4, kBlock, 0, stream>>>(sc, qin, qcount + g, wb.res_t, wb.res_id, fr.counters);
+            // two instantiations, each takes the queue sizes it is efficient for (the size lives on the device)
+            const unsigned fgrid = (unsigned)sm_count * 2u;
+            const uint32_t split = fgrid * kBlock * 8u;
+            if (count) {
+                wave_trace_filter<8, true><<<fgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, split, 0xffffffffu, wb.res_t, wb.res_id, fr.counters);
+                wave_trace_filter<2, true><<<fgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, 0u, split, wb.res_t, wb.res_id, fr.counters);
+            } else {
+                wave_trace_filter<8, false><<<fgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, split, 0xffffffffu, wb.res_t, wb.res_id, fr.counters);
+                wave_trace_filter<2, false><<<fgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, 0u, split, wb.res_t, wb.res_id, fr.counters);
+            }
+            ++nl;
         } else {
             if (count)
                 wave_trace_brute<true><<<sgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, wb.res_t, wb.res_id, fr.counters);
