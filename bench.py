@@ -38,7 +38,7 @@ from pyrt import scenes, types  # noqa: E402
 METRIC = "Mrays/s (primary+shadow+reflect)"
 
 # flops of the arithmetic each counted unit executes (DESIGN.md "Work per unit")
-FLOPS_FILTER = 17.0   # bounding-sphere filter: 3 sub + 3 (mul,fma,fma) x2 + mul + fma ...
+FLOPS_FILTER = 16.0   # bounding-sphere filter, expanded form: 1 add + 1 mul + 7 fma (rt_wavefront.cu)
 FLOPS_EXACT = 78.0    # reference arithmetic of one ray x object test as written
 FLOPS_NODE = 62.0     # two inflated slab tests of one BVH node
 FLOPS_SHADE = 100.0   # Phong terms per (hit, light)
@@ -166,6 +166,8 @@ def main():
     ap.add_argument("--accel", type=int, default=-1, help="-1 auto, 0 brute (exact on every pair), 1 filter, 2 bvh")
     ap.add_argument("--block-rows", type=int, default=16)
     ap.add_argument("--cpu-sample", type=int, default=0, help="side of the pixel lattice of the CPU sample (0 = auto)")
+    ap.add_argument("--leaf", type=int, default=0, help="BVH leaf size (0 = library default)")
+    ap.add_argument("--pipeline", type=int, default=-1, help="-1 auto, 0 megakernel, 1 wavefront")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-brute-leg", action="store_true")
     args = ap.parse_args()
@@ -215,6 +217,10 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    if args.leaf:
+        ctx.set_option(lib.OPT_BVH_LEAF, args.leaf)
+    if args.pipeline >= 0:
+        ctx.set_option(lib.OPT_PIPELINE, args.pipeline)
     t_up0 = time.perf_counter()
     ctx.upload_scene(objs, lights)
     ctx.set_camera(W, H, zdir)
@@ -377,6 +383,7 @@ def main():
                            scene_upload_ms=upload_ms),
             "rays": {"traced": rays_traced, "reference": rays_reference, "primary": r_prim, "shadow_traced": t_shadow,
                      "shadow_reference": r_shadow, "reflect_traced": t_refl, "reflect_reference": r_refl, "hit_pixels": hit_pixels,
+                     "pair_tests": pair_tests, "exact_tests": exact_tests, "node_visits": node_visits,
                      "mrays_reference_equivalent": rays_reference / (ms_dev * 1e-3) / 1e6},
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": 0,
                     "d2h_bytes_per_step": W * H * 16,

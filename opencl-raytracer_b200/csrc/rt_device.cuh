@@ -263,13 +263,21 @@ __device__ __forceinline__ bool sphere_may_hit(const RayK& k, float cx, float cy
     return !(lhs > r2);
 }
 
-// Inflated slab test of one child box against [0, tlimit].  Returns the (conservative)
-// entry parameter through tnear.
+// Slab test of one child box against [0, tlimit], the box inflated by  pad + f * d_far  where d_far is the
+// distance from the ray origin to the farthest point of the box: every object centre c of the subtree lies in
+// the box, so |oc| <= d_far and f * d_far bounds the cone term of each object (rt_scene.cpp).  Returns the
+// (conservative) entry parameter through tnear.
 __device__ __forceinline__ bool box_may_hit(const RayK& k, const float* __restrict__ lo, const float* __restrict__ hi,
-                                            float infl, float tlimit, float& tnear) {
-    const float ax = (lo[0] - k.ox) * k.idx, bx = (hi[0] - k.ox) * k.idx;
-    const float ay = (lo[1] - k.oy) * k.idy, by = (hi[1] - k.oy) * k.idy;
-    const float az = (lo[2] - k.oz) * k.idz, bz = (hi[2] - k.oz) * k.idz;
+                                            float pad, float f, float tlimit, float& tnear) {
+    const float lx = lo[0] - k.ox, hx = hi[0] - k.ox;
+    const float ly = lo[1] - k.oy, hy = hi[1] - k.oy;
+    const float lz = lo[2] - k.oz, hz = hi[2] - k.oz;
+    const float mx = fmaxf(fabsf(lx), fabsf(hx)), my = fmaxf(fabsf(ly), fabsf(hy)), mz = fmaxf(fabsf(lz), fabsf(hz));
+    const float dfar = sqrtf(fmaf(mz, mz, fmaf(my, my, mx * mx))) * 1.000001f;
+    const float infl = fmaf(f, dfar, pad);
+    const float ax = lx * k.idx, bx = hx * k.idx;
+    const float ay = ly * k.idy, by = hy * k.idy;
+    const float az = lz * k.idz, bz = hz * k.idz;
     const float nx = fmaf(-infl, k.aix, fminf(ax, bx)), fx = fmaf(infl, k.aix, fmaxf(ax, bx));
     const float ny = fmaf(-infl, k.aiy, fminf(ay, by)), fy = fmaf(infl, k.aiy, fmaxf(ay, by));
     const float nz = fmaf(-infl, k.aiz, fminf(az, bz)), fz = fmaf(infl, k.aiz, fmaxf(az, bz));
@@ -371,11 +379,10 @@ __device__ __forceinline__ Hit trace_bvh(const Scene& sc, const Ray& ray, float 
             const float lo0[3] = {q0.x, q0.y, q0.z}, hi0[3] = {q0.w, q1.x, q1.y};
             const float lo1[3] = {q1.z, q1.w, q2.x}, hi1[3] = {q2.y, q2.z, q2.w};
             const int32_t c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
-            const float infl0 = fmaf(ff.x, rk.onorm, q3.z), infl1 = fmaf(ff.y, rk.onorm, q3.w);
             const float tlimit = ANYHIT ? fminf(h.t, tcap) : h.t;
             float tn0, tn1;
-            const bool h0 = cv::box_may_hit(rk, lo0, hi0, infl0, tlimit, tn0);
-            const bool h1 = cv::box_may_hit(rk, lo1, hi1, infl1, tlimit, tn1);
+            const bool h0 = cv::box_may_hit(rk, lo0, hi0, q3.z, ff.x, tlimit, tn0);
+            const bool h1 = cv::box_may_hit(rk, lo1, hi1, q3.w, ff.y, tlimit, tn1);
             if (h0 && h1) {
                 const bool first0 = tn0 <= tn1;
                 cur = first0 ? c0 : c1;

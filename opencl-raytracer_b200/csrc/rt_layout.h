@@ -18,9 +18,9 @@ struct BvhNode {  // 64 B: both children's boxes
     float lo0[3], hi0[3];
     float lo1[3], hi1[3];
     int32_t c0, c1;  // >= 0: inner node index; < 0: leaf, ~c = (first << 4) | (count - 1)
-    float a0, a1;    // static inflation of each child box: pad + f * r_far
+    float a0, a1;    // static pad of each child box (rounding of the slab arithmetic)
 };
-struct BvhNodeF {  // cone coefficient per child; inflation = a + f * |ray origin|
+struct BvhNodeF {  // cone coefficient per child; inflation = a + f * (distance origin -> farthest box point)
     float f0, f1;
 };
 

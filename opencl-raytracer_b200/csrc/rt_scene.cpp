@@ -13,7 +13,7 @@
 //      fuzzy squared radius (object space)   rho^2 <= 1 + K u |s|^2,          |s| <= |oc| / sigma_min
 //      => view space, any direction          extent <= sigma_max * rho
 //      => bounding sphere test               p^2 <= R^2 + g |oc|^2,           g = K u (sigma_max/sigma_min)^2
-//      => box inflation                      + sqrt(g) * |oc|,                |oc| <= |o| + r_far
+//      => box inflation                      + sqrt(g) * |oc|,                |oc| <= distance origin -> farthest box point
 //
 // plus static pads for the rounding of the transform itself.  K = 32 is twice the first-order worst case.
 // tests/test_bounds.py checks on adversarial scenes that no exact hit is ever filtered.
@@ -463,7 +463,7 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
         const double rfar = sqrt(rf2);
         f = up(n.f);
         // slab arithmetic of cv::box_may_hit: (lo - o) rounds with error <= u * max(|lo|, |o|)
-        a = up(8.0 * U * (omax + rfar) + (double)f * rfar * (1.0 + 1e-6));
+        a = up(8.0 * U * (omax + rfar));
     };
     for (size_t i = 0; i < bld.bn.size(); ++i) {
         const BuildNode& n = bld.bn[i];

@@ -115,6 +115,16 @@ __device__ __noinline__ void exact_pair_call(const Scene& sc, const float4 s, co
     exact_pair(sc, r, obj, type, best, btype);
 }
 
+// Bounding-sphere filter of one leaf object (the direct form of cv::sphere_may_hit).
+__device__ __forceinline__ bool leaf_filter(const Scene& sc, uint32_t slot, float ox, float oy, float oz, float ux, float uy, float uz) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(sc.leaf_cull) + 2 * (size_t)slot);
+    const float h = __ldg(&sc.leaf_cull[slot].h);
+    const float x = a.x - ox, y = a.y - oy, z = a.z - oz;
+    const float oc2 = fmaf(z, z, fmaf(y, y, x * x));
+    const float dt = fmaf(z, uz, fmaf(y, uy, x * ux));
+    return !(fmaf(-dt, dt, oc2 * h) > a.w);
+}
+
 // Persistent warps.  Every lane owns one ray of the queue and is in one of four states:
 //   T  traversing (stands on an inner node)           S  traversing, but its candidate buffer is nearly full
 //   F  traversal finished, candidates still queued    I  idle (no ray)
@@ -138,7 +148,7 @@ __global__ void __launch_bounds__(kBlock, 3) wave_trace_bvh(const Scene sc, cons
 
     bool have = false, tdone = false, anyhit = false;
     uint32_t task = 0;
-    float ox = 0.f, oy = 0.f, oz = 0.f, idx = 0.f, idy = 0.f, idz = 0.f, onorm = 0.f;
+    float ox = 0.f, oy = 0.f, oz = 0.f, idx = 0.f, idy = 0.f, idz = 0.f, ux = 0.f, uy = 0.f, uz = 0.f;
     Hit best;
     best.t = RT_MAX_FLOAT;
     best.id = -1;
@@ -148,7 +158,7 @@ __global__ void __launch_bounds__(kBlock, 3) wave_trace_bvh(const Scene sc, cons
     int32_t stack[RT_BVH_STACK];
     bool exhausted = false;
     const int stall_level = kPendCap - 2 * (int)min(leaf_max, (uint32_t)(kPendCap / 2));
-    const float fglob = sc.root_f;
+    const float fglob = sc.root_f * 1.00001f;  // covers the approximate square root of d_far
 
     for (;;) {
         // ---- refill
@@ -170,7 +180,10 @@ __global__ void __launch_bounds__(kBlock, 3) wave_trace_bvh(const Scene sc, cons
                         idx = fabsf(d.x) < 1e-30f ? copysignf(1e30f, d.x) : __fdividef(1.f, d.x);
                         idy = fabsf(d.y) < 1e-30f ? copysignf(1e30f, d.y) : __fdividef(1.f, d.y);
                         idz = fabsf(d.z) < 1e-30f ? copysignf(1e30f, d.z) : __fdividef(1.f, d.z);
-                        onorm = sqrtf(fmaf(oz, oz, fmaf(oy, oy, ox * ox))) * 1.000001f;
+                        {  // unit direction for the bounding-sphere filter (correctly rounded: its error is in g)
+                            const float len = __fsqrt_rn(d.x * d.x + d.y * d.y + d.z * d.z);
+                            ux = __fdiv_rn(d.x, len); uy = __fdiv_rn(d.y, len); uz = __fdiv_rn(d.z, len);
+                        }
                         best.t = RT_MAX_FLOAT;
                         best.id = -1;
                         btype = 0;
@@ -212,17 +225,18 @@ __global__ void __launch_bounds__(kBlock, 3) wave_trace_bvh(const Scene sc, cons
                 const float4 q0 = __ldg(np + 0), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
                 if (COUNT) lc.node_visits++;
                 const float tlimit = anyhit ? fminf(best.t, 1.f) : best.t;
-                const float infl0 = fmaf(fglob, onorm, q3.z), infl1 = fmaf(fglob, onorm, q3.w);
                 const float aix = fabsf(idx), aiy = fabsf(idy), aiz = fabsf(idz);
                 // child 0: lo (q0.x q0.y q0.z) hi (q0.w q1.x q1.y); child 1: lo (q1.z q1.w q2.x) hi (q2.y q2.z q2.w)
-                float ax = (q0.x - ox) * idx, bx = (q0.w - ox) * idx;
-                float ay = (q0.y - oy) * idy, by = (q1.x - oy) * idy;
-                float az = (q0.z - oz) * idz, bz = (q1.y - oz) * idz;
+                float lx = q0.x - ox, hx = q0.w - ox, ly = q0.y - oy, hy = q1.x - oy, lz = q0.z - oz, hz = q1.y - oz;
+                float mx = fmaxf(fabsf(lx), fabsf(hx)), my = fmaxf(fabsf(ly), fabsf(hy)), mz = fmaxf(fabsf(lz), fabsf(hz));
+                const float infl0 = fmaf(fglob, sqrtf(fmaf(mz, mz, fmaf(my, my, mx * mx))), q3.z);
+                float ax = lx * idx, bx = hx * idx, ay = ly * idy, by = hy * idy, az = lz * idz, bz = hz * idz;
                 float tn0 = fmaxf(fmaxf(fmaf(-infl0, aix, fminf(ax, bx)), fmaf(-infl0, aiy, fminf(ay, by))), fmaf(-infl0, aiz, fminf(az, bz)));
                 float tf0 = fminf(fminf(fmaf(infl0, aix, fmaxf(ax, bx)), fmaf(infl0, aiy, fmaxf(ay, by))), fmaf(infl0, aiz, fmaxf(az, bz)));
-                ax = (q1.z - ox) * idx; bx = (q2.y - ox) * idx;
-                ay = (q1.w - oy) * idy; by = (q2.z - oy) * idy;
-                az = (q2.x - oz) * idz; bz = (q2.w - oz) * idz;
+                lx = q1.z - ox; hx = q2.y - ox; ly = q1.w - oy; hy = q2.z - oy; lz = q2.x - oz; hz = q2.w - oz;
+                mx = fmaxf(fabsf(lx), fabsf(hx)); my = fmaxf(fabsf(ly), fabsf(hy)); mz = fmaxf(fabsf(lz), fabsf(hz));
+                const float infl1 = fmaf(fglob, sqrtf(fmaf(mz, mz, fmaf(my, my, mx * mx))), q3.w);
+                ax = lx * idx; bx = hx * idx; ay = ly * idy; by = hy * idy; az = lz * idz; bz = hz * idz;
                 float tn1 = fmaxf(fmaxf(fmaf(-infl1, aix, fminf(ax, bx)), fmaf(-infl1, aiy, fminf(ay, by))), fmaf(-infl1, aiz, fminf(az, bz)));
                 float tf1 = fminf(fminf(fmaf(infl1, aix, fmaxf(ax, bx)), fmaf(infl1, aiy, fmaxf(ay, by))), fmaf(infl1, aiz, fmaxf(az, bz)));
                 const float s0 = 1e-5f * fmaxf(fabsf(tn0), fabsf(tf0)), s1 = 1e-5f * fmaxf(fabsf(tn1), fabsf(tf1));
@@ -232,13 +246,15 @@ __global__ void __launch_bounds__(kBlock, 3) wave_trace_bvh(const Scene sc, cons
                 if (h0 && c0 < 0) {  // leaf child: its objects become candidates
                     const uint32_t code = (uint32_t)(~c0);
                     const uint32_t first = code >> 4, cnt = (code & 15u) + 1u;
-                    for (uint32_t j = 0; j < cnt; ++j) pend[npend++][tid] = first + j;
+                    for (uint32_t j = 0; j < cnt; ++j)
+                        if (leaf_filter(sc, first + j, ox, oy, oz, ux, uy, uz)) pend[npend++][tid] = first + j;
                     h0 = false;
                 }
                 if (h1 && c1 < 0) {
                     const uint32_t code = (uint32_t)(~c1);
                     const uint32_t first = code >> 4, cnt = (code & 15u) + 1u;
-                    for (uint32_t j = 0; j < cnt; ++j) pend[npend++][tid] = first + j;
+                    for (uint32_t j = 0; j < cnt; ++j)
+                        if (leaf_filter(sc, first + j, ox, oy, oz, ux, uy, uz)) pend[npend++][tid] = first + j;
                     h1 = false;
                 }
                 if (h0 && h1) {
