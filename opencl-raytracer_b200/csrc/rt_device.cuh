@@ -263,30 +263,25 @@ __device__ __forceinline__ bool sphere_may_hit(const RayK& k, float cx, float cy
     return !(lhs > r2);
 }
 
-// Slab test of one child box against [0, tlimit], the box inflated by  pad + f * d_far  where d_far is the
-// distance from the ray origin to the farthest point of the box: every object centre c of the subtree lies in
-// the box, so |oc| <= d_far and f * d_far bounds the cone term of each object (rt_scene.cpp).  Returns the
-// (conservative) entry parameter through tnear.
-__device__ __forceinline__ bool box_may_hit(const RayK& k, const float* __restrict__ lo, const float* __restrict__ hi,
-                                            float pad, float f, float tlimit, float& tnear) {
-    const float lx = lo[0] - k.ox, hx = hi[0] - k.ox;
-    const float ly = lo[1] - k.oy, hy = hi[1] - k.oy;
-    const float lz = lo[2] - k.oz, hz = hi[2] - k.oz;
-    const float mx = fmaxf(fabsf(lx), fabsf(hx)), my = fmaxf(fabsf(ly), fabsf(hy)), mz = fmaxf(fabsf(lz), fabsf(hz));
-    const float dfar = sqrtf(fmaf(mz, mz, fmaf(my, my, mx * mx))) * 1.000001f;
+// Slab test of one child box (centre c, half extent e) against [0, tlimit], the box inflated by
+// pad + f * d_far  where d_far is the distance from the ray origin to the farthest point of the box: every
+// object centre of the subtree lies in the box, so |oc| <= d_far and f * d_far bounds the cone term of each
+// object (rt_scene.cpp).  The rounding of the slab arithmetic itself (relative, <= 4e-7 of d_far in space units)
+// is covered by kSlabRel added to f.  Returns the conservative entry parameter through tnear.
+#define RT_SLAB_REL 2e-6f
+__device__ __forceinline__ bool box_may_hit(float ox, float oy, float oz, float idx, float idy, float idz, float cx, float cy,
+                                            float cz, float ex, float ey, float ez, float pad, float f, float tlimit,
+                                            float& tnear) {
+    const float x = cx - ox, y = cy - oy, z = cz - oz;
+    const float mx = fabsf(x) + ex, my = fabsf(y) + ey, mz = fabsf(z) + ez;
+    const float dfar = sqrtf(fmaf(mz, mz, fmaf(my, my, mx * mx)));
     const float infl = fmaf(f, dfar, pad);
-    const float ax = lx * k.idx, bx = hx * k.idx;
-    const float ay = ly * k.idy, by = hy * k.idy;
-    const float az = lz * k.idz, bz = hz * k.idz;
-    const float nx = fmaf(-infl, k.aix, fminf(ax, bx)), fx = fmaf(infl, k.aix, fmaxf(ax, bx));
-    const float ny = fmaf(-infl, k.aiy, fminf(ay, by)), fy = fmaf(infl, k.aiy, fmaxf(ay, by));
-    const float nz = fmaf(-infl, k.aiz, fminf(az, bz)), fz = fmaf(infl, k.aiz, fmaxf(az, bz));
-    const float tn = fmaxf(fmaxf(nx, ny), nz);
-    const float tf = fminf(fminf(fx, fy), fz);
+    const float tx = x * idx, ty = y * idy, tz = z * idz;
+    const float rx = (ex + infl) * fabsf(idx), ry = (ey + infl) * fabsf(idy), rz = (ez + infl) * fabsf(idz);
+    const float tn = fmaxf(fmaxf(tx - rx, ty - ry), tz - rz);
+    const float tf = fminf(fminf(tx + rx, ty + ry), tz + rz);
     tnear = tn;
-    // relative slack on the parameters themselves (rounding of the six products)
-    const float slack = 1e-5f * fmaxf(fabsf(tn), fabsf(tf));
-    return !(tn - slack > fminf(tf, tlimit)) && !(tf + slack < 0.f);
+    return !(tn > fminf(tf, tlimit)) && !(tf < 0.f);
 }
 
 }  // namespace cv
@@ -376,13 +371,14 @@ __device__ __forceinline__ Hit trace_bvh(const Scene& sc, const Ray& ray, float 
             const float4 q0 = __ldg(np + 0), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
             const float2 ff = __ldg(reinterpret_cast<const float2*>(sc.nodef + cur));
             ++nn;
-            const float lo0[3] = {q0.x, q0.y, q0.z}, hi0[3] = {q0.w, q1.x, q1.y};
-            const float lo1[3] = {q1.z, q1.w, q2.x}, hi1[3] = {q2.y, q2.z, q2.w};
             const int32_t c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
             const float tlimit = ANYHIT ? fminf(h.t, tcap) : h.t;
             float tn0, tn1;
-            const bool h0 = cv::box_may_hit(rk, lo0, hi0, q3.z, ff.x, tlimit, tn0);
-            const bool h1 = cv::box_may_hit(rk, lo1, hi1, q3.w, ff.y, tlimit, tn1);
+            // child 0: ctr (q0.x q0.y q0.z) ext (q0.w q1.x q1.y); child 1: ctr (q1.z q1.w q2.x) ext (q2.y q2.z q2.w)
+            const bool h0 = cv::box_may_hit(rk.ox, rk.oy, rk.oz, rk.idx, rk.idy, rk.idz, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q3.z,
+                                            ff.x * 1.00001f + RT_SLAB_REL, tlimit, tn0);
+            const bool h1 = cv::box_may_hit(rk.ox, rk.oy, rk.oz, rk.idx, rk.idy, rk.idz, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, q3.w,
+                                            ff.y * 1.00001f + RT_SLAB_REL, tlimit, tn1);
             if (h0 && h1) {
                 const bool first0 = tn0 <= tn1;
                 cur = first0 ? c0 : c1;

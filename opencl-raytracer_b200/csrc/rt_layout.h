@@ -14,9 +14,9 @@ struct CullRec {       // 32 B, two 128-bit loads
     uint32_t type;     // 0 sphere, 1 box, other: never hit (the kernels' switch has no default)
 };
 
-struct BvhNode {  // 64 B: both children's boxes
-    float lo0[3], hi0[3];
-    float lo1[3], hi1[3];
+struct BvhNode {  // 64 B: both children's boxes as centre + half extent (the slab test needs no min/max then)
+    float ctr0[3], ext0[3];
+    float ctr1[3], ext1[3];
     int32_t c0, c1;  // >= 0: inner node index; < 0: leaf, ~c = (first << 4) | (count - 1)
     float a0, a1;    // static pad of each child box (rounding of the slab arithmetic)
 };

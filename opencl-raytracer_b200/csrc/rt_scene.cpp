@@ -451,18 +451,20 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
         if (n.left >= 0) return inner_index[bi];
         return ~(int32_t)((n.first << 4) | (n.count - 1));
     };
-    auto child = [&](int bi, float* lo, float* hi, float& a, float& f) {
+    auto child = [&](int bi, float* ctr, float* ext, float& a, float& f) {
         const BuildNode& n = bld.bn[bi];
         double rf2 = 0;
         for (int k = 0; k < 3; ++k) {
-            lo[k] = down(n.lo[k]);
-            hi[k] = up(n.hi[k]);
+            const double c = 0.5 * (n.lo[k] + n.hi[k]);
+            ctr[k] = (float)c;
+            // half extent measured from the ROUNDED centre, rounded up
+            ext[k] = up(std::max(n.hi[k] - (double)ctr[k], (double)ctr[k] - n.lo[k]));
             const double m = std::max(fabs(n.lo[k]), fabs(n.hi[k]));
             rf2 += m * m;
         }
         const double rfar = sqrt(rf2);
         f = up(n.f);
-        // slab arithmetic of cv::box_may_hit: (lo - o) rounds with error <= u * max(|lo|, |o|)
+        // slab arithmetic of cv::box_may_hit: (ctr - o) rounds with error <= u * max(|ctr|, |o|)
         a = up(8.0 * U * (omax + rfar));
     };
     for (size_t i = 0; i < bld.bn.size(); ++i) {
@@ -470,8 +472,8 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
         if (n.left < 0) continue;
         BvhNode& d = out.nodes[inner_index[i]];
         BvhNodeF& df = out.nodef[inner_index[i]];
-        child(n.left, d.lo0, d.hi0, d.a0, df.f0);
-        child(n.right, d.lo1, d.hi1, d.a1, df.f1);
+        child(n.left, d.ctr0, d.ext0, d.a0, df.f0);
+        child(n.right, d.ctr1, d.ext1, d.a1, df.f1);
         d.c0 = ref_of(n.left);
         d.c1 = ref_of(n.right);
     }

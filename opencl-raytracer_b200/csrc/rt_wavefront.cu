@@ -12,6 +12,8 @@
 // generation costs an early-exit launch, never a host round trip.
 #include "rt_wavefront.cuh"
 
+#include <stdlib.h>
+
 #include "rt_wave.cuh"
 
 namespace rt {
@@ -139,7 +141,8 @@ __device__ __forceinline__ bool leaf_filter(const Scene& sc, uint32_t slot, floa
 template <bool COUNT>
 __global__ void __launch_bounds__(kBlock, 3) wave_trace_bvh(const Scene sc, const TaskQueue q, const uint32_t* __restrict__ n_ptr,
                                                             uint32_t* __restrict__ fetch, float* __restrict__ res_t,
-                                                            int32_t* __restrict__ res_id, const uint32_t leaf_max, Counters* ctr) {
+                                                            int32_t* __restrict__ res_id, const int min_t, const int drain_t,
+                                                            const int refill_t, Counters* ctr) {
     const uint32_t n = *n_ptr;
     if (n == 0u) return;
     __shared__ uint32_t pend[kPendCap][kBlock];
@@ -157,15 +160,14 @@ __global__ void __launch_bounds__(kBlock, 3) wave_trace_bvh(const Scene sc, cons
     int sp = 0, npend = 0;
     int32_t stack[RT_BVH_STACK];
     bool exhausted = false;
-    const int stall_level = kPendCap - 2 * (int)min(leaf_max, (uint32_t)(kPendCap / 2));
-    const float fglob = sc.root_f * 1.00001f;  // covers the approximate square root of d_far
+    const float fglob = sc.root_f * 1.00001f + RT_SLAB_REL;  // covers the approximate square root of d_far and the slab rounding
 
     for (;;) {
         // ---- refill
         {
             const unsigned idle = __ballot_sync(kFull, !have);
             const unsigned trav = __ballot_sync(kFull, have && !tdone);
-            if (idle && !exhausted && (__popc(idle) >= 8 || trav == 0u)) {
+            if (idle && !exhausted && (__popc(idle) >= refill_t || trav == 0u)) {
                 uint32_t base = 0;
                 if (lane == 0) base = atomicAdd(fetch, (uint32_t)__popc(idle));
                 base = __shfl_sync(kFull, base, 0);
@@ -210,61 +212,51 @@ __global__ void __launch_bounds__(kBlock, 3) wave_trace_bvh(const Scene sc, cons
 
         // ---- node steps
         for (;;) {
-            const bool go = have && !tdone && npend <= stall_level;
+            // a lane that holds a candidate waits for its exact test: nothing is traversed with a stale best t
+            const bool go = have && !tdone && npend == 0;
             const unsigned T = __ballot_sync(kFull, go);
             if (T == 0u) break;
-            if (__popc(T) < 20) {
-                const unsigned P = __ballot_sync(kFull, have && npend > 0);
-                if (__popc(P) >= 16) break;
-                if (__any_sync(kFull, have && !tdone && npend > stall_level)) break;
-                if (!exhausted && __popc(__ballot_sync(kFull, !have || (tdone && npend == 0))) >= 8) break;
-                if (__popc(__ballot_sync(kFull, have && tdone && npend > 0)) >= 12) break;
+            if (__popc(T) < min_t) {
+                if (__popc(__ballot_sync(kFull, have && npend > 0)) >= drain_t) break;
+                if (!exhausted && __popc(__ballot_sync(kFull, !have || (tdone && npend == 0))) >= refill_t) break;
             }
             if (go) {
                 const float4* np = reinterpret_cast<const float4*>(sc.nodes + cur);
                 const float4 q0 = __ldg(np + 0), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
                 if (COUNT) lc.node_visits++;
                 const float tlimit = anyhit ? fminf(best.t, 1.f) : best.t;
-                const float aix = fabsf(idx), aiy = fabsf(idy), aiz = fabsf(idz);
-                // child 0: lo (q0.x q0.y q0.z) hi (q0.w q1.x q1.y); child 1: lo (q1.z q1.w q2.x) hi (q2.y q2.z q2.w)
-                float lx = q0.x - ox, hx = q0.w - ox, ly = q0.y - oy, hy = q1.x - oy, lz = q0.z - oz, hz = q1.y - oz;
-                float mx = fmaxf(fabsf(lx), fabsf(hx)), my = fmaxf(fabsf(ly), fabsf(hy)), mz = fmaxf(fabsf(lz), fabsf(hz));
-                const float infl0 = fmaf(fglob, sqrtf(fmaf(mz, mz, fmaf(my, my, mx * mx))), q3.z);
-                float ax = lx * idx, bx = hx * idx, ay = ly * idy, by = hy * idy, az = lz * idz, bz = hz * idz;
-                float tn0 = fmaxf(fmaxf(fmaf(-infl0, aix, fminf(ax, bx)), fmaf(-infl0, aiy, fminf(ay, by))), fmaf(-infl0, aiz, fminf(az, bz)));
-                float tf0 = fminf(fminf(fmaf(infl0, aix, fmaxf(ax, bx)), fmaf(infl0, aiy, fmaxf(ay, by))), fmaf(infl0, aiz, fmaxf(az, bz)));
-                lx = q1.z - ox; hx = q2.y - ox; ly = q1.w - oy; hy = q2.z - oy; lz = q2.x - oz; hz = q2.w - oz;
-                mx = fmaxf(fabsf(lx), fabsf(hx)); my = fmaxf(fabsf(ly), fabsf(hy)); mz = fmaxf(fabsf(lz), fabsf(hz));
-                const float infl1 = fmaf(fglob, sqrtf(fmaf(mz, mz, fmaf(my, my, mx * mx))), q3.w);
-                ax = lx * idx; bx = hx * idx; ay = ly * idy; by = hy * idy; az = lz * idz; bz = hz * idz;
-                float tn1 = fmaxf(fmaxf(fmaf(-infl1, aix, fminf(ax, bx)), fmaf(-infl1, aiy, fminf(ay, by))), fmaf(-infl1, aiz, fminf(az, bz)));
-                float tf1 = fminf(fminf(fmaf(infl1, aix, fmaxf(ax, bx)), fmaf(infl1, aiy, fmaxf(ay, by))), fmaf(infl1, aiz, fmaxf(az, bz)));
-                const float s0 = 1e-5f * fmaxf(fabsf(tn0), fabsf(tf0)), s1 = 1e-5f * fmaxf(fabsf(tn1), fabsf(tf1));
-                bool h0 = !(tn0 - s0 > fminf(tf0, tlimit)) && !(tf0 + s0 < 0.f);
-                bool h1 = !(tn1 - s1 > fminf(tf1, tlimit)) && !(tf1 + s1 < 0.f);
+                float tn0, tn1;
+                // child 0: ctr (q0.x q0.y q0.z) ext (q0.w q1.x q1.y); child 1: ctr (q1.z q1.w q2.x) ext (q2.y q2.z q2.w)
+                bool h0 = cv::box_may_hit(ox, oy, oz, idx, idy, idz, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q3.z, fglob, tlimit, tn0);
+                bool h1 = cv::box_may_hit(ox, oy, oz, idx, idy, idz, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, q3.w, fglob, tlimit, tn1);
                 const int32_t c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
-                if (h0 && c0 < 0) {  // leaf child: its objects become candidates
-                    const uint32_t code = (uint32_t)(~c0);
-                    const uint32_t first = code >> 4, cnt = (code & 15u) + 1u;
-                    for (uint32_t j = 0; j < cnt; ++j)
-                        if (leaf_filter(sc, first + j, ox, oy, oz, ux, uy, uz)) pend[npend++][tid] = first + j;
-                    h0 = false;
-                }
-                if (h1 && c1 < 0) {
-                    const uint32_t code = (uint32_t)(~c1);
-                    const uint32_t first = code >> 4, cnt = (code & 15u) + 1u;
-                    for (uint32_t j = 0; j < cnt; ++j)
-                        if (leaf_filter(sc, first + j, ox, oy, oz, ux, uy, uz)) pend[npend++][tid] = first + j;
-                    h1 = false;
+                if ((h0 && c0 < 0) || (h1 && c1 < 0)) {  // leaf children: their objects become candidates
+#pragma unroll 1
+                    for (int side = 0; side < 2; ++side) {
+                        const int32_t c = side ? c1 : c0;
+                        if (!(side ? h1 : h0) || c >= 0) continue;
+                        const uint32_t code = (uint32_t)(~c);
+                        const uint32_t first = code >> 4, cnt = (code & 15u) + 1u;
+                        for (uint32_t j = 0; j < cnt; ++j)
+                            if (leaf_filter(sc, first + j, ox, oy, oz, ux, uy, uz)) {
+                                if (npend < kPendCap) {
+                                    pend[npend++][tid] = first + j;
+                                } else {  // buffer full (leaves larger than the buffer): test in place
+                                    exact_pair_call(sc, q.s[task], q.d[task], __ldg(sc.leaf_obj + first + j),
+                                                    __ldg(&sc.leaf_cull[first + j].type), best, btype);
+                                    if (COUNT) lc.exact_tests++;
+                                }
+                            }
+                    }
+                    h0 = h0 && c0 >= 0;
+                    h1 = h1 && c1 >= 0;
                 }
                 if (h0 && h1) {
                     const bool first0 = tn0 <= tn1;
                     cur = first0 ? c0 : c1;
                     stack[sp++] = first0 ? c1 : c0;
-                } else if (h0) {
-                    cur = c0;
-                } else if (h1) {
-                    cur = c1;
+                } else if (h0 || h1) {
+                    cur = h0 ? c0 : c1;
                 } else if (sp > 0) {
                     cur = stack[--sp];
                 } else {
@@ -278,10 +270,8 @@ __global__ void __launch_bounds__(kBlock, 3) wave_trace_bvh(const Scene sc, cons
             const bool has = have && npend > 0;
             const unsigned P = __ballot_sync(kFull, has);
             if (P == 0u) break;
-            const unsigned T = __ballot_sync(kFull, have && !tdone && npend <= stall_level);
-            const bool stalled = __any_sync(kFull, have && !tdone && npend > stall_level);
-            const int nF = __popc(__ballot_sync(kFull, has && tdone));
-            if (!(__popc(P) >= 16 || stalled || T == 0u || nF >= 12)) break;
+            const unsigned T = __ballot_sync(kFull, have && !tdone && npend == 0);
+            if (!(__popc(P) >= drain_t || T == 0u)) break;
             if (has) {
                 const uint32_t slot = pend[--npend][tid];
                 exact_pair_call(sc, q.s[task], q.d[task], __ldg(sc.leaf_obj + slot), __ldg(&sc.leaf_cull[slot].type), best, btype);
@@ -493,8 +483,16 @@ uint32_t wave_max_generations(uint32_t max_bounces, uint32_t n_lights, int mode)
     return (uint32_t)(g > 0x7fffffffull ? 0x7fffffffull : g);
 }
 
+static int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return v && *v ? atoi(v) : dflt;
+}
+
 cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb, int accel, uint32_t leaf_max, int sm_count,
                         uint32_t* launches, cudaStream_t stream) {
+    // warp-scheduler thresholds of wave_trace_bvh (tunable for experiments)
+    static const int min_t = env_int("RT_WAVE_MIN_T", 20), drain_t = env_int("RT_WAVE_DRAIN", 12), refill_t = env_int("RT_WAVE_REFILL", 8);
+    (void)leaf_max;
     const uint32_t gens = wave_max_generations(fr.max_bounces, sc.n_lights, fr.mode);
     if (gens + 1 > wb.n_counts) return cudaErrorInvalidValue;
     cudaError_t e = cudaMemsetAsync(wb.counts, 0, sizeof(uint32_t) * 2 * (size_t)wb.n_counts, stream);
@@ -526,9 +524,9 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
         const TaskQueue& qout = wb.q[(g + 1u) & 1u];
         if (accel == 2) {
             if (count)
-                wave_trace_bvh<true><<<pgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, fetch + g, wb.res_t, wb.res_id, leaf_max, fr.counters);
+                wave_trace_bvh<true><<<pgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, fetch + g, wb.res_t, wb.res_id, min_t, drain_t, refill_t, fr.counters);
             else
-                wave_trace_bvh<false><<<pgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, fetch + g, wb.res_t, wb.res_id, leaf_max, fr.counters);
+                wave_trace_bvh<false><<<pgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, fetch + g, wb.res_t, wb.res_id, min_t, drain_t, refill_t, fr.counters);
         } else if (accel == 1) {
             // two instantiations, each takes the queue sizes it is efficient for (the size lives on the device)
             const unsigned fgrid = (unsigned)sm_count * 2u;
