@@ -100,7 +100,7 @@ struct rt_ctx {
     uint32_t last_launches = 1;
 
     // options
-    int opt_pipeline = -1, opt_count = 0, opt_leaf = 4, opt_skip_dead = 1;
+    int opt_pipeline = -1, opt_count = 0, opt_leaf = 2, opt_skip_dead = 1;
 
     rt_stats stats;
 };
