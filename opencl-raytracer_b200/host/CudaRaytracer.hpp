@@ -1,0 +1,50 @@
+// CudaRaytracer -- drop-in backend behind the reference's IRaytracer interface (IRaytracer.hpp:10-21),
+// next to OpenCLRaytracer (OpenCLRaytracer.hpp:24-89).  Same constructor signature as
+// OpenCLRaytracer.hpp:61, same ownership rules as OpenCLRaytracer.cpp:13-105:
+//   * objects / lights / rays are borrowed references (the caller keeps them alive);
+//   * the scene and the rays are uploaded once, in the constructor (OpenCLRaytracer.cpp:70-73);
+//   * Render() launches, reads the frame back synchronously and returns a pointer to a buffer this object
+//     owns: rays.size() x cl_float4, index = ray index, xyz = unclamped linear RGB, w = 1; stable across
+//     calls, overwritten by each call, never freed by the caller.
+// Differences: the buffer is pinned host memory and is released in the destructor (the reference leaks it,
+// OpenCLRaytracer.cpp:76-78); errors surface as std::runtime_error carrying rt_last_error() instead of
+// boost::compute::opencl_error; there is no run-time kernel source and no CPU fallback.
+//
+// Reused unchanged from the reference: IRaytracer.hpp, ObjectData.hpp, Material.hpp, Light.hpp, Ray3D.hpp,
+// HitRecord.hpp (put the reference directory on the include path).  This class calls nothing but the
+// extern "C" layer of include/rt_b200.h.
+#pragma once
+
+#include <vector>
+
+#include "IRaytracer.hpp"
+#include "rt_b200.h"
+
+class CudaRaytracer : public IRaytracer {
+public:
+    CudaRaytracer(const std::vector<ObjectData>& objects, const std::vector<Light>& lights, const std::vector<Ray3D>& rays,
+                  const unsigned int MAX_BOUNCES);
+    ~CudaRaytracer();
+    CudaRaytracer(const CudaRaytracer&) = delete;
+    CudaRaytracer& operator=(const CudaRaytracer&) = delete;
+
+    // Inherited via IRaytracer
+    cl_float4* Render() override;
+
+    // Optional knobs the reference leaves as TODOs (OpenCL-Raytracer.cpp:29,34); defaults reproduce it.
+    void SetMode(rt_mode mode) { mode_ = mode; }        // default RT_MODE_SHADE_AND_REFLECT (the live kernel)
+    void SetAccel(rt_accel accel) { accel_ = accel; }   // default RT_ACCEL_AUTO
+    void SetOption(rt_option option, long long value);
+    // If `rays` is exactly the pinhole grid main() builds (OpenCL-Raytracer.cpp:68-72) for width x height, the rays
+    // are generated on the device instead of being uploaded (bit-identical, saves 32 B/ray of HBM and PCIe).
+    bool UseCameraIfPinhole(unsigned width, unsigned height);
+    rt_stats Stats() const;
+    size_t PixelCount() const { return rays.size(); }
+
+private:
+    rt_ctx* ctx_ = nullptr;
+    cl_float4* pixelDataArr = nullptr;  // pinned, rays.size() entries
+    const unsigned int MAX_BOUNCES;
+    rt_mode mode_ = RT_MODE_SHADE_AND_REFLECT;
+    rt_accel accel_ = RT_ACCEL_AUTO;
+};
