@@ -4,4 +4,4 @@
 `pyrt.lib` (the ctypes binding of librt_b200.so) is imported lazily; it fails loudly
 when the CUDA library is missing -- there is no CPU fallback.
 """
-from . import glm32, scenes, types  # noqa: F401
+from . import glm32, scenes, shard, types  # noqa: F401
