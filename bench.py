@@ -38,7 +38,7 @@ from pyrt import scenes, types  # noqa: E402
 METRIC = "Mrays/s (primary+shadow+reflect)"
 
 # flops of the arithmetic each counted unit executes (DESIGN.md "Work per unit")
-FLOPS_FILTER = 16.0   # bounding-sphere filter, expanded form: 1 add + 1 mul + 7 fma (rt_wavefront.cu)
+FLOPS_FILTER = 14.0   # bounding-sphere filter, expanded form: 7 fma per (ray, object) pair (rt_wavefront.cu)
 FLOPS_EXACT = 78.0    # reference arithmetic of one ray x object test as written
 FLOPS_NODE = 62.0     # two inflated slab tests of one BVH node
 FLOPS_SHADE = 100.0   # Phong terms per (hit, light)

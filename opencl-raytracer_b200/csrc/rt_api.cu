@@ -158,6 +158,7 @@ int sync_scene(rt_ctx* c) {
     s.n_nodes = (uint32_t)c->hs.nodes.size();
     s.root = c->hs.root;
     s.root_f = c->hs.f_global;
+    s.filter_h = c->hs.h_min;
     c->scene_dirty = false;
     return RT_OK;
 }

@@ -53,6 +53,7 @@ struct Scene {
     const Light* __restrict__ lights;
     uint32_t n_objs, n_lights, n_nodes, root_is_leaf;
     int32_t root;  // child-style reference to the root (leaf if negative)
+    float filter_h;        // smallest h = 1 - g of the scene (brute-force filter folds it into per-ray constants)
     float root_a, root_f;  // root_f: the scene-wide largest cone coefficient (wavefront traversal uses it for every node)
 };
 

@@ -405,6 +405,7 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
         const double ccf = (double)cr.cx * cr.cx + (double)cr.cy * cr.cy + (double)cr.cz * cr.cz;
         cr.cc = (float)ccf;
         cr.e0 = down((double)cr.h * ccf * (1.0 - 8.0 * U) - (double)cr.r2);
+        out.h_min = std::min(out.h_min, cr.h);
         live.push_back(i);
     }
 

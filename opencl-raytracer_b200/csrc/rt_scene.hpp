@@ -32,6 +32,7 @@ struct HostScene {
     float omax = 0.f;      // bound on |ray origin| the pads were computed for
     float scene_radius = 0.f;
     uint32_t bvh_depth = 0;
+    float h_min = 1.f;     // smallest filter coefficient h = 1 - g over the live objects
     float f_global = 0.f;  // largest cone coefficient of the scene (per-node values are in nodef)
 };
 

@@ -316,28 +316,25 @@ __global__ void __launch_bounds__(kBlock) wave_trace_brute(const Scene sc, const
 }
 
 // N-body layout: RPT rays per thread in registers, the filter records of a tile of objects in shared memory
-// (every lane of a warp reads the same record: one broadcast wavefront per load), survivors run the exact test.
+// (every lane of a warp reads the same 16-byte record: one broadcast LDS.128 per object), survivors run the
+// exact test.
 //
-// Per pair the filter evaluates  h*|c-o|^2 - ((c-o).u)^2 > r2  in expanded form, 1 FADD + 1 FMUL + 7 FFMA:
-//     dt  = c.u - o.u                 3 FFMA   (o.u per ray)
-//     oc2 = |c|^2 + |o|^2 - 2 c.o     1 FADD + 3 FFMA   (|c|^2 per object, |o|^2 and -2o per ray)
-//     lhs = h*oc2 - dt*dt             1 FMUL + 1 FFMA
-// The expanded form cancels when |c|, |o| >> |c-o|; its rounding error is below 42 u (|c|^2 + |o|^2), which is
-// added to the accept side (kExpandPad on r2 per object and on |o|^2 per ray) so the filter stays conservative.
-constexpr int kFilterTile = 1024;          // objects per tile
-constexpr float kExpandPad = 3.8147e-06f;  // 64 u
-
-struct FilterRec {  // 24 B per object in shared memory: one LDS.128 + one LDS.64, both warp-broadcast
-    float4 a;       // cx, cy, cz, |c|^2
-    float2 b;       // r2 + pad, h
-};
+// The bounding-sphere filter  h*|c-o|^2 - ((c-o).u)^2 > r2  (reject) is evaluated in expanded form with the
+// scene-wide smallest h (conservative: a smaller h only lets more pairs through) folded into per-ray constants:
+//     dt   = c.u - o.u                          3 FFMA      (o.u per ray)
+//     w    = h*|o|^2 - 2h c.o                   3 FFMA      (h*|o|^2 and -2h*o per ray)
+//     lhs2 = w - dt*dt                          1 FFMA
+//     reject iff lhs2 > e,  e = r2 - h*|c|^2    1 FSETP     (e per object, computed when the tile is staged)
+// 7 FFMA + 1 compare per pair.  The expanded form cancels when |c|, |o| >> |c-o|; its rounding error is below
+// 44 u (|c|^2 + |o|^2), which is added to the accept side (kExpandPad on e per object and on |o|^2 per ray).
+constexpr int kFilterTile = 2048;          // objects per tile (32 KB of shared memory)
+constexpr float kExpandPad = 4.7684e-06f;  // 80 u
 
 __device__ __noinline__ void filter_exact(const Scene& sc, const TaskQueue& q, uint32_t ray_idx, uint32_t obj, float* bt, int32_t* bi) {
     Hit best;
     best.t = *bt;
     best.id = *bi;
-    const uint32_t btype0 = best.id >= 0 ? __ldg(&sc.cull[best.id].type) : 0u;
-    uint32_t btype = btype0;
+    uint32_t btype = best.id >= 0 ? __ldg(&sc.cull[best.id].type) : 0u;
     Ray r;
     r.s = q.s[ray_idx];
     r.d = q.d[ray_idx];
@@ -352,12 +349,12 @@ __global__ void __launch_bounds__(kBlock, 2) wave_trace_filter(const Scene sc, c
                                                                int32_t* __restrict__ res_id, Counters* ctr) {
     const uint32_t n = *n_ptr;
     if (n == 0u || n < n_min || n >= n_max) return;  // the other instantiation handles this queue size
-    __shared__ float4 tA[kFilterTile];
-    __shared__ float2 tB[kFilterTile];
+    __shared__ float4 tile[kFilterTile];             // cx, cy, cz, e
     __shared__ float best_t[RPT][kBlock];
     __shared__ int32_t best_i[RPT][kBlock];
     LocalCounters lc;
     const uint32_t M = sc.n_objs;
+    const float hmin = sc.filter_h;
     const float4* cull4 = reinterpret_cast<const float4*>(sc.cull);
     const uint32_t per_block = kBlock * RPT;
     const uint32_t n_groups = (n + per_block - 1) / per_block;
@@ -377,11 +374,11 @@ __global__ void __launch_bounds__(kBlock, 2) wave_trace_filter(const Scene sc, c
                 ry.d = q.d[i];
                 const cv::RayK rk = cv::prepare(ry);
                 ux[r] = rk.ux; uy[r] = rk.uy; uz[r] = rk.uz;
-                px[r] = -2.f * rk.ox; py[r] = -2.f * rk.oy; pz[r] = -2.f * rk.oz;
+                px[r] = -2.f * hmin * rk.ox; py[r] = -2.f * hmin * rk.oy; pz[r] = -2.f * hmin * rk.oz;
                 nq[r] = -(rk.ox * rk.ux + rk.oy * rk.uy + rk.oz * rk.uz);
                 const float o2 = rk.ox * rk.ox + rk.oy * rk.oy + rk.oz * rk.oz;
-                oo[r] = o2 - 2.f * kExpandPad * o2;
-            } else {  // padding: u = 0, o = 0 -> lhs = h*|c|^2, rejected unless the object sits on the origin
+                oo[r] = hmin * (o2 - 2.f * kExpandPad * o2);
+            } else {  // padding: everything 0 -> lhs2 = 0, rejected unless the object contains the origin
                 ux[r] = uy[r] = uz[r] = px[r] = py[r] = pz[r] = nq[r] = oo[r] = 0.f;
             }
         }
@@ -391,21 +388,21 @@ __global__ void __launch_bounds__(kBlock, 2) wave_trace_filter(const Scene sc, c
             for (uint32_t j = tid; j < cnt; j += kBlock) {
                 const float4 a = __ldg(cull4 + 2 * (size_t)(t0 + j));       // cx cy cz r2
                 const float4 b = __ldg(cull4 + 2 * (size_t)(t0 + j) + 1);   // h cc e0 type
-                tA[j] = make_float4(a.x, a.y, a.z, b.y);
-                tB[j] = make_float2(a.w < 0.f ? a.w : fmaf(kExpandPad, b.y, a.w), b.x);  // r2 < 0 marks "never hit"
+                // r2 < 0 marks "never hit": e = -inf rejects every finite lhs2
+                const float e = a.w < 0.f ? -__int_as_float(0x7f800000) : fmaf(-hmin, b.y, fmaf(kExpandPad, b.y, a.w));
+                tile[j] = make_float4(a.x, a.y, a.z, e);
             }
             __syncthreads();
 #pragma unroll 2
             for (uint32_t j = 0; j < cnt; ++j) {
-                const float4 a = tA[j];
-                const float2 b = tB[j];
+                const float4 a = tile[j];
                 bool pass[RPT];
                 bool any = false;
 #pragma unroll
                 for (int r = 0; r < RPT; ++r) {
                     const float dt = fmaf(a.x, ux[r], fmaf(a.y, uy[r], fmaf(a.z, uz[r], nq[r])));
-                    const float oc2 = fmaf(a.x, px[r], fmaf(a.y, py[r], fmaf(a.z, pz[r], a.w + oo[r])));
-                    pass[r] = !(fmaf(-dt, dt, oc2 * b.y) > b.x);
+                    const float w = fmaf(a.x, px[r], fmaf(a.y, py[r], fmaf(a.z, pz[r], oo[r])));
+                    pass[r] = !(fmaf(-dt, dt, w) > a.w);
                     any |= pass[r];
                 }
                 if (any) {

@@ -38,6 +38,8 @@ void bind(const rt::HostScene& hs, rt::Scene& s) {
     s.n_lights = hs.n_lights;
     s.n_nodes = (uint32_t)hs.nodes.size();
     s.root = hs.root;
+    s.root_f = hs.f_global;
+    s.filter_h = hs.h_min;
 }
 
 template <int ACCEL>
