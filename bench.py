@@ -50,6 +50,9 @@ def workload(name: str, args):
     if name == "cfg5-box":
         o, l = scenes.synthetic_scene(100_000, 4096)
         return o, l, 7680, 4320, 4, 2, "synthetic 100k boxes + 4096 spheres, 7680x4320, reflection depth 4"
+    if name == "cfg5-tri":  # extension: type 2 unit triangles (no reference primitive)
+        o, l = scenes.synthetic_scene(100_000, 4096, second_type=types.TRIANGLE)
+        return o, l, 7680, 4320, 4, 2, "synthetic 100k triangles (extension) + 4096 spheres, 7680x4320, reflection depth 4"
     if name == "cfg5-small":
         o, l = scenes.synthetic_scene(100_000, 4096)
         return o, l, 1920, 1080, 4, 2, "synthetic 100k boxes + 4096 spheres, 1920x1080, reflection depth 4"

@@ -72,7 +72,10 @@ typedef struct rt_object {
     rt_material mat;
     float mv[16];
     float mvInverse[16];
-    uint32_t type; /* 0 = unit sphere, 1 = unit cube [-0.5,0.5]^3 (ObjectData.hpp:9-12) */
+    uint32_t type; /* 0 = unit sphere, 1 = unit cube [-0.5,0.5]^3 (ObjectData.hpp:9-12);
+                    * 2 = EXTENSION, unit triangle x >= -0.5, y >= -0.5, x + y <= 0 in the plane z = 0 (the reference has no
+                    * triangle primitive; static_cast<ObjectData::PrimativeType>(2) encodes it without a header change);
+                    * any other value is never hit, as in the reference kernels' switch without default */
 } rt_object;
 
 /* Light.hpp:4-16 / cl_Light OpenCLRaytracer.hpp:52-58. position is view space. */

@@ -169,12 +169,22 @@ __device__ __forceinline__ bool candidate(uint32_t type, const float4 s, const f
         t = tHit;
         return true;
     }
+    if (type == 2u) {  // EXTENSION: unit triangle x >= -0.5, y >= -0.5, x + y <= 0 in the plane z = 0 (oracle_rt.c, type 2)
+        if (d.z == 0.f) return false;
+        const float tHit = div(sub(0.f, s.z), d.z);
+        if (tHit < 0.f) return false;
+        const float px = add(s.x, mul(tHit, d.x));
+        const float py = add(s.y, mul(tHit, d.y));
+        if (px < -0.5f || py < -0.5f || add(px, py) > 0.f) return false;
+        t = tHit;
+        return true;
+    }
     return false;  // any other type value: the kernels' switch has no default
 }
 
 // Does candidate (tc, c) replace the current best (tk, k)?  Order-independent form of
 // the sequential rules "sphere skipped only if hit.time < t" (SAR:108) and "box skipped
-// if hit.time <= t" (SAR:147): among objects tied at the minimum t the winner is the
+// if hit.time <= t" (SAR:147; the triangle extension follows the box rule): among objects tied at the minimum t the winner is the
 // highest-index sphere if any sphere is tied, else the lowest-index box.
 __device__ __forceinline__ bool replaces(float tc, int32_t c, uint32_t type_c, float tk, int32_t k, uint32_t type_k) {
     if (k < 0) return true;
@@ -205,8 +215,11 @@ __device__ __forceinline__ Surface surface(const Scene& sc, int32_t id, float t,
     Surface sf;
     sf.P = xform(c0, c1, c2, c3, po);
     float4 no;
-    if (__ldg(&sc.cull[id].type) == 0u) {
+    const uint32_t type = __ldg(&sc.cull[id].type);
+    if (type == 0u) {
         no = make_float4(po.x, po.y, po.z, 0.f);
+    } else if (type == 2u) {  // EXTENSION: unit triangle, plane normal
+        no = make_float4(0.f, 0.f, 1.f, 0.f);
     } else {
         no = make_float4(0.f, 0.f, 0.f, 0.f);
         if (po.x > 0.4998f) no.x = add(no.x, 1.f); else if (po.x < -0.4998f) no.x = sub(no.x, 1.f);

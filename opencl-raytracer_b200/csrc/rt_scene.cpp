@@ -319,7 +319,7 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
         M3 A, F;
         for (int r = 0; r < 3; ++r)
             for (int c = 0; c < 3; ++c) A.a[r][c] = mi[4 * c + r];
-        if (o.type > 1u) {  // never hit: keep a degenerate record far away
+        if (o.type > 2u) {  // never hit: keep a degenerate record far away
             g.c[0] = g.c[1] = g.c[2] = 0;
             g.ext[0] = g.ext[1] = g.ext[2] = 0;
             g.R = 0;
@@ -339,6 +339,22 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
         if (o.type == 0u) {
             for (int r = 0; r < 3; ++r) g.ext[r] = sqrt(F.a[r][0] * F.a[r][0] + F.a[r][1] * F.a[r][1] + F.a[r][2] * F.a[r][2]);
             g.R = g.smax;
+        } else if (o.type == 2u) {
+            // unit triangle (-.5,-.5,0) (.5,-.5,0) (-.5,.5,0): bounded around the image of the object origin (the midpoint
+            // of the hypotenuse).  Its hit decision rounds like the box's slabs (error linear in |s|), same pads.
+            const double vx[3] = {-0.5, 0.5, -0.5}, vy[3] = {-0.5, -0.5, 0.5};
+            double rmax = 0;
+            for (int r = 0; r < 3; ++r) g.ext[r] = 0;
+            for (int v = 0; v < 3; ++v) {
+                double v2 = 0;
+                for (int r = 0; r < 3; ++r) {
+                    const double c = F.a[r][0] * vx[v] + F.a[r][1] * vy[v];
+                    g.ext[r] = std::max(g.ext[r], fabs(c));
+                    v2 += c * c;
+                }
+                rmax = std::max(rmax, sqrt(v2));
+            }
+            g.R = rmax;
         } else {
             for (int r = 0; r < 3; ++r) g.ext[r] = 0.5 * (fabs(F.a[r][0]) + fabs(F.a[r][1]) + fabs(F.a[r][2]));
             double rmax = 0;
@@ -369,7 +385,7 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
         const Geo& g = geo[i];
         CullRec& cr = out.cull[i];
         cr.type = objs[i].type;
-        if (objs[i].type > 1u) {
+        if (objs[i].type > 2u) {
             cr.cx = cr.cy = cr.cz = 0.f;
             cr.r2 = -1.f;  // h*|oc|^2 - dt^2 >= ... never <= -1 unless NaN
             cr.h = 1.f;

@@ -45,6 +45,7 @@ assert LIGHT_DTYPE.itemsize == 52
 assert RAY_DTYPE.itemsize == 32
 
 SPHERE, BOX = 0, 1
+TRIANGLE = 2  # extension (no reference primitive): unit triangle x >= -0.5, y >= -0.5, x + y <= 0, z = 0
 MODE_HITTEST, MODE_SHADE, MODE_SAR = 0, 1, 2
 ACCEL_AUTO, ACCEL_BRUTE, ACCEL_CULL, ACCEL_BVH = -1, 0, 1, 2
 MAX_FLOAT = np.float32(3.402823466e38)

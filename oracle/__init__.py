@@ -7,6 +7,8 @@ legs may import this package.  The product path (opencl-raytracer_b200/) never d
           (parity build, -O2 -ffp-contract=off); ref(fast=True) is the -O3 AVX2 timing build
   port()  oracle/liboracle_rt.so          the plain-C restatement (oracle_rt.c) that also
           reports hit ids, t and ray counts, which the reference never outputs
+  ocl_*() oracle/libocl_ref.so            the reference's unchanged .cl source on the box's OpenCL platform
+          (baseline/_ref/*.cl staged by `make ocl`), when one enumerates
 """
 from __future__ import annotations
 
@@ -107,3 +109,50 @@ def port_trace(objs, rays, nthreads: int = 0):
     if rc != 0:
         raise RuntimeError("oracle_trace failed: %d" % rc)
     return hid, ht
+
+
+# ---------------------------------------------------------------- the reference .cl on the box's OpenCL platform
+_ROOT = os.path.dirname(_HERE)
+_CL_FILES = {1: ("shade_kernel.cl", "shade"), 2: ("shade_and_reflect_kernel.cl", "shade_and_reflect")}
+
+
+def ocl():
+    if "ocl" not in _libs:
+        lib = C.CDLL(os.path.join(_HERE, "libocl_ref.so"))
+        lib.ocl_ref_probe.restype = C.c_int
+        lib.ocl_ref_probe.argtypes = [C.c_char_p, C.c_int]
+        lib.ocl_ref_render.restype = C.c_int
+        lib.ocl_ref_render.argtypes = [C.c_char_p, C.c_char_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32,
+                                       C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.POINTER(C.c_double),
+                                       C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_char_p, C.c_int]
+        _libs["ocl"] = lib
+    return _libs["ocl"]
+
+
+def ocl_probe():
+    """-> (available, description): is there an OpenCL GPU platform, and the staged kernel sources, on this box?"""
+    if not os.path.exists(os.path.join(_HERE, "libocl_ref.so")):
+        return False, "oracle/libocl_ref.so not built"
+    if not os.path.exists(os.path.join(_ROOT, "baseline", "_ref", "shade_and_reflect_kernel.cl")):
+        return False, "baseline/_ref/*.cl not staged (make -C oracle ocl in the build container)"
+    buf = C.create_string_buffer(512)
+    rc = ocl().ocl_ref_probe(buf, 512)
+    return rc == 0, buf.value.decode(errors="replace")
+
+
+def ocl_render(kernel: int, max_bounces: int, objs, lights, rays, frames: int = 1):
+    """OpenCLRaytracer ctor + `frames` x Render() with the reference's unchanged kernel source.
+    -> (rgba (N,4) f32, {"kernel_ms", "render_ms", "build_ms"})"""
+    fname, kname = _CL_FILES[kernel]
+    objs = np.ascontiguousarray(objs)
+    lights = np.ascontiguousarray(lights)
+    rays = np.ascontiguousarray(rays)
+    out = np.empty((rays.shape[0], 4), dtype=np.float32)
+    k, r, b = C.c_double(0), C.c_double(0), C.c_double(0)
+    log = C.create_string_buffer(2048)
+    rc = ocl().ocl_ref_render(os.path.join(_ROOT, "baseline", "_ref", fname).encode(), kname.encode(), max_bounces,
+                              _ptr(objs), objs.shape[0], _ptr(lights), lights.shape[0], _ptr(rays), rays.shape[0], frames,
+                              _ptr(out), C.byref(k), C.byref(r), C.byref(b), log, 2048)
+    if rc != 0:
+        raise RuntimeError("ocl_ref_render failed: %s" % log.value.decode(errors="replace"))
+    return out, {"kernel_ms": k.value, "render_ms": r.value, "build_ms": b.value}

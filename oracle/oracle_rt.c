@@ -152,6 +152,27 @@ static int raycast(const rt_object* objs, uint32_t count, v4 rstart, v4 rdir, hi
             v3 n3 = {n.x, n.y, n.z};
             hit->N = v3normalize(n3);
             hit->mat = &obj->mat;
+        } else if (obj->type == 2) {
+            /* EXTENSION (no reference code): canonical unit triangle, the half of the
+             * unit square [-0.5,0.5]^2 of the plane z = 0 below its diagonal: x >= -0.5, y >= -0.5, x + y <= 0.
+             * Written in the style of the box case: object-space ray, IEEE divide, "skip if hit.time <= t" (lowest
+             * index wins ties among non-spheres), normal = normalize(mv * (0,0,1,0)), two-sided. */
+            if (d.z == 0) continue;
+            const float tHit = (0.f - s.z) / d.z;
+            if (tHit < 0) continue;
+            const float px = s.x + tHit * d.x;
+            const float py = s.y + tHit * d.y;
+            if (px < -0.5f || py < -0.5f || px + py > 0.f) continue;
+            if (hit->time <= tHit) continue;
+            v4 po = {px, py, s.z + tHit * d.z, s.w + tHit * d.w};
+            v4 no = {0.f, 0.f, 1.f, 0.f};
+            hit->time = tHit;
+            hit->id = (int)k;
+            hit->P = xform(obj->mv, po);
+            const v4 n = xform(obj->mv, no);
+            v3 n3 = {n.x, n.y, n.z};
+            hit->N = v3normalize(n3);
+            hit->mat = &obj->mat;
         }
         /* any other type value: the kernels' switch has no default, the object is skipped */
     }

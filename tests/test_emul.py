@@ -32,13 +32,15 @@ def test_device_code_bit_exact_on_reference_scenes(oracle_mod, name, accel):
                 assert c["traced_shadow"] == c["ref_shadow"] and c["traced_reflect"] == c["ref_reflect"]
 
 
-@pytest.mark.parametrize("second_type", [T.BOX, T.SPHERE])
+@pytest.mark.parametrize("second_type", [T.BOX, T.SPHERE, T.TRIANGLE])
 def test_bvh_and_cull_equal_brute_force_synthetic(oracle_mod, second_type):
     objs, lights = S.synthetic_scene(3000, 300, second_type=second_type)
     _, rays = frame_rays(96, 54)
     ref, hid, ht, st = oracle_mod.port_render(2, 4, objs, lights, rays)
     assert st.rays_reflect > st.hit_pixels  # reflective materials are exercised
-    for accel in (1, 2):
+    if second_type == T.TRIANGLE:
+        assert np.isin(hid[hid >= 0], np.flatnonzero(objs["type"] == T.TRIANGLE)).mean() > 0.2
+    for accel in (0, 1, 2):
         out, eid, et, c = emul.render(objs, lights, rays, 4, 2, accel, 1)
         assert np.array_equal(eid, hid) and np.array_equal(et, ht) and np.array_equal(out, ref)
     for leaf in (1, 2, 8, 16):
@@ -46,12 +48,15 @@ def test_bvh_and_cull_equal_brute_force_synthetic(oracle_mod, second_type):
         assert np.array_equal(eid, hid) and np.array_equal(out, ref)
 
 
-def test_filters_never_drop_a_noisy_hit(oracle_mod):
-    """Adversarial for the bounds: tiny, strongly anisotropic spheres very far from the ray origins, where the
-    reference's discriminant is dominated by rounding noise (rt_scene.cpp header)."""
+@pytest.mark.parametrize("second_type", [T.SPHERE, T.BOX, T.TRIANGLE])
+def test_filters_never_drop_a_noisy_hit(oracle_mod, second_type):
+    """Adversarial for the bounds: tiny, strongly anisotropic objects very far from the ray origins, where the
+    reference's discriminant (spheres) / slab arithmetic is dominated by rounding noise (rt_scene.cpp header).
+    Rays are aimed at the jittered image of the object origin -- for the triangle extension that is a point ON its
+    hypotenuse, so about half of them graze the edge."""
     rng = np.random.Generator(np.random.PCG64(7))
     n = 400
-    objs, _ = S.synthetic_scene(n, 0, seed=11, second_type=T.SPHERE)
+    objs, _ = S.synthetic_scene(n, 0, seed=11, second_type=second_type)
     # shrink every object by 20x about its centre: mv' = mv * S(1/20), mvInverse' = S(20) * mvInverse
     mv = objs["mv"].reshape(n, 4, 4).copy()
     mi = objs["mvInverse"].reshape(n, 4, 4).copy()
@@ -69,7 +74,7 @@ def test_filters_never_drop_a_noisy_hit(oracle_mod):
     rays["start"][:, 3] = 1.0
     rays["direction"][:, :3] = (tgt - o) * rng.uniform(0.5, 30.0, size=(k, 1)).astype(np.float32)
     hid, ht = oracle_mod.port_trace(objs, rays)
-    assert (hid >= 0).sum() > k // 10
+    assert (hid >= 0).sum() > (k // 10 if second_type == T.SPHERE else k // 50), (hid >= 0).sum()
     lights = np.zeros(0, dtype=T.LIGHT_DTYPE)
     for accel in (1, 2):
         _, eid, et, _ = emul.render(objs, lights, rays, 0, 0, accel, 1)
@@ -172,3 +177,31 @@ def test_wavefront_state_machine_synthetic(oracle_mod):
     out, c, gens = emul.render_wave(objs, lights[:0], rays, 4, 2, 2)
     ref, *_ = oracle_mod.port_render(2, 4, objs, lights[:0], rays)
     assert np.array_equal(out, ref)
+
+
+def test_triangle_extension_geometry(oracle_mod):
+    """The type-2 extension against first principles: an axis-aligned unit triangle at z = -5, scale 2, seen from the
+    origin.  A pixel hits iff its ray meets the plane inside x >= -1, y >= -1, x + y <= 0 (object units x 2); two
+    coincident triangles tie towards the lower index (box rule); types >= 3 stay skipped like in the reference."""
+    mv = np.eye(4, dtype=np.float32)
+    mv[0, 0] = mv[1, 1] = mv[2, 2] = 2.0
+    mv[3, :3] = (0, 0, -5)
+    inv = np.linalg.inv(mv.astype(np.float64)).astype(np.float32)
+    tri = T.make_object(T.TRIANGLE, mv, inv, ambient=(0.2, 0.3, 0.4), diffuse=(0.5, 0.5, 0.5))
+    dead = T.make_object(3, mv, inv)
+    objs = np.stack([dead, tri, tri])
+    lights = np.stack([T.make_light((0, 0, 0, 1), ambient=(1, 1, 1), diffuse=(1, 1, 1))])
+    W, H = 96, 96
+    z, rays = frame_rays(W, H)
+    ref, hid, ht, _ = oracle_mod.port_render(2, 2, objs, lights, rays)
+    d = rays["direction"].astype(np.float64)
+    t = -5.0 / d[:, 2]
+    x, y = t * d[:, 0], t * d[:, 1]
+    inside = (x > -1 + 1e-6) & (y > -1 + 1e-6) & (x + y < -1e-6)
+    outside = (x < -1 - 1e-6) | (y < -1 - 1e-6) | (x + y > 1e-6)
+    assert inside.sum() > 50
+    assert (hid[inside] == 1).all() and (hid[outside] == -1).all()
+    assert np.allclose(ht[inside], t[inside], rtol=1e-6)
+    for accel in (0, 1, 2):
+        out, eid, et, _ = emul.render(objs, lights, rays, 2, 2, accel, 1, leaf=1)
+        assert np.array_equal(eid, hid) and np.array_equal(et, ht) and np.array_equal(out, ref)

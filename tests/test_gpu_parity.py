@@ -137,7 +137,7 @@ def test_golden_vectors(rt, ctx):
         ctx.set_option(rt.OPT_SKIP_DEAD_RAYS, 1)
 
 
-@pytest.mark.parametrize("second_type", [T.BOX, T.SPHERE])
+@pytest.mark.parametrize("second_type", [T.BOX, T.SPHERE, T.TRIANGLE])
 def test_synthetic_scene_against_oracle(rt, ctx, oracle_mod, second_type):
     objs, lights = S.synthetic_scene(6000, 500, second_type=second_type)
     W, H = 160, 90
