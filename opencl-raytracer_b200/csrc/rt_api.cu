@@ -71,7 +71,6 @@ struct rt_ctx {
     DevBuf<rt::F4> d_minv, d_mv, d_mat, d_lights;
     DevBuf<rt::CullRec> d_cull, d_leaf_cull;
     DevBuf<rt::BvhNode> d_nodes;
-    DevBuf<rt::BvhNodeF> d_nodef;
     DevBuf<uint32_t> d_leaf_obj;
     rt::Scene scene;
 
@@ -100,7 +99,7 @@ struct rt_ctx {
     uint32_t last_launches = 1;
 
     // options
-    int opt_pipeline = -1, opt_count = 0, opt_leaf = 2, opt_skip_dead = 1;
+    int opt_pipeline = -1, opt_count = 0, opt_leaf = 1, opt_skip_dead = 1;
 
     rt_stats stats;
 };
@@ -140,7 +139,6 @@ int sync_scene(rt_ctx* c) {
     RT_CUDA(c->d_cull.upload(c->hs.cull, c->stream));
     RT_CUDA(c->d_leaf_cull.upload(c->hs.leaf_cull, c->stream));
     RT_CUDA(c->d_nodes.upload(c->hs.nodes, c->stream));
-    RT_CUDA(c->d_nodef.upload(c->hs.nodef, c->stream));
     RT_CUDA(c->d_leaf_obj.upload(c->hs.leaf_obj, c->stream));
     RT_CUDA(cudaStreamSynchronize(c->stream));
     rt::Scene& s = c->scene;
@@ -149,7 +147,6 @@ int sync_scene(rt_ctx* c) {
     s.mat = reinterpret_cast<const float4*>(c->d_mat.p);
     s.cull = c->d_cull.p;
     s.nodes = c->d_nodes.p;
-    s.nodef = c->d_nodef.p;
     s.leaf_obj = c->d_leaf_obj.p;
     s.leaf_cull = c->d_leaf_cull.p;
     s.lights = reinterpret_cast<const rt::Light*>(c->d_lights.p);
@@ -350,7 +347,7 @@ int rt_destroy(rt_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     c->d_minv.release(); c->d_mv.release(); c->d_mat.release(); c->d_lights.release();
-    c->d_cull.release(); c->d_leaf_cull.release(); c->d_nodes.release(); c->d_nodef.release(); c->d_leaf_obj.release();
+    c->d_cull.release(); c->d_leaf_cull.release(); c->d_nodes.release(); c->d_leaf_obj.release();
     c->d_rays.release(); c->d_fb.release(); c->d_hit_id.release(); c->d_hit_t.release(); c->d_counters.release();
     c->d_sink.release();
     c->w_acc.release(); c->w_refl.release(); c->w_P.release(); c->w_Nm.release(); c->w_Rc.release(); c->w_out.release();

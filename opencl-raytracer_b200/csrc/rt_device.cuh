@@ -47,14 +47,13 @@ struct Scene {
     const float4* __restrict__ mat;    // M x 3: (ambient, absorption) (diffuse, shininess) (specular, 0)
     const CullRec* __restrict__ cull;  // M
     const BvhNode* __restrict__ nodes;
-    const BvhNodeF* __restrict__ nodef;
     const uint32_t* __restrict__ leaf_obj;  // object ids in leaf order
     const CullRec* __restrict__ leaf_cull;  // cull records in leaf order
     const Light* __restrict__ lights;
     uint32_t n_objs, n_lights, n_nodes, root_is_leaf;
     int32_t root;  // child-style reference to the root (leaf if negative)
     float filter_h;        // smallest h = 1 - g of the scene (brute-force filter folds it into per-ray constants)
-    float root_a, root_f;  // root_f: the scene-wide largest cone coefficient (wavefront traversal uses it for every node)
+    float root_a, root_f;  // root_f: the scene-wide largest noise coefficient (informational)
 };
 
 struct Ray {
@@ -277,23 +276,24 @@ __device__ __forceinline__ bool sphere_may_hit(const RayK& k, float cx, float cy
     return !(lhs > r2);
 }
 
-// Slab test of one child box (centre c, half extent e) against [0, tlimit], the box inflated by
-// pad + f * d_far  where d_far is the distance from the ray origin to the farthest point of the box: every
-// object centre of the subtree lies in the box, so |oc| <= d_far and f * d_far bounds the cone term of each
-// object (rt_scene.cpp).  The rounding of the slab arithmetic itself (relative, <= 4e-7 of d_far in space units)
-// is covered by kSlabRel added to f.  Returns the conservative entry parameter through tnear.
+// Slab test of one child box against [0, tlimit].  The box (centre c, half extent e) has to be inflated by
+// f * d_far, d_far = distance from the ray origin to the farthest point of the box: every object centre of the subtree
+// lies in the box, so |oc| <= d_far and f * d_far bounds the noise term of each object (rt_scene.cpp).  d_far is
+// bounded by its 1-norm  sum_k (|c_k - o_k| + e_k)  -- no square root -- whose static part f * sum(e) the scene builder
+// has already added to the stored half extent, together with the pad for the rounding of (c - o); the relative
+// rounding of the slab arithmetic itself (<= 4e-7 of d_far) is covered by RT_SLAB_REL, also already inside f.
+// 3 FADD + 2 FADD + FMUL (inflation), 3 FMUL + 3 FADD + 6 FFMA (slabs), 2 x 3-input min/max.
+// Returns the conservative entry parameter through tnear.
 #define RT_SLAB_REL 2e-6f
 __device__ __forceinline__ bool box_may_hit(float ox, float oy, float oz, float idx, float idy, float idz, float cx, float cy,
-                                            float cz, float ex, float ey, float ez, float pad, float f, float tlimit,
-                                            float& tnear) {
+                                            float cz, float ex, float ey, float ez, float f, float tlimit, float& tnear) {
     const float x = cx - ox, y = cy - oy, z = cz - oz;
-    const float mx = fabsf(x) + ex, my = fabsf(y) + ey, mz = fabsf(z) + ez;
-    const float dfar = sqrtf(fmaf(mz, mz, fmaf(my, my, mx * mx)));
-    const float infl = fmaf(f, dfar, pad);
+    const float infl = f * (fabsf(x) + fabsf(y) + fabsf(z));
     const float tx = x * idx, ty = y * idy, tz = z * idz;
-    const float rx = (ex + infl) * fabsf(idx), ry = (ey + infl) * fabsf(idy), rz = (ez + infl) * fabsf(idz);
-    const float tn = fmaxf(fmaxf(tx - rx, ty - ry), tz - rz);
-    const float tf = fminf(fminf(tx + rx, ty + ry), tz + rz);
+    const float Ex = ex + infl, Ey = ey + infl, Ez = ez + infl;
+    const float ax = fabsf(idx), ay = fabsf(idy), az = fabsf(idz);
+    const float tn = fmaxf(fmaxf(fmaf(-Ex, ax, tx), fmaf(-Ey, ay, ty)), fmaf(-Ez, az, tz));
+    const float tf = fminf(fminf(fmaf(Ex, ax, tx), fmaf(Ey, ay, ty)), fmaf(Ez, az, tz));
     tnear = tn;
     return !(tn > fminf(tf, tlimit)) && !(tf < 0.f);
 }
@@ -383,16 +383,15 @@ __device__ __forceinline__ Hit trace_bvh(const Scene& sc, const Ray& ray, float 
         if (cur >= 0) {
             const float4* np = reinterpret_cast<const float4*>(sc.nodes + cur);
             const float4 q0 = __ldg(np + 0), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
-            const float2 ff = __ldg(reinterpret_cast<const float2*>(sc.nodef + cur));
             ++nn;
             const int32_t c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
             const float tlimit = ANYHIT ? fminf(h.t, tcap) : h.t;
             float tn0, tn1;
             // child 0: ctr (q0.x q0.y q0.z) ext (q0.w q1.x q1.y); child 1: ctr (q1.z q1.w q2.x) ext (q2.y q2.z q2.w)
             const bool h0 = cv::box_may_hit(rk.ox, rk.oy, rk.oz, rk.idx, rk.idy, rk.idz, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q3.z,
-                                            ff.x * 1.00001f + RT_SLAB_REL, tlimit, tn0);
+                                            tlimit, tn0);
             const bool h1 = cv::box_may_hit(rk.ox, rk.oy, rk.oz, rk.idx, rk.idy, rk.idz, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, q3.w,
-                                            ff.y * 1.00001f + RT_SLAB_REL, tlimit, tn1);
+                                            tlimit, tn1);
             if (h0 && h1) {
                 const bool first0 = tn0 <= tn1;
                 cur = first0 ? c0 : c1;

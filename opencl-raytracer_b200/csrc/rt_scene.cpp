@@ -30,6 +30,14 @@ namespace {
 
 const double U = 5.9604644775390625e-08;  // 2^-24
 const double K_FUZZ = 32.0;
+// Boxes (and the triangle extension) decide hit / miss without a cancelling discriminant: their noise is LINEAR in the
+// distance.  The ray direction in object space carries a relative error <= 3 sqrt(3) u ratio (three products summed,
+// |A dir| >= |dir| / sigma_max), i.e. the object appears moved sideways by <= 5.2 u ratio^2 |oc| in view space; every
+// slab parameter t = (+-0.5 - s) / d carries <= 2u relative error (a face moved by <= 2u ratio |oc|); the triangle's
+// in-plane point s + t d <= 8u ratio |oc|.  Together <= 13.2 u ratio^2 |oc|; C_LIN = 24 leaves a factor 1.8.
+const double C_LIN = 24.0;
+// bounding-sphere filter for a linear-noise object:  (R + lin |oc|)^2 <= R^2 (1 + eps) + lin^2 (1 + 1/eps) |oc|^2
+const double LIN_EPS = 1.0 / 64.0;
 
 struct M3 {
     double a[3][3];
@@ -104,8 +112,8 @@ struct ObjBound {
     double c[3];     // centre
     double half[3];  // padded half extents of the AABB
     double R;        // padded bounding-sphere radius
-    double g;        // cone coefficient on |oc|^2
-    double f;        // sqrt(g)
+    double g;        // bounding-sphere filter: hit => p^2 <= R^2 + g |oc|^2
+    double f;        // boxes: hit => the ray passes within (half + f |oc|) of the centre per axis
 };
 
 struct BuildNode {
@@ -394,8 +402,17 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
             continue;
         }
         const double ratio = g.smax / g.smin;
-        const double gg = K_FUZZ * U * ratio * ratio + 24.0 * U;
-        if (gg > 0.25) {
+        // 24u: rounding of the filter's own arithmetic (h |oc|^2 - dt^2 in binary32)
+        double gg, ff, rscale = 1.0;
+        if (objs[i].type == 0u) {  // sphere: noisy discriminant, radius^2 grows by K u ratio^2 |oc|^2
+            gg = K_FUZZ * U * ratio * ratio + 24.0 * U;
+            ff = sqrt(gg);
+        } else {  // box / triangle: linear noise
+            ff = C_LIN * U * ratio * ratio;
+            gg = ff * ff * (1.0 + 1.0 / LIN_EPS) + 24.0 * U;
+            rscale = sqrt(1.0 + LIN_EPS);
+        }
+        if (gg > 0.25 || ff > 0.5) {
             err = "object " + std::to_string(i) + ": anisotropy too extreme for conservative bounds";
             return RT_ERR_UNSUPPORTED;
         }
@@ -408,9 +425,9 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
             b.c[a] = g.c[a];
             b.half[a] = g.ext[a] * (1.0 + 1e-6) + pad;
         }
-        b.R = g.R * (1.0 + 1e-6) + pad;
+        b.R = (g.R * (1.0 + 1e-6) + pad) * rscale;
         b.g = gg;
-        b.f = sqrt(gg);
+        b.f = ff;
         cr.cx = (float)g.c[0];
         cr.cy = (float)g.c[1];
         cr.cz = (float)g.c[2];
@@ -432,7 +449,6 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
         BvhNode n;
         memset(&n, 0, sizeof n);
         out.nodes.push_back(n);
-        out.nodef.push_back(BvhNodeF{0.f, 0.f});
         out.leaf_obj.push_back(0);
         CullRec dead;
         memset(&dead, 0, sizeof dead);
@@ -461,36 +477,41 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
     for (size_t i = 0; i < bld.bn.size(); ++i)
         if (bld.bn[i].left >= 0) inner_index[i] = n_inner++;
     out.nodes.resize(std::max(n_inner, 1));
-    out.nodef.resize(std::max(n_inner, 1));
     memset(out.nodes.data(), 0, out.nodes.size() * sizeof(BvhNode));
     auto ref_of = [&](int bi) -> int32_t {
         const BuildNode& n = bld.bn[bi];
         if (n.left >= 0) return inner_index[bi];
         return ~(int32_t)((n.first << 4) | (n.count - 1));
     };
-    auto child = [&](int bi, float* ctr, float* ext, float& a, float& f) {
+    auto child = [&](int bi, float* ctr, float* ext, float& f) {
         const BuildNode& n = bld.bn[bi];
         double rf2 = 0;
         for (int k = 0; k < 3; ++k) {
-            const double c = 0.5 * (n.lo[k] + n.hi[k]);
-            ctr[k] = (float)c;
-            // half extent measured from the ROUNDED centre, rounded up
-            ext[k] = up(std::max(n.hi[k] - (double)ctr[k], (double)ctr[k] - n.lo[k]));
             const double m = std::max(fabs(n.lo[k]), fabs(n.hi[k]));
             rf2 += m * m;
         }
-        const double rfar = sqrt(rf2);
-        f = up(n.f);
-        // slab arithmetic of cv::box_may_hit: (ctr - o) rounds with error <= u * max(|ctr|, |o|)
-        a = up(8.0 * U * (omax + rfar));
+        // slab arithmetic of cv::box_may_hit: (ctr - o) rounds with error <= u * max(|ctr|, |o|); folded into ext
+        const double a = 8.0 * U * (omax + sqrt(rf2));
+        // 1.00001: rounding of f * (|x| + |y| + |z|) on the device; RT_SLAB_REL (2e-6): relative rounding of the slab test
+        const double fd = n.f * 1.00001 + 2e-6;
+        f = up(fd);
+        double h[3], hsum = 0;
+        for (int k = 0; k < 3; ++k) {
+            const double c = 0.5 * (n.lo[k] + n.hi[k]);
+            ctr[k] = (float)c;
+            // half extent measured from the ROUNDED centre
+            h[k] = std::max(n.hi[k] - (double)ctr[k], (double)ctr[k] - n.lo[k]) + a;
+            hsum += h[k];
+        }
+        // static part of the inflation f * |farthest point - origin|_1 = f * sum(|c - o|) + f * sum(half extents)
+        for (int k = 0; k < 3; ++k) ext[k] = up(h[k] + (double)f * hsum * (1.0 + 1e-6));
     };
     for (size_t i = 0; i < bld.bn.size(); ++i) {
         const BuildNode& n = bld.bn[i];
         if (n.left < 0) continue;
         BvhNode& d = out.nodes[inner_index[i]];
-        BvhNodeF& df = out.nodef[inner_index[i]];
-        child(n.left, d.ctr0, d.ext0, d.a0, df.f0);
-        child(n.right, d.ctr1, d.ext1, d.a1, df.f1);
+        child(n.left, d.ctr0, d.ext0, d.f0);
+        child(n.right, d.ctr1, d.ext1, d.f1);
         d.c0 = ref_of(n.left);
         d.c1 = ref_of(n.right);
     }

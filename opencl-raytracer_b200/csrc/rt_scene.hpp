@@ -23,7 +23,6 @@ struct HostScene {
     std::vector<F4> mat;   // 3 per object
     std::vector<CullRec> cull;
     std::vector<BvhNode> nodes;
-    std::vector<BvhNodeF> nodef;
     std::vector<uint32_t> leaf_obj;
     std::vector<CullRec> leaf_cull;
     std::vector<F4> lights;  // 4 per light
@@ -33,7 +32,7 @@ struct HostScene {
     float scene_radius = 0.f;
     uint32_t bvh_depth = 0;
     float h_min = 1.f;     // smallest filter coefficient h = 1 - g over the live objects
-    float f_global = 0.f;  // largest cone coefficient of the scene (per-node values are in nodef)
+    float f_global = 0.f;  // largest noise coefficient of the scene (per-child values are in the nodes)
 };
 
 // Returns RT_OK or RT_ERR_UNSUPPORTED / RT_ERR_INVALID with a message in err.

@@ -117,21 +117,12 @@ __device__ __noinline__ void exact_pair_call(const Scene& sc, const float4 s, co
     exact_pair(sc, r, obj, type, best, btype);
 }
 
-// Bounding-sphere filter of one leaf object (the direct form of cv::sphere_may_hit).
-__device__ __forceinline__ bool leaf_filter(const Scene& sc, uint32_t slot, float ox, float oy, float oz, float ux, float uy, float uz) {
-    const float4 a = __ldg(reinterpret_cast<const float4*>(sc.leaf_cull) + 2 * (size_t)slot);
-    const float h = __ldg(&sc.leaf_cull[slot].h);
-    const float x = a.x - ox, y = a.y - oy, z = a.z - oz;
-    const float oc2 = fmaf(z, z, fmaf(y, y, x * x));
-    const float dt = fmaf(z, uz, fmaf(y, uy, x * ux));
-    return !(fmaf(-dt, dt, oc2 * h) > a.w);
-}
-
 // Persistent warps.  Every lane owns one ray of the queue and is in one of four states:
 //   T  traversing (stands on an inner node)           S  traversing, but its candidate buffer is nearly full
 //   F  traversal finished, candidates still queued    I  idle (no ray)
 // A node step tests the two child boxes; a child that is a leaf is not visited -- its objects go straight into
-// the lane's candidate buffer (shared memory) -- so the traversal loop consists of node steps only.  The warp
+// the lane's candidate buffer (shared memory), without a per-object filter: with the default one object per leaf
+// the child box IS the object's padded bounding box -- so the traversal loop consists of node steps only.  The warp
 // then schedules whole-warp rounds of the three activities so that each runs with most lanes taking part:
 //   node steps   while >= 20 lanes are in T (or nothing else is worth doing)
 //   exact tests  when >= 16 lanes have a candidate queued, a lane is in S, or nobody can traverse
@@ -151,7 +142,7 @@ __global__ void __launch_bounds__(kBlock, 3) wave_trace_bvh(const Scene sc, cons
 
     bool have = false, tdone = false, anyhit = false;
     uint32_t task = 0;
-    float ox = 0.f, oy = 0.f, oz = 0.f, idx = 0.f, idy = 0.f, idz = 0.f, ux = 0.f, uy = 0.f, uz = 0.f;
+    float ox = 0.f, oy = 0.f, oz = 0.f, idx = 0.f, idy = 0.f, idz = 0.f;
     Hit best;
     best.t = RT_MAX_FLOAT;
     best.id = -1;
@@ -160,7 +151,6 @@ __global__ void __launch_bounds__(kBlock, 3) wave_trace_bvh(const Scene sc, cons
     int sp = 0, npend = 0;
     int32_t stack[RT_BVH_STACK];
     bool exhausted = false;
-    const float fglob = sc.root_f * 1.00001f + RT_SLAB_REL;  // covers the approximate square root of d_far and the slab rounding
 
     for (;;) {
         // ---- refill
@@ -182,10 +172,6 @@ __global__ void __launch_bounds__(kBlock, 3) wave_trace_bvh(const Scene sc, cons
                         idx = fabsf(d.x) < 1e-30f ? copysignf(1e30f, d.x) : __fdividef(1.f, d.x);
                         idy = fabsf(d.y) < 1e-30f ? copysignf(1e30f, d.y) : __fdividef(1.f, d.y);
                         idz = fabsf(d.z) < 1e-30f ? copysignf(1e30f, d.z) : __fdividef(1.f, d.z);
-                        {  // unit direction for the bounding-sphere filter (correctly rounded: its error is in g)
-                            const float len = __fsqrt_rn(d.x * d.x + d.y * d.y + d.z * d.z);
-                            ux = __fdiv_rn(d.x, len); uy = __fdiv_rn(d.y, len); uz = __fdiv_rn(d.z, len);
-                        }
                         best.t = RT_MAX_FLOAT;
                         best.id = -1;
                         btype = 0;
@@ -227,8 +213,8 @@ __global__ void __launch_bounds__(kBlock, 3) wave_trace_bvh(const Scene sc, cons
                 const float tlimit = anyhit ? fminf(best.t, 1.f) : best.t;
                 float tn0, tn1;
                 // child 0: ctr (q0.x q0.y q0.z) ext (q0.w q1.x q1.y); child 1: ctr (q1.z q1.w q2.x) ext (q2.y q2.z q2.w)
-                bool h0 = cv::box_may_hit(ox, oy, oz, idx, idy, idz, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q3.z, fglob, tlimit, tn0);
-                bool h1 = cv::box_may_hit(ox, oy, oz, idx, idy, idz, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, q3.w, fglob, tlimit, tn1);
+                bool h0 = cv::box_may_hit(ox, oy, oz, idx, idy, idz, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q3.z, tlimit, tn0);
+                bool h1 = cv::box_may_hit(ox, oy, oz, idx, idy, idz, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, q3.w, tlimit, tn1);
                 const int32_t c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
                 if ((h0 && c0 < 0) || (h1 && c1 < 0)) {  // leaf children: their objects become candidates
 #pragma unroll 1
@@ -237,16 +223,15 @@ __global__ void __launch_bounds__(kBlock, 3) wave_trace_bvh(const Scene sc, cons
                         if (!(side ? h1 : h0) || c >= 0) continue;
                         const uint32_t code = (uint32_t)(~c);
                         const uint32_t first = code >> 4, cnt = (code & 15u) + 1u;
-                        for (uint32_t j = 0; j < cnt; ++j)
-                            if (leaf_filter(sc, first + j, ox, oy, oz, ux, uy, uz)) {
-                                if (npend < kPendCap) {
-                                    pend[npend++][tid] = first + j;
-                                } else {  // buffer full (leaves larger than the buffer): test in place
-                                    exact_pair_call(sc, q.s[task], q.d[task], __ldg(sc.leaf_obj + first + j),
-                                                    __ldg(&sc.leaf_cull[first + j].type), best, btype);
-                                    if (COUNT) lc.exact_tests++;
-                                }
+                        for (uint32_t j = 0; j < cnt; ++j) {
+                            if (npend < kPendCap) {
+                                pend[npend++][tid] = first + j;
+                            } else {  // buffer full (leaves larger than the buffer): test in place
+                                exact_pair_call(sc, q.s[task], q.d[task], __ldg(sc.leaf_obj + first + j),
+                                                __ldg(&sc.leaf_cull[first + j].type), best, btype);
+                                if (COUNT) lc.exact_tests++;
                             }
+                        }
                     }
                     h0 = h0 && c0 >= 0;
                     h1 = h1 && c1 >= 0;

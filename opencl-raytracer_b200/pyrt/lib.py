@@ -12,7 +12,8 @@ import numpy as np
 from .types import LIGHT_DTYPE, OBJECT_DTYPE, RAY_DTYPE
 
 _PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB_PATH = os.path.join(_PKG, "librt_b200.so")
+# RT_B200_LIB: an alternative build of the same library (kernel experiments); never a fallback
+LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_PKG, "librt_b200.so")
 
 OPT_PIPELINE, OPT_COUNT_RAYS, OPT_BVH_LEAF, OPT_SKIP_DEAD_RAYS = 1, 2, 3, 4
 

@@ -30,7 +30,6 @@ void bind(const rt::HostScene& hs, rt::Scene& s) {
     s.mat = reinterpret_cast<const float4*>(hs.mat.data());
     s.cull = hs.cull.data();
     s.nodes = hs.nodes.data();
-    s.nodef = hs.nodef.data();
     s.leaf_obj = hs.leaf_obj.data();
     s.leaf_cull = hs.leaf_cull.data();
     s.lights = reinterpret_cast<const rt::Light*>(hs.lights.data());
