@@ -38,7 +38,7 @@ from pyrt import scenes, types  # noqa: E402
 METRIC = "Mrays/s (primary+shadow+reflect)"
 
 # flops of the arithmetic each counted unit executes (DESIGN.md "Work per unit")
-FLOPS_FILTER = 14.0   # bounding-sphere filter, expanded form: 7 fma per (ray, object) pair (rt_wavefront.cu)
+FLOPS_FILTER = 14.0   # bounding-sphere filter, expanded form: 7 fma per (ray, object) pair = 3.5 FFMA2 (rt_wavefront.cu)
 FLOPS_EXACT = 78.0    # reference arithmetic of one ray x object test as written
 FLOPS_NODE = 62.0     # two inflated slab tests of one BVH node
 FLOPS_SHADE = 100.0   # Phong terms per (hit, light)
@@ -171,6 +171,7 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=0, help="side of the pixel lattice of the CPU sample (0 = auto)")
     ap.add_argument("--leaf", type=int, default=0, help="BVH leaf size (0 = library default)")
     ap.add_argument("--pipeline", type=int, default=-1, help="-1 auto, 0 megakernel, 1 wavefront")
+    ap.add_argument("--bands", type=int, default=0, help="readback bands of rt_render (0 = library default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-brute-leg", action="store_true")
     args = ap.parse_args()
@@ -195,7 +196,7 @@ def main():
         sample = "%dx%d pixel lattice of the frame (%d rays/step), %s, %d threads" % (side, side, nrays, build, cores)
         print(json.dumps({
             "impl": "reference", "metric": METRIC, "value": v, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": config,
             "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -224,6 +225,8 @@ def main():
         ctx.set_option(lib.OPT_BVH_LEAF, args.leaf)
     if args.pipeline >= 0:
         ctx.set_option(lib.OPT_PIPELINE, args.pipeline)
+    if args.bands:
+        ctx.set_option(lib.OPT_READBACK_BANDS, args.bands)
     t_up0 = time.perf_counter()
     ctx.upload_scene(objs, lights)
     ctx.set_camera(W, H, zdir)
@@ -301,9 +304,22 @@ def main():
 
     ms_e2e, _, _ = timed(step_e2e, args.steps, args.warmup)
     e2e_value = rays_traced / (ms_e2e * 1e-3) / 1e6
+    e2e_stats = ctx.stats()
+
+    # cold start, once: what `OpenCLRaytracer tracer(...); tracer.Render();` costs (OpenCLRaytracer.cpp:13-105) -- context,
+    # scene repack + BVH build on the host, H2D of the scene, first frame, readback
+    cold_ms = None
+    if rank == 0 and world == 1:
+        t0 = time.perf_counter()
+        with lib.Context(local_rank) as c4:
+            c4.upload_scene(objs, lights)
+            c4.set_camera(W, H, zdir)
+            c4.render(max_bounces, mode, args.accel, out=host.array)
+        cold_ms = (time.perf_counter() - t0) * 1e3
 
     # ------------------------------------------------------------------ roofline of the timed kernel
     peak_tf, peak_mhz = ctx.measure_fp32_peak()
+    peak_scalar, peak_packed = ctx.fp32_peak_detail()
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -322,7 +338,8 @@ def main():
     roofline = {
         "kernel": kernel_names[accel_used], "bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
         "frac": achieved_tf / peak_tf if peak_tf else None, "traffic": None,
-        "peak_source": "rt_measure_fp32_peak (register-only FFMA loop, this GPU, this run; implies %.0f MHz)" % peak_mhz,
+        "peak_source": "rt_measure_fp32_peak (register-only loops, this GPU, this run: scalar FFMA %.1f, packed FFMA2 %.1f TFLOP/s; "
+                       "the larger is the peak and implies %.0f MHz)" % (peak_scalar, peak_packed, peak_mhz),
         "flops_per_launch": flops / world,
         "hbm": {"framebuffer_bytes_per_launch": pixels * 16 / world, "achieved_gbs": pixels * 16 / world / (ms_dev * 1e-3) / 1e9,
                 "peak_gbs": peaks.get("hbm_gbs")},
@@ -374,6 +391,37 @@ def main():
         cpu = {"value": v, "unit": "Mrays/s", "cores": cores, "kind": kind,
                "sample": "%dx%d pixel lattice of the frame, %d reference rays, %.1f s, %s" % (side, side, nrays, ms / 1e3, build)}
 
+    # ------------------------------------------------------------------ the reference's own .cl on this GPU (rank 0, N = 1)
+    ref_ocl = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            import oracle
+
+            ok, info = oracle.ocl_probe()
+            if not ok:
+                ref_ocl = {"unavailable": info}
+            else:
+                # brute force over every object: a band of rows sized for about a second of kernel time
+                rows = H if len(objs) <= 48 else max(1, min(H, int(4.0e10 / (len(objs) * W * 7))))
+                r0 = H // 2 - rows // 2
+                band = types.camera_rays(W, H, zdir, rows=np.arange(r0, r0 + rows))
+                with lib.Context(local_rank) as c5:  # reference ray count of the band
+                    c5.upload_scene(objs, lights)
+                    c5.set_rays(band)
+                    c5.set_option(lib.OPT_COUNT_RAYS, 1)
+                    c5.set_option(lib.OPT_SKIP_DEAD_RAYS, 0)
+                    c5.render_device(max_bounces, mode, -1)
+                    nref = c5.stats().rays_reference
+                _, tm = oracle.ocl_render(mode if mode in (1, 2) else 2, max_bounces, objs, lights, band, frames=2)
+                ref_ocl = {"platform": info, "sample": "%d rows x %d px band at row %d" % (rows, W, r0), "reference_rays": nref,
+                           "kernel_ms": tm["kernel_ms"], "render_ms": tm["render_ms"], "jit_build_ms": tm["build_ms"],
+                           "mrays_per_s_kernel": nref / (tm["kernel_ms"] * 1e-3) / 1e6,
+                           "mrays_per_s_render": nref / (tm["render_ms"] * 1e-3) / 1e6,
+                           "note": "shade_and_reflect_kernel.cl unchanged, JIT-built by the box's OpenCL platform, local size 32 "
+                                   "(OpenCLRaytracer.cpp:80-105); counts every ray the reference traces"}
+        except Exception as e:  # baseline infrastructure must never take the bench line down
+            ref_ocl = {"unavailable": "error: %s" % e}
+
     if rank == 0:
         out = {
             "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -390,7 +438,10 @@ def main():
                      "mrays_reference_equivalent": rays_reference / (ms_dev * 1e-3) / 1e6},
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": 0,
                     "d2h_bytes_per_step": W * H * 16,
-                    "note": "rt_render == IRaytracer::Render(): launch + blocking readback; scene/camera resident as in the reference ctor"},
+                    "device_ms": {"kernels": e2e_stats.kernel_ms, "kernels_plus_copy": e2e_stats.total_ms},
+                    "ctor_plus_first_render_ms": cold_ms, "scene_h2d_bytes_once": int(len(objs)) * 276 + int(len(lights)) * 64,
+                    "note": "rt_render == IRaytracer::Render(): launch + blocking readback (bands of rows, copy overlapped with the next "
+                            "band's kernels); scene/camera resident as in the reference ctor, whose one-off cost is ctor_plus_first_render_ms"},
             "gpu_launches": args.steps * launches_per_step,
             "clocks": clocks,
             "roofline": roofline,
@@ -399,6 +450,8 @@ def main():
             out["roofline_brute"] = roofline_brute
         if cpu:
             out["cpu_baseline"] = cpu
+        if ref_ocl:
+            out["reference_opencl_gpu"] = ref_ocl
         print(json.dumps(out))
     if world > 1:
         if target:

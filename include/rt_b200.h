@@ -120,7 +120,9 @@ typedef enum rt_option {
     RT_OPT_PIPELINE = 1,   /* -1 auto, 0 megakernel, 1 wavefront */
     RT_OPT_COUNT_RAYS = 2, /* 1: fill the ray/test counters of rt_stats (small atomics cost) */
     RT_OPT_BVH_LEAF = 3,   /* max objects per BVH leaf (1..16) */
-    RT_OPT_SKIP_DEAD_RAYS = 4 /* 1 (default): do not trace rays whose result is dead; 0: trace every ray the reference traces */
+    RT_OPT_SKIP_DEAD_RAYS = 4, /* 1 (default): do not trace rays whose result is dead; 0: trace every ray the reference traces */
+    RT_OPT_READBACK_BANDS = 5  /* rt_render of a large whole frame: bands of rows whose readback overlaps the next band's kernels
+                                  (geometrically shrinking, default 2; 1 = render the frame, then copy it) */
 } rt_option;
 
 const char* rt_last_error(void);
@@ -186,6 +188,8 @@ int rt_host_free(void* p);
 
 /* Register-only FFMA loop: measured FP32 peak of this device in TFLOP/s (roofline denominator). */
 int rt_measure_fp32_peak(rt_ctx* ctx, float* tflops, float* sm_mhz_hint);
+/* The two loops of the last rt_measure_fp32_peak separately: scalar FFMA, packed FFMA2 (its result is their maximum). */
+int rt_fp32_peak_detail(rt_ctx* ctx, float* scalar_tflops, float* packed_tflops);
 
 #ifdef __cplusplus
 }

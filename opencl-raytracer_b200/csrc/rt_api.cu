@@ -60,8 +60,10 @@ struct DevBuf {
 
 struct rt_ctx {
     int device = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr, copy_stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
+    static const int kMaxBands = 16;
+    cudaEvent_t band_done[kMaxBands] = {};
 
     // host copy of the AoS scene (kept so that the bounds can be rebuilt when the ray-origin bound grows)
     std::vector<rt_object> objs;
@@ -99,9 +101,10 @@ struct rt_ctx {
     uint32_t last_launches = 1;
 
     // options
-    int opt_pipeline = -1, opt_count = 0, opt_leaf = 1, opt_skip_dead = 1;
+    int opt_pipeline = -1, opt_count = 0, opt_leaf = 1, opt_skip_dead = 1, opt_bands = 2;
 
     rt_stats stats;
+    float fp32_peak_tf[2] = {0.f, 0.f};  // last rt_measure_fp32_peak: scalar FFMA loop, packed FFMA2 loop
 };
 
 namespace {
@@ -180,17 +183,53 @@ int check_render_args(rt_ctx* c, int mode, int accel) {
 
 uint64_t n_pixels(const rt_ctx* c) { return c->use_camera ? (uint64_t)c->width * c->height : c->n_rays; }
 
-void fill_frame_desc(rt_ctx* c, rt::Frame& fr, uint32_t max_bounces, int mode, float4* out) {
+// band >= 0 (whole-frame camera renders only): the frame is cut into n_bands contiguous bands of rows so that the
+// readback of a finished band overlaps the next band's kernels.  Every band costs the pipeline its ramp-up and its
+// thin last generations again, and the copy is ~7x faster than the kernels of the same rows, so the bands shrink
+// geometrically (7 : 1 for two bands): only the last, small band's copy is left exposed.
+void band_range(const rt_ctx* c, int band, int n_bands, uint32_t* r0, uint32_t* r1) {
+    double total = 0.0, w = 1.0;
+    for (int i = 0; i < n_bands; ++i, w /= 7.0) total += w;
+    double acc = 0.0;
+    w = 1.0;
+    uint32_t start = 0, end = 0;
+    for (int i = 0; i <= band; ++i, w /= 7.0) {
+        start = end;
+        acc += w;
+        end = i == n_bands - 1 ? c->height : std::min(c->height, (uint32_t)(acc / total * c->height + 0.5));
+        if (end < start) end = start;
+    }
+    *r0 = start;
+    *r1 = end;
+}
+uint32_t band_rows(const rt_ctx* c, int n_bands) {  // rows of the largest band (the first)
+    uint32_t r0, r1;
+    band_range(c, 0, n_bands, &r0, &r1);
+    return r1 - r0;
+}
+
+void fill_frame_desc(rt_ctx* c, rt::Frame& fr, uint32_t max_bounces, int mode, float4* out, int band = -1, int n_bands = 1) {
     memset(&fr, 0, sizeof fr);
     fr.rays = c->use_camera ? nullptr : c->d_rays.p;
     fr.width = c->width;
     fr.height = c->height;
     fr.zdir = c->zdir;
-    fr.block_rows = c->use_camera ? c->block_rows : 1;
-    fr.shard = c->use_camera ? c->shard : 0;
-    fr.n_shards = c->use_camera ? c->n_shards : 1;
-    fr.local_rows = shard_local_rows(c);
-    fr.n_local = c->use_camera ? (uint64_t)shard_rows(c) * c->width : c->n_rays;
+    if (band >= 0) {
+        uint32_t r0, r1;
+        band_range(c, band, n_bands, &r0, &r1);
+        fr.block_rows = std::max(r1 - r0, 1u);
+        fr.shard = 0;
+        fr.n_shards = 1;
+        fr.row0 = r0;
+        fr.local_rows = r1 - r0;
+        fr.n_local = (uint64_t)(r1 - r0) * c->width;
+    } else {
+        fr.block_rows = c->use_camera ? c->block_rows : 1;
+        fr.shard = c->use_camera ? c->shard : 0;
+        fr.n_shards = c->use_camera ? c->n_shards : 1;
+        fr.local_rows = shard_local_rows(c);
+        fr.n_local = c->use_camera ? (uint64_t)shard_rows(c) * c->width : c->n_rays;
+    }
     fr.max_bounces = max_bounces;
     fr.mode = mode;
     fr.skip_dead = c->opt_skip_dead;
@@ -266,31 +305,44 @@ int ensure_wave_buffers(rt_ctx* c, uint64_t capacity, uint32_t gens, rt::WaveBuf
 }
 
 // kernels of one render on c->stream, bracketed by ev0/ev1
-int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float4* out, int* accel_used, bool aov_only = false) {
+int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float4* out, int* accel_used, bool aov_only = false,
+                     int band = -1, int n_bands = 1) {
     int rc = sync_scene(c);
     if (rc != RT_OK) return rc;
     accel = pick_accel(c, accel);
     *accel_used = accel;
     rt::Frame fr;
-    fill_frame_desc(c, fr, max_bounces, mode, out);
+    fill_frame_desc(c, fr, max_bounces, mode, out, band, n_bands);
     if (aov_only) {
         fr.hit_id = c->d_hit_id.p;
         fr.hit_t = c->d_hit_t.p;
     }
     if (c->opt_count) {
         RT_CUDA(c->d_counters.ensure(1));
-        RT_CUDA(cudaMemsetAsync(c->d_counters.p, 0, sizeof(rt::Counters), c->stream));
+        if (band <= 0) RT_CUDA(cudaMemsetAsync(c->d_counters.p, 0, sizeof(rt::Counters), c->stream));
         fr.counters = c->d_counters.p;
     }
     const int pipeline = pick_pipeline(c, accel);
     c->last_pipeline = pipeline;
-    c->last_launches = 1;
+    if (band <= 0) c->last_launches = 0;
+    if (band > 0) {  // later bands of a banded render: kernels only, ev0 stays at the start of band 0
+        if (fr.n_local == 0) return RT_OK;
+        uint32_t gens = rt::wave_max_generations(max_bounces, c->scene.n_lights, mode);
+        rt::WaveBuffers wb;
+        rc = ensure_wave_buffers(c, (uint64_t)band_rows(c, n_bands) * c->width, gens, wb);
+        if (rc != RT_OK) return rc;
+        uint32_t nl = 0;
+        RT_CUDA(rt::wave_render(c->scene, fr, wb, accel, (uint32_t)c->opt_leaf, c->sm_count, &nl, c->stream));
+        c->last_launches += nl;
+        RT_CUDA(cudaEventRecord(c->ev1, c->stream));
+        return RT_OK;
+    }
     if (pipeline == 1 && fr.n_local > 0) {
         uint32_t gens = rt::wave_max_generations(max_bounces, c->scene.n_lights, mode);
         if (gens > 4096) return fail(RT_ERR_INVALID, "max_bounces x lights too large for the wavefront pipeline; use RT_OPT_PIPELINE 0");
         rt::WaveBuffers wb;
         // camera tiles may include a ragged edge; capacity counts real pixels only
-        rc = ensure_wave_buffers(c, fr.n_local, gens, wb);
+        rc = ensure_wave_buffers(c, band == 0 ? (uint64_t)band_rows(c, n_bands) * c->width : fr.n_local, gens, wb);
         if (rc != RT_OK) return rc;
         RT_CUDA(cudaEventRecord(c->ev0, c->stream));
         uint32_t nl = 0;
@@ -299,6 +351,7 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
         RT_CUDA(cudaEventRecord(c->ev1, c->stream));
         return RT_OK;
     }
+    c->last_launches = 1;
     RT_CUDA(cudaEventRecord(c->ev0, c->stream));
     RT_CUDA(rt::launch_megakernel(c->scene, fr, accel, aov_only, c->stream));
     RT_CUDA(cudaEventRecord(c->ev1, c->stream));
@@ -333,7 +386,10 @@ int rt_create(rt_ctx** out, int device) {
     c->sm_count = prop.multiProcessorCount;
     memset(&c->stats, 0, sizeof c->stats);
     memset(&c->scene, 0, sizeof c->scene);
-    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&c->ev0) != cudaSuccess ||
+    bool bands_ok = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) == cudaSuccess;
+    for (int i = 0; i < rt_ctx::kMaxBands && bands_ok; ++i)
+        bands_ok = cudaEventCreateWithFlags(&c->band_done[i], cudaEventDisableTiming) == cudaSuccess;
+    if (!bands_ok || cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&c->ev0) != cudaSuccess ||
         cudaEventCreate(&c->ev1) != cudaSuccess || cudaEventCreate(&c->ev2) != cudaSuccess) {
         delete c;
         return fail(RT_ERR_CUDA, "stream/event creation failed");
@@ -356,6 +412,9 @@ int rt_destroy(rt_ctx* c) {
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->ev2) cudaEventDestroy(c->ev2);
+    for (int i = 0; i < rt_ctx::kMaxBands; ++i)
+        if (c->band_done[i]) cudaEventDestroy(c->band_done[i]);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
     return RT_OK;
@@ -372,6 +431,10 @@ int rt_set_option(rt_ctx* c, int option, int64_t value) {
             c->scene_dirty = true;
             return RT_OK;
         case RT_OPT_SKIP_DEAD_RAYS: c->opt_skip_dead = value ? 1 : 0; return RT_OK;
+        case RT_OPT_READBACK_BANDS:
+            if (value < 1 || value > rt_ctx::kMaxBands) return fail(RT_ERR_INVALID, "readback bands must be 1..16");
+            c->opt_bands = (int)value;
+            return RT_OK;
         default: return fail(RT_ERR_INVALID, "unknown option");
     }
 }
@@ -458,6 +521,36 @@ int rt_render(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float* host_
     if (!host_out) return fail(RT_ERR_INVALID, "null output buffer");
     RT_CUDA(cudaSetDevice(c->device));
     int used = 0;
+    // Whole-frame camera renders on the wavefront pipeline are cut into bands of rows: the device->host copy of a
+    // finished band (copy stream) overlaps the kernels of the next one (compute stream).
+    const bool banded = c->use_camera && c->n_shards == 1 && c->opt_bands > 1 && (uint64_t)c->width * c->height >= (1ull << 22) &&
+                        c->height >= (uint32_t)c->opt_bands && c->have_scene && pick_pipeline(c, pick_accel(c, accel)) == 1;
+    if (banded) {
+        const int nb = c->opt_bands;
+        for (int b = 0; b < nb; ++b) {
+            rc = render_on_device(c, max_bounces, mode, accel, c->d_fb.p, &used, false, b, nb);
+            if (rc != RT_OK) return rc;
+            uint32_t r0, r1;
+            band_range(c, b, nb, &r0, &r1);
+            if (r1 == r0) continue;
+            RT_CUDA(cudaEventRecord(c->band_done[b], c->stream));
+            RT_CUDA(cudaStreamWaitEvent(c->copy_stream, c->band_done[b], 0));
+            const uint64_t first = (uint64_t)r0 * c->width, cnt = (uint64_t)(r1 - r0) * c->width;
+            RT_CUDA(cudaMemcpyAsync(host_out + 4 * first, c->d_fb.p + first, cnt * sizeof(float4), cudaMemcpyDeviceToHost, c->copy_stream));
+        }
+        RT_CUDA(cudaEventRecord(c->band_done[0], c->copy_stream));
+        RT_CUDA(cudaStreamWaitEvent(c->stream, c->band_done[0], 0));  // ev2 on the compute stream, after the last copy
+        RT_CUDA(cudaEventRecord(c->ev2, c->stream));
+        RT_CUDA(cudaStreamSynchronize(c->stream));
+        rc = collect_stats(c, used, n_pixels(c), 1);
+        if (rc != RT_OK) return rc;
+        float ms = 0.f, ms2 = 0.f;
+        RT_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+        RT_CUDA(cudaEventElapsedTime(&ms2, c->ev0, c->ev2));
+        c->stats.kernel_ms = ms;  // kernels of all bands (copies of earlier bands run underneath)
+        c->stats.total_ms = ms2;
+        return RT_OK;
+    }
     rc = render_on_device(c, max_bounces, mode, accel, c->d_fb.p, &used);
     if (rc != RT_OK) return rc;
     // readback: the shard's row-blocks (or everything)
@@ -620,18 +713,31 @@ int rt_measure_fp32_peak(rt_ctx* c, float* tflops, float* sm_mhz_hint) {
     RT_CUDA(c->d_sink.ensure(1));
     const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 4096;
     float best = 0.f;
-    for (int rep = 0; rep < 5; ++rep) {
-        RT_CUDA(cudaEventRecord(c->ev0, c->stream));
-        RT_CUDA(rt::launch_fp32_peak(c->d_sink.p, iters, blocks, threads, c->stream));
-        RT_CUDA(cudaEventRecord(c->ev1, c->stream));
-        RT_CUDA(cudaStreamSynchronize(c->stream));
-        float ms = 0.f;
-        RT_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
-        const double flops = 2.0 * 8.0 * 16.0 * (double)iters * (double)blocks * threads;
-        if (rep > 0 && ms > 0.f) best = std::max(best, (float)(flops / (ms * 1e-3) / 1e12));
+    // scalar FFMA and packed FFMA2 loops; the denominator is whichever the device runs faster
+    for (int packed = 0; packed < 2; ++packed) {
+        float b = 0.f;
+        for (int rep = 0; rep < 5; ++rep) {
+            RT_CUDA(cudaEventRecord(c->ev0, c->stream));
+            RT_CUDA(rt::launch_fp32_peak(c->d_sink.p, iters, blocks, threads, packed != 0, c->stream));
+            RT_CUDA(cudaEventRecord(c->ev1, c->stream));
+            RT_CUDA(cudaStreamSynchronize(c->stream));
+            float ms = 0.f;
+            RT_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+            const double flops = (packed ? 4.0 : 2.0) * 8.0 * 16.0 * (double)iters * (double)blocks * threads;
+            if (rep > 0 && ms > 0.f) b = std::max(b, (float)(flops / (ms * 1e-3) / 1e12));
+        }
+        c->fp32_peak_tf[packed] = b;
+        best = std::max(best, b);
     }
     *tflops = best;
     if (sm_mhz_hint) *sm_mhz_hint = best > 0.f ? (float)(best * 1e12 / (2.0 * 128.0 * prop.multiProcessorCount) / 1e6) : 0.f;
+    return RT_OK;
+}
+
+int rt_fp32_peak_detail(rt_ctx* c, float* scalar_tflops, float* packed_tflops) {
+    if (!c || !scalar_tflops || !packed_tflops) return fail(RT_ERR_INVALID, "null argument");
+    *scalar_tflops = c->fp32_peak_tf[0];
+    *packed_tflops = c->fp32_peak_tf[1];
     return RT_OK;
 }
 

@@ -49,7 +49,7 @@ __device__ __forceinline__ bool locate_pixel(const Frame& fr, uint32_t& ii, uint
     const uint32_t ly = ty * kTileH + (warp >> 2) * 4u + (lane >> 3);
     if (lx >= fr.width || ly >= fr.local_rows) return false;
     const uint32_t blk = ly / fr.block_rows, rib = ly % fr.block_rows;
-    const uint32_t row = (blk * fr.n_shards + fr.shard) * fr.block_rows + rib;
+    const uint32_t row = fr.row0 + (blk * fr.n_shards + fr.shard) * fr.block_rows + rib;
     if (row >= fr.height) return false;
     ii = lx;
     jj = row;
@@ -130,6 +130,22 @@ __global__ void __launch_bounds__(256) fp32_peak(float* sink, const int iters) {
     if (s == 123.456f) sink[0] = s;  // never true; keeps the loop alive
 }
 
+// The same with the sm_100 packed form: 8 independent chains of FFMA2 (two IEEE fmas per instruction), 4 flops each.
+__global__ void __launch_bounds__(256) fp32_peak_packed(float* sink, const int iters) {
+    float2 a0 = make_float2(threadIdx.x * 1e-3f, 0.5f), a1 = a0, a2 = a0, a3 = a0, a4 = a0, a5 = a0, a6 = a0, a7 = a0;
+    a1.x += 1.f; a2.x += 2.f; a3.x += 3.f; a4.x += 4.f; a5.x += 5.f; a6.x += 6.f; a7.x += 7.f;
+    const float2 m = make_float2(0.999f + blockIdx.x * 1e-9f, 0.998f), c = make_float2(1e-3f, 2e-3f);
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+            a0 = __ffma2_rn(a0, m, c); a1 = __ffma2_rn(a1, m, c); a2 = __ffma2_rn(a2, m, c); a3 = __ffma2_rn(a3, m, c);
+            a4 = __ffma2_rn(a4, m, c); a5 = __ffma2_rn(a5, m, c); a6 = __ffma2_rn(a6, m, c); a7 = __ffma2_rn(a7, m, c);
+        }
+    }
+    const float s = a0.x + a1.x + a2.x + a3.x + a4.x + a5.x + a6.x + a7.x + a0.y + a1.y + a2.y + a3.y + a4.y + a5.y + a6.y + a7.y;
+    if (s == 123.456f) sink[0] = s;
+}
+
 template <int ACCEL>
 cudaError_t launch_mega_t(const Scene& sc, const Frame& fr, bool aov_only, cudaStream_t stream) {
     unsigned grid;
@@ -190,8 +206,11 @@ cudaError_t launch_fill(float4* out, uint64_t n, cudaStream_t stream) {
     return cudaGetLastError();
 }
 
-cudaError_t launch_fp32_peak(float* sink, int iters, int blocks, int threads, cudaStream_t stream) {
-    fp32_peak<<<blocks, threads, 0, stream>>>(sink, iters);
+cudaError_t launch_fp32_peak(float* sink, int iters, int blocks, int threads, bool packed, cudaStream_t stream) {
+    if (packed)
+        fp32_peak_packed<<<blocks, threads, 0, stream>>>(sink, iters);
+    else
+        fp32_peak<<<blocks, threads, 0, stream>>>(sink, iters);
     return cudaGetLastError();
 }
 

@@ -26,6 +26,7 @@ struct Frame {
     float zdir;
     // shard: row-blocks of block_rows rows dealt round-robin; this context owns b % n_shards == shard
     uint32_t block_rows, shard, n_shards;
+    uint32_t row0;            // added to every row (a band of a banded whole-frame render; 0 otherwise)
     uint32_t local_rows;      // rows of this shard (camera) -- local image is width x local_rows
     uint64_t n_local;         // pixels / rays handled by this launch
     uint32_t max_bounces;
@@ -44,6 +45,6 @@ cudaError_t launch_trace(const Scene& sc, const Ray* rays, uint64_t n, int accel
 cudaError_t launch_quantize(const float4* rgba, uint64_t n, int32_t* rgb, cudaStream_t stream);
 cudaError_t launch_fill(float4* out, uint64_t n, cudaStream_t stream);
 // register-only FFMA loop; returns flops executed through *flops, kernel on `stream`
-cudaError_t launch_fp32_peak(float* sink, int iters, int blocks, int threads, cudaStream_t stream);
+cudaError_t launch_fp32_peak(float* sink, int iters, int blocks, int threads, bool packed, cudaStream_t stream);
 
 }  // namespace rt

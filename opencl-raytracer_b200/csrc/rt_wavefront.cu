@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(kBlock) wave_gen(const Frame fr, const TaskQue
         active = lx < fr.width && ly < fr.local_rows;
         if (active) {
             const uint32_t blk = ly / fr.block_rows, rib = ly % fr.block_rows;
-            const uint32_t row = (blk * fr.n_shards + fr.shard) * fr.block_rows + rib;
+            const uint32_t row = fr.row0 + (blk * fr.n_shards + fr.shard) * fr.block_rows + rib;
             active = row < fr.height;
             if (active) {
                 oi = (uint64_t)row * fr.width + lx;
@@ -124,9 +124,10 @@ __device__ __noinline__ void exact_pair_call(const Scene& sc, const float4 s, co
 // the lane's candidate buffer (shared memory), without a per-object filter: with the default one object per leaf
 // the child box IS the object's padded bounding box -- so the traversal loop consists of node steps only.  The warp
 // then schedules whole-warp rounds of the three activities so that each runs with most lanes taking part:
-//   node steps   while >= 20 lanes are in T (or nothing else is worth doing)
-//   exact tests  when >= 16 lanes have a candidate queued, a lane is in S, or nobody can traverse
-//   refill       when >= 8 lanes are idle (or nobody is traversing) and the queue is not exhausted
+//   node steps   while >= 16 lanes are in T (or nothing else is worth doing)
+//   exact tests  when >= 8 lanes have a candidate queued or nobody can traverse
+//   refill       when >= 12 lanes are idle (or nobody is traversing) and the queue is not exhausted
+// (thresholds swept on the B200 with tools/sweep_sched.sh; RT_WAVE_MIN_T / _DRAIN / _REFILL override them)
 // Deferring exact tests never changes the result: every queued candidate is tested before its ray retires, and
 // pruning against the best t found so far only ever skips nodes that cannot contain a better hit.
 template <bool COUNT>
@@ -301,104 +302,219 @@ __global__ void __launch_bounds__(kBlock) wave_trace_brute(const Scene sc, const
 }
 
 // N-body layout: RPT rays per thread in registers, the filter records of a tile of objects in shared memory
-// (every lane of a warp reads the same 16-byte record: one broadcast LDS.128 per object), survivors run the
-// exact test.
+// (every lane of a warp reads the same record: broadcast LDS.128), survivors run the exact test.
 //
 // The bounding-sphere filter  h*|c-o|^2 - ((c-o).u)^2 > r2  (reject) is evaluated in expanded form with the
 // scene-wide smallest h (conservative: a smaller h only lets more pairs through) folded into per-ray constants:
-//     dt   = c.u - o.u                          3 FFMA      (o.u per ray)
-//     w    = h*|o|^2 - 2h c.o                   3 FFMA      (h*|o|^2 and -2h*o per ray)
-//     lhs2 = w - dt*dt                          1 FFMA
-//     reject iff lhs2 > e,  e = r2 - h*|c|^2    1 FSETP     (e per object, computed when the tile is staged)
-// 7 FFMA + 1 compare per pair.  The expanded form cancels when |c|, |o| >> |c-o|; its rounding error is below
-// 44 u (|c|^2 + |o|^2), which is added to the accept side (kExpandPad on e per object and on |o|^2 per ray).
-constexpr int kFilterTile = 2048;          // objects per tile (32 KB of shared memory)
+//     dt = c.u - o.u                            3 FMA      (o.u per ray)
+//     w  = 2h c.o - h*|o|^2                     3 FMA      (h*|o|^2 and 2h*o per ray)
+//     l  = dt*dt + w                            1 FMA
+//     reject iff l < e',  e' = h*|c|^2 - r2     (e' per object, computed when the tile is staged)
+// The expanded form cancels when |c|, |o| >> |c-o|; its rounding error is below 44 u (|c|^2 + |o|^2), which is added
+// to the accept side (kExpandPad on e' per object and on |o|^2 per ray).
+//
+// sm_100a packed arithmetic: two rays share one 64-bit register pair and every FMA above is one FFMA2
+// (__ffma2_rn, two IEEE fmas per issue slot), so 8 rays x 1 object cost 28 FFMA2 = 56 FMA-pipe cycles but only 28
+// issue slots; the tile stores every value twice ({cx,cx,cy,cy} {cz,cz,e',e'}) so that the broadcast operand arrives
+// as an aligned pair.  "Does any of my rays pass" is a 3-input max tree over the eight l values and ONE compare, the
+// warp then votes; the per-ray compares run only on the rare slow path.
+//
+// Survivors (about 1e-4 of the pairs) do not run the exact test where they are found -- that would be ~400
+// instructions with one or two lanes active -- but are appended to a per-warp list in shared memory; whenever the
+// list holds 32 entries the warp runs 32 exact tests at once, one per lane, and every owner lane then merges the
+// results of its own rays (ex::replaces is order independent, so the merge order does not matter).
 constexpr float kExpandPad = 4.7684e-06f;  // 80 u
 
-__device__ __noinline__ void filter_exact(const Scene& sc, const TaskQueue& q, uint32_t ray_idx, uint32_t obj, float* bt, int32_t* bi) {
-    Hit best;
-    best.t = *bt;
-    best.id = *bi;
-    uint32_t btype = best.id >= 0 ? __ldg(&sc.cull[best.id].type) : 0u;
-    Ray r;
-    r.s = q.s[ray_idx];
-    r.d = q.d[ray_idx];
-    exact_pair(sc, r, obj, __ldg(&sc.cull[obj].type), best, btype);
-    *bt = best.t;
-    *bi = best.id;
+template <int CAP>     // CAP: per warp, 31 left over + (rays per thread x 32 lanes) of one object
+struct FilterShared {  // static part; the tile is dynamic shared memory
+    uint32_t cand_obj[kBlock / 32][CAP];
+    uint16_t cand_who[kBlock / 32][CAP];  // (owner lane << 3) | ray slot
+    float res_t[kBlock / 32][32];              // results of one batch of exact tests (< 0: no candidate)
+    uint32_t res_type[kBlock / 32][32];
+    uint32_t cand_n[kBlock / 32];
+};
+
+// One batch: lanes [0, k) each run the exact arithmetic of one listed (ray, object) pair, then every lane merges the
+// results that belong to its rays into best_t / best_i.  Whole warp, converged.
+template <int RPT, int CAP>
+__device__ __noinline__ void filter_flush(const Scene& sc, const TaskQueue& q, FilterShared<CAP>& fs, float (*best_t)[kBlock],
+                                          int32_t (*best_i)[kBlock], uint32_t warp_base, uint32_t first, uint32_t k) {
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, tid = threadIdx.x;
+    uint32_t obj = 0;
+    if (lane < k) {
+        obj = fs.cand_obj[warp][first + lane];
+        const uint32_t who = fs.cand_who[warp][first + lane];
+        const uint32_t i = warp_base + (who >> 3) + (who & 7u) * kBlock;
+        const uint32_t type = __ldg(&sc.cull[obj].type);
+        const float4* mi = sc.minv + 4 * (size_t)obj;
+        const float4 c0 = __ldg(mi + 0), c1 = __ldg(mi + 1), c2 = __ldg(mi + 2), c3 = __ldg(mi + 3);
+        const float4 s = ex::xform(c0, c1, c2, c3, q.s[i]);
+        const float4 d = ex::xform(c0, c1, c2, c3, q.d[i]);
+        float t = 0.f;
+        const bool hit = ex::candidate(type, s, d, t);
+        fs.res_t[warp][lane] = hit ? t : -1.f;  // candidates have t >= 0 (or NaN: ex::replaces treats it like the kernels do)
+        fs.res_type[warp][lane] = type;
+    }
+    __syncwarp();
+    for (uint32_t e = 0; e < k; ++e) {
+        const uint32_t who = fs.cand_who[warp][first + e];
+        if ((who >> 3) == lane) {
+            const float tc = fs.res_t[warp][e];
+            if (!(tc < 0.f)) {
+                const uint32_t r = who & 7u;
+                const int32_t c = (int32_t)fs.cand_obj[warp][first + e];
+                const int32_t kcur = best_i[r][tid];
+                const uint32_t type_k = kcur >= 0 ? __ldg(&sc.cull[kcur].type) : 0u;
+                if (ex::replaces(tc, c, fs.res_type[warp][e], best_t[r][tid], kcur, type_k)) {
+                    best_t[r][tid] = tc;
+                    best_i[r][tid] = c;
+                }
+            }
+        }
+    }
+    __syncwarp();
 }
 
-template <int RPT, bool COUNT>
-__global__ void __launch_bounds__(kBlock, 2) wave_trace_filter(const Scene sc, const TaskQueue q, const uint32_t* __restrict__ n_ptr,
-                                                               const uint32_t n_min, const uint32_t n_max, float* __restrict__ res_t,
-                                                               int32_t* __restrict__ res_id, Counters* ctr) {
+// RPT rays per thread (even), OPI objects per loop iteration (independent FMA chains for latency hiding), MINB resident
+// blocks per SM, TILE objects per shared-memory tile.
+template <int RPT, int OPI, int MINB, int TILE, bool COUNT>
+__global__ void __launch_bounds__(kBlock, MINB) wave_trace_filter(const Scene sc, const TaskQueue q, const uint32_t* __restrict__ n_ptr,
+                                                                  const uint32_t n_min, const uint32_t n_max, float* __restrict__ res_t,
+                                                                  int32_t* __restrict__ res_id, Counters* ctr) {
+    static_assert(RPT % 2 == 0 && RPT <= 8, "rays come in pairs; the ray slot is packed into 3 bits");
+    static_assert(TILE % OPI == 0, "tile is a whole number of iterations");
+    constexpr int P = RPT / 2;
+    constexpr int CAP = 32 + RPT * 32;  // 31 left over + every ray of the warp on one object
     const uint32_t n = *n_ptr;
     if (n == 0u || n < n_min || n >= n_max) return;  // the other instantiation handles this queue size
-    __shared__ float4 tile[kFilterTile];             // cx, cy, cz, e
+    extern __shared__ float4 tile[];                 // 2 per object: {cx, cx, cy, cy} {cz, cz, e', e'}
     __shared__ float best_t[RPT][kBlock];
     __shared__ int32_t best_i[RPT][kBlock];
+    __shared__ FilterShared<CAP> fs;
     LocalCounters lc;
     const uint32_t M = sc.n_objs;
     const float hmin = sc.filter_h;
     const float4* cull4 = reinterpret_cast<const float4*>(sc.cull);
     const uint32_t per_block = kBlock * RPT;
     const uint32_t n_groups = (n + per_block - 1) / per_block;
-    const uint32_t tid = threadIdx.x;
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const float inf = __int_as_float(0x7f800000);
 
     for (uint32_t g = blockIdx.x; g < n_groups; g += gridDim.x) {
-        float ux[RPT], uy[RPT], uz[RPT], px[RPT], py[RPT], pz[RPT], nq[RPT], oo[RPT];
+        float2 UX[P], UY[P], UZ[P], NQ[P], PX[P], PY[P], PZ[P], OO[P];
         const uint32_t base = g * per_block + tid;  // ray r of this thread: base + r * kBlock (coalesced loads)
+        const uint32_t warp_base = g * per_block + warp * 32u;
+        if (lane == 0) fs.cand_n[warp] = 0u;
 #pragma unroll
         for (int r = 0; r < RPT; ++r) {
             const uint32_t i = base + r * kBlock;
             best_t[r][tid] = RT_MAX_FLOAT;
             best_i[r][tid] = -1;
+            float ux = 0.f, uy = 0.f, uz = 0.f, nq = 0.f, px = 0.f, py = 0.f, pz = 0.f, oo = -inf;  // padding: never passes
             if (i < n) {
                 Ray ry;
                 ry.s = q.s[i];
                 ry.d = q.d[i];
                 const cv::RayK rk = cv::prepare(ry);
-                ux[r] = rk.ux; uy[r] = rk.uy; uz[r] = rk.uz;
-                px[r] = -2.f * hmin * rk.ox; py[r] = -2.f * hmin * rk.oy; pz[r] = -2.f * hmin * rk.oz;
-                nq[r] = -(rk.ox * rk.ux + rk.oy * rk.uy + rk.oz * rk.uz);
+                ux = rk.ux; uy = rk.uy; uz = rk.uz;
+                px = 2.f * hmin * rk.ox; py = 2.f * hmin * rk.oy; pz = 2.f * hmin * rk.oz;
+                nq = -(rk.ox * rk.ux + rk.oy * rk.uy + rk.oz * rk.uz);
                 const float o2 = rk.ox * rk.ox + rk.oy * rk.oy + rk.oz * rk.oz;
-                oo[r] = hmin * (o2 - 2.f * kExpandPad * o2);
-            } else {  // padding: everything 0 -> lhs2 = 0, rejected unless the object contains the origin
-                ux[r] = uy[r] = uz[r] = px[r] = py[r] = pz[r] = nq[r] = oo[r] = 0.f;
+                oo = -(hmin * (o2 - 2.f * kExpandPad * o2));
+                // a degenerate ray (zero or non-finite direction / origin) must reach the exact test on every object,
+                // as a NaN did in the compare form  !(lhs > e):  l = +inf passes every e'
+                const float chk = ux + uy + uz + nq + px + py + pz + oo;
+                if (!(fabsf(chk) < inf)) {
+                    ux = uy = uz = nq = px = py = pz = 0.f;
+                    oo = inf;
+                }
+            }
+            if (r & 1) {
+                UX[r / 2].y = ux; UY[r / 2].y = uy; UZ[r / 2].y = uz; NQ[r / 2].y = nq;
+                PX[r / 2].y = px; PY[r / 2].y = py; PZ[r / 2].y = pz; OO[r / 2].y = oo;
+            } else {
+                UX[r / 2].x = ux; UY[r / 2].x = uy; UZ[r / 2].x = uz; NQ[r / 2].x = nq;
+                PX[r / 2].x = px; PY[r / 2].x = py; PZ[r / 2].x = pz; OO[r / 2].x = oo;
             }
         }
-        for (uint32_t t0 = 0; t0 < M; t0 += kFilterTile) {
-            const uint32_t cnt = min((uint32_t)kFilterTile, M - t0);
+        for (uint32_t t0 = 0; t0 < M; t0 += TILE) {
+            const uint32_t cnt = min((uint32_t)TILE, M - t0);
+            const uint32_t cnt_pad = (cnt + OPI - 1) / OPI * OPI;
             __syncthreads();
-            for (uint32_t j = tid; j < cnt; j += kBlock) {
-                const float4 a = __ldg(cull4 + 2 * (size_t)(t0 + j));       // cx cy cz r2
-                const float4 b = __ldg(cull4 + 2 * (size_t)(t0 + j) + 1);   // h cc e0 type
-                // r2 < 0 marks "never hit": e = -inf rejects every finite lhs2
-                const float e = a.w < 0.f ? -__int_as_float(0x7f800000) : fmaf(-hmin, b.y, fmaf(kExpandPad, b.y, a.w));
-                tile[j] = make_float4(a.x, a.y, a.z, e);
+            for (uint32_t j = tid; j < cnt_pad; j += kBlock) {
+                float4 a = make_float4(0.f, 0.f, 0.f, -1.f), b = make_float4(1.f, 0.f, 0.f, 0.f);
+                if (j < cnt) {
+                    a = __ldg(cull4 + 2 * (size_t)(t0 + j));      // cx cy cz r2
+                    b = __ldg(cull4 + 2 * (size_t)(t0 + j) + 1);  // h cc e0 type
+                }
+                // r2 < 0 marks "never hit" (and the padding of the last iteration): e' = +inf rejects every finite l
+                const float e = a.w < 0.f ? inf : -fmaf(-hmin, b.y, fmaf(kExpandPad, b.y, a.w));
+                tile[2 * j] = make_float4(a.x, a.x, a.y, a.y);
+                tile[2 * j + 1] = make_float4(a.z, a.z, e, e);
             }
             __syncthreads();
-#pragma unroll 2
-            for (uint32_t j = 0; j < cnt; ++j) {
-                const float4 a = tile[j];
-                bool pass[RPT];
-                bool any = false;
+            for (uint32_t j = 0; j < cnt_pad; j += OPI) {
+                float2 l[OPI][P];
+                float thr[OPI];
+                bool mine = false;
 #pragma unroll
-                for (int r = 0; r < RPT; ++r) {
-                    const float dt = fmaf(a.x, ux[r], fmaf(a.y, uy[r], fmaf(a.z, uz[r], nq[r])));
-                    const float w = fmaf(a.x, px[r], fmaf(a.y, py[r], fmaf(a.z, pz[r], oo[r])));
-                    pass[r] = !(fmaf(-dt, dt, w) > a.w);
-                    any |= pass[r];
+                for (int o = 0; o < OPI; ++o) {
+                    const float4 A = tile[2 * (j + o)], B = tile[2 * (j + o) + 1];
+                    const float2 ax = make_float2(A.x, A.y), ay = make_float2(A.z, A.w), az = make_float2(B.x, B.y);
+                    thr[o] = B.z;
+#pragma unroll
+                    for (int p = 0; p < P; ++p) {
+                        const float2 dt = __ffma2_rn(ax, UX[p], __ffma2_rn(ay, UY[p], __ffma2_rn(az, UZ[p], NQ[p])));
+                        const float2 w = __ffma2_rn(ax, PX[p], __ffma2_rn(ay, PY[p], __ffma2_rn(az, PZ[p], OO[p])));
+                        l[o][p] = __ffma2_rn(dt, dt, w);
+                    }
                 }
-                if (any) {
 #pragma unroll
-                    for (int r = 0; r < RPT; ++r)
-                        if (pass[r] && base + r * kBlock < n) {
-                            filter_exact(sc, q, base + r * kBlock, t0 + j, &best_t[r][tid], &best_i[r][tid]);
-                            if (COUNT) lc.exact_tests++;
+                for (int o = 0; o < OPI; ++o) {
+                    float m = fmaxf(l[o][0].x, l[o][0].y);
+#pragma unroll
+                    for (int p = 1; p < P; ++p) m = fmaxf(fmaxf(m, l[o][p].x), l[o][p].y);
+                    mine |= m >= thr[o];
+                }
+                if (__any_sync(kFull, mine)) {  // warp-uniform: somebody has a survivor
+#pragma unroll
+                    for (int o = 0; o < OPI; ++o) {
+                        if (j + o >= cnt) continue;  // padding of the last iteration
+#pragma unroll
+                        for (int p = 0; p < P; ++p) {
+                            if (l[o][p].x >= thr[o]) {
+                                const uint32_t slot = atomicAdd(&fs.cand_n[warp], 1u);
+                                fs.cand_obj[warp][slot] = t0 + j + o;
+                                fs.cand_who[warp][slot] = (uint16_t)((lane << 3) | (2 * p));
+                            }
+                            if (l[o][p].y >= thr[o]) {
+                                const uint32_t slot = atomicAdd(&fs.cand_n[warp], 1u);
+                                fs.cand_obj[warp][slot] = t0 + j + o;
+                                fs.cand_who[warp][slot] = (uint16_t)((lane << 3) | (2 * p + 1));
+                            }
                         }
+                        __syncwarp();
+                        uint32_t have = fs.cand_n[warp];
+                        if (have >= 32u) {  // full batches from the tail of the list (the list holds at most CAP entries)
+                            do {
+                                filter_flush<RPT, CAP>(sc, q, fs, best_t, best_i, warp_base, have - 32u, 32u);
+                                if (COUNT) lc.exact_tests++;
+                                have -= 32u;
+                            } while (have >= 32u);
+                            __syncwarp();
+                            if (lane == 0) fs.cand_n[warp] = have;
+                        }
+                        __syncwarp();
+                    }
                 }
             }
+        }
+        {  // the remainder of the list
+            __syncwarp();
+            const uint32_t have = fs.cand_n[warp];
+            if (have) filter_flush<RPT, CAP>(sc, q, fs, best_t, best_i, warp_base, 0u, have);
+            if (COUNT && lane < have) lc.exact_tests++;
+            __syncwarp();
         }
 #pragma unroll
         for (int r = 0; r < RPT; ++r) {
@@ -412,6 +528,33 @@ __global__ void __launch_bounds__(kBlock, 2) wave_trace_filter(const Scene sc, c
         }
     }
     if (COUNT) flush_local(lc, ctr);
+}
+
+// One configuration of the filter kernel: launches the big-queue and the small-queue instantiation.
+template <int RPT, int OPI, int MINB, int TILE>
+cudaError_t launch_filter(const Scene& sc, const TaskQueue& qin, const uint32_t* n_ptr, float* res_t, int32_t* res_id, Counters* ctr,
+                          bool count, int sm_count, cudaStream_t stream) {
+    const unsigned fgrid = (unsigned)sm_count * MINB;
+    const uint32_t split = fgrid * kBlock * RPT;
+    const int bytes = TILE * 2 * (int)sizeof(float4);
+    static const cudaError_t attr = [] {
+        const int by = TILE * 2 * (int)sizeof(float4);
+        cudaError_t a = cudaFuncSetAttribute(wave_trace_filter<RPT, OPI, MINB, TILE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, by);
+        if (a == cudaSuccess) a = cudaFuncSetAttribute(wave_trace_filter<RPT, OPI, MINB, TILE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, by);
+        if (a == cudaSuccess) a = cudaFuncSetAttribute(wave_trace_filter<2, 1, MINB, TILE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, by);
+        if (a == cudaSuccess) a = cudaFuncSetAttribute(wave_trace_filter<2, 1, MINB, TILE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, by);
+        return a;
+    }();
+    if (attr != cudaSuccess) return attr;
+    // two instantiations, each takes the queue sizes it is efficient for (the size lives on the device)
+    if (count) {
+        wave_trace_filter<RPT, OPI, MINB, TILE, true><<<fgrid, kBlock, bytes, stream>>>(sc, qin, n_ptr, split, 0xffffffffu, res_t, res_id, ctr);
+        wave_trace_filter<2, 1, MINB, TILE, true><<<fgrid, kBlock, bytes, stream>>>(sc, qin, n_ptr, 0u, split, res_t, res_id, ctr);
+    } else {
+        wave_trace_filter<RPT, OPI, MINB, TILE, false><<<fgrid, kBlock, bytes, stream>>>(sc, qin, n_ptr, split, 0xffffffffu, res_t, res_id, ctr);
+        wave_trace_filter<2, 1, MINB, TILE, false><<<fgrid, kBlock, bytes, stream>>>(sc, qin, n_ptr, 0u, split, res_t, res_id, ctr);
+    }
+    return cudaGetLastError();
 }
 
 // ------------------------------------------------------------------------------------------------ advance
@@ -473,7 +616,7 @@ static int env_int(const char* name, int dflt) {
 cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb, int accel, uint32_t leaf_max, int sm_count,
                         uint32_t* launches, cudaStream_t stream) {
     // warp-scheduler thresholds of wave_trace_bvh (tunable for experiments)
-    static const int min_t = env_int("RT_WAVE_MIN_T", 20), drain_t = env_int("RT_WAVE_DRAIN", 12), refill_t = env_int("RT_WAVE_REFILL", 8);
+    static const int min_t = env_int("RT_WAVE_MIN_T", 16), drain_t = env_int("RT_WAVE_DRAIN", 8), refill_t = env_int("RT_WAVE_REFILL", 12);
     (void)leaf_max;
     const uint32_t gens = wave_max_generations(fr.max_bounces, sc.n_lights, fr.mode);
     if (gens + 1 > wb.n_counts) return cudaErrorInvalidValue;
@@ -510,16 +653,10 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
             else
                 wave_trace_bvh<false><<<pgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, fetch + g, wb.res_t, wb.res_id, min_t, drain_t, refill_t, fr.counters);
         } else if (accel == 1) {
-            // two instantiations, each takes the queue sizes it is efficient for (the size lives on the device)
-            const unsigned fgrid = (unsigned)sm_count * 2u;
-            const uint32_t split = fgrid * kBlock * 8u;
-            if (count) {
-                wave_trace_filter<8, true><<<fgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, split, 0xffffffffu, wb.res_t, wb.res_id, fr.counters);
-                wave_trace_filter<2, true><<<fgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, 0u, split, wb.res_t, wb.res_id, fr.counters);
-            } else {
-                wave_trace_filter<8, false><<<fgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, split, 0xffffffffu, wb.res_t, wb.res_id, fr.counters);
-                wave_trace_filter<2, false><<<fgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, 0u, split, wb.res_t, wb.res_id, fr.counters);
-            }
+            // 4 rays per thread x 4 objects per iteration, 2 blocks per SM, 2048-object tiles: the fastest of the
+            // configurations swept on the B200 (tools/sweep_filter.sh history in DESIGN.md)
+            const cudaError_t fe = launch_filter<4, 4, 2, 2048>(sc, qin, qcount + g, wb.res_t, wb.res_id, fr.counters, count, sm_count, stream);
+            if (fe != cudaSuccess) return fe;
             ++nl;
         } else {
             if (count)

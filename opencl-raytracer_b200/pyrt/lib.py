@@ -15,13 +15,13 @@ _PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 # RT_B200_LIB: an alternative build of the same library (kernel experiments); never a fallback
 LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_PKG, "librt_b200.so")
 
-OPT_PIPELINE, OPT_COUNT_RAYS, OPT_BVH_LEAF, OPT_SKIP_DEAD_RAYS = 1, 2, 3, 4
+OPT_PIPELINE, OPT_COUNT_RAYS, OPT_BVH_LEAF, OPT_SKIP_DEAD_RAYS, OPT_READBACK_BANDS = 1, 2, 3, 4, 5
 
 # every symbol include/rt_b200.h declares (tests check the library exports all of them)
 ABI_SYMBOLS = (
     "rt_last_error", "rt_abi_version", "rt_create", "rt_destroy", "rt_set_option", "rt_upload_scene", "rt_set_rays",
     "rt_set_camera", "rt_set_shard", "rt_render", "rt_render_device", "rt_framebuffer", "rt_render_aov", "rt_trace",
-    "rt_get_stats", "rt_quantize_rgb8", "rt_host_alloc", "rt_host_free", "rt_measure_fp32_peak",
+    "rt_get_stats", "rt_quantize_rgb8", "rt_host_alloc", "rt_host_free", "rt_measure_fp32_peak", "rt_fp32_peak_detail",
     "rt_ipc_export_framebuffer", "rt_ipc_open", "rt_ipc_close", "rt_readback",
 )
 
@@ -81,6 +81,7 @@ def load():
             "rt_host_alloc": [C.POINTER(vp), u64],
             "rt_host_free": [vp],
             "rt_measure_fp32_peak": [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)],
+            "rt_fp32_peak_detail": [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)],
             "rt_ipc_export_framebuffer": [vp, vp],
             "rt_ipc_open": [vp, vp, C.POINTER(vp)],
             "rt_ipc_close": [vp, vp],
@@ -230,6 +231,12 @@ class Context:
         t, mhz = C.c_float(), C.c_float()
         _check(load().rt_measure_fp32_peak(self._h, C.byref(t), C.byref(mhz)))
         return t.value, mhz.value
+
+    def fp32_peak_detail(self):
+        """(scalar FFMA loop, packed FFMA2 loop) TFLOP/s of the last measure_fp32_peak()."""
+        a, b = C.c_float(), C.c_float()
+        _check(load().rt_fp32_peak_detail(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
 
     # -- multi-GPU plumbing: framebuffer shared between processes (CUDA IPC)
     def ipc_export_framebuffer(self) -> bytes:

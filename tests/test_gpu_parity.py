@@ -211,6 +211,29 @@ def test_sharded_render_equals_whole_frame(rt, oracle_mod):
         assert np.array_equal(frame, whole)
 
 
+def test_banded_readback_equals_plain_render(rt, ctx):
+    """rt_render of a large whole frame is cut into bands whose device->host copy overlaps the next band's kernels
+    (RT_OPT_READBACK_BANDS); the frame, the ray counts and the hit statistics must not depend on the banding."""
+    objs, lights = S.synthetic_scene(3000, 300)
+    W, H = 2048, 2051  # >= 4 Mpixel, ragged last band
+    z = T.camera_zdir(H)
+    ctx.set_option(rt.OPT_COUNT_RAYS, 1)
+    ctx.upload_scene(objs, lights)
+    ctx.set_camera(W, H, z)
+    ctx.set_option(rt.OPT_READBACK_BANDS, 1)
+    plain = ctx.render(4, 2, 2).copy()
+    s0 = ctx.stats()
+    ref_counts = (s0.rays_primary, s0.rays_shadow, s0.rays_reflect, s0.traced_shadow, s0.traced_reflect, s0.hit_pixels, s0.pixels)
+    assert s0.pixels == W * H and s0.hit_pixels > 0
+    for bands in (4, 7, 16):
+        ctx.set_option(rt.OPT_READBACK_BANDS, bands)
+        out = np.full((W * H, 4), -3.0, dtype=np.float32)
+        ctx.render(4, 2, 2, out=out)
+        s1 = ctx.stats()
+        assert np.array_equal(out, plain)
+        assert (s1.rays_primary, s1.rays_shadow, s1.rays_reflect, s1.traced_shadow, s1.traced_reflect, s1.hit_pixels, s1.pixels) == ref_counts
+
+
 def test_quantize_is_byte_identical_to_ppm_rule(rt, ctx):
     rng = np.random.Generator(np.random.PCG64(1))
     rgba = rng.uniform(-0.2, 1.3, size=(50000, 4)).astype(np.float32)
