@@ -139,7 +139,8 @@ def cpu_arm(objs, lights, rays, max_bounces, mode, steps, warmup, n_ref_rays=Non
     if n_ref_rays is None:
         _, _, _, st = oracle.port_render(mode, max_bounces, objs, lights, rays, nthreads=cores)
         n_ref_rays = st.rays_primary + st.rays_shadow + st.rays_reflect
-    use_ref = oracle.have_ref()
+    # the reference kernels skip every type but sphere / box: a scene with the triangle extension is timed on the C restatement
+    use_ref = oracle.have_ref() and not bool((np.asarray(objs["type"]) > 1).any())
     fast = use_ref and oracle.cpu_has_avx2_fma() and os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libsar_ref_fast.so"))
     kind = "reference" if use_ref else "port"
 
@@ -398,7 +399,9 @@ def main():
             import oracle
 
             ok, info = oracle.ocl_probe()
-            if not ok:
+            if bool((np.asarray(objs["type"]) > 1).any()):
+                ref_ocl = {"unavailable": "the reference kernels have no triangle primitive (type 2 is this project's extension)"}
+            elif not ok:
                 ref_ocl = {"unavailable": info}
             else:
                 # brute force over every object: a band of rows sized for about a second of kernel time

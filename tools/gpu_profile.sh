@@ -12,7 +12,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 700 --csv --log-fil
 S="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-brute-leg --workload cfg5-small"
 $S > $O/${TAG}_bench_small.json 2>&1 || { echo "small bench failed"; exit 1; }
 ncu --set full --clock-control none --import-source on -k regex:wave_trace_bvh -c 4 -f -o $O/${TAG}_trace_bvh $S > $O/${TAG}_ncu_bvh.log 2>&1
-F="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-brute-leg --workload cfg5-tiny --accel 1"
+F="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-brute-leg --workload cfg5-small --accel 1"
 $F > $O/${TAG}_bench_filter.json 2>&1 || { echo "filter bench failed"; exit 1; }
-ncu --set full --clock-control none --import-source on -k regex:wave_trace_filter -c 2 -f -o $O/${TAG}_trace_filter $F > $O/${TAG}_ncu_filter.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:wave_trace_filter -c 1 -f -o $O/${TAG}_trace_filter $F > $O/${TAG}_ncu_filter.log 2>&1
 ls -la $O | tail -20
