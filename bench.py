@@ -205,6 +205,10 @@ def main():
         return
 
     # ------------------------------------------------------------------ our arm (CUDA)
+    # stdout carries exactly one JSON line: libraries that print there (NCCL's version banner) go to stderr instead
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     import torch
     import torch.distributed as dist
 
@@ -262,6 +266,8 @@ def main():
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
 
+    last_rank_ms = []
+
     def timed(fn, steps, warmup):
         for _ in range(warmup):
             fn()
@@ -279,6 +285,9 @@ def main():
         clocks = sampler_local.stop()
         t = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
         if world > 1:
+            every = [torch.zeros_like(t) for _ in range(world)]
+            dist.all_gather(every, t)
+            last_rank_ms[:] = [float(x.item()) / steps for x in every]
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item()) / steps, wall_ms / steps, clocks
 
@@ -287,6 +296,7 @@ def main():
         return ctx.stats().kernel_ms
 
     ms_dev, _, clocks = timed(step_device, args.steps, args.warmup)
+    rank_ms = list(last_rank_ms)
     value = rays_traced / (ms_dev * 1e-3) / 1e6
 
     # e2e: Render() semantics -- launch + readback of the whole frame to pinned host memory on rank 0
@@ -294,16 +304,46 @@ def main():
 
     def step_e2e():
         t0 = time.perf_counter()
-        if world == 1:
-            ctx.render(max_bounces, mode, args.accel, out=host.array)
-        else:
-            ctx.render_device(max_bounces, mode, args.accel, target)
-            barrier()  # every shard has landed in rank 0's HBM
-            if rank == 0:
-                ctx.readback(host.array)
+        ctx.render(max_bounces, mode, args.accel, out=host.array)
         return (time.perf_counter() - t0) * 1e3
 
-    ms_e2e, _, _ = timed(step_e2e, args.steps, args.warmup)
+    def step_e2e_gather():  # N > 1, variant A: peer stores into rank 0's HBM over NVLink, rank 0 reads the frame back
+        t0 = time.perf_counter()
+        ctx.render_device(max_bounces, mode, args.accel, target)
+        barrier()  # every shard has landed in rank 0's HBM
+        if rank == 0:
+            ctx.readback(host.array)
+        return (time.perf_counter() - t0) * 1e3
+
+    e2e_gather = None
+    if world == 1:
+        ms_e2e, _, _ = timed(step_e2e, args.steps, args.warmup)
+    else:
+        ms_gather, _, _ = timed(step_e2e_gather, args.steps, args.warmup)
+        e2e_gather = {"value": rays_traced / (ms_gather * 1e-3) / 1e6, "ms_per_step": ms_gather,
+                      "path": "kernels store into rank 0's framebuffer over NVLink (CUDA IPC), rank 0 copies the frame to the host"}
+        # variant B (the headline at N > 1): one host frame in shared memory, page-locked in every rank; each GPU renders
+        # into its own framebuffer and copies its own row-blocks to the host over its own PCIe link
+        name = [None]
+        shared = None
+        if rank == 0:
+            shared = lib.SharedFrame(W * H)
+            name[0] = shared.name
+        dist.broadcast_object_list(name, src=0)
+        if rank != 0:
+            shared = lib.SharedFrame(W * H, name=name[0])
+
+        def step_e2e_direct():
+            t0 = time.perf_counter()
+            ctx.render(max_bounces, mode, args.accel, out=shared.array)
+            barrier()  # every rank's rows are in the host frame
+            return (time.perf_counter() - t0) * 1e3
+
+        ms_e2e, _, _ = timed(step_e2e_direct, args.steps, args.warmup)
+        if rank == 0:  # the two paths must produce the same frame
+            assert np.array_equal(shared.array, host.array), "direct per-GPU readback differs from the NVLink gather"
+        barrier()
+        shared.close()
     e2e_value = rays_traced / (ms_e2e * 1e-3) / 1e6
     e2e_stats = ctx.stats()
 
@@ -442,10 +482,14 @@ def main():
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": 0,
                     "d2h_bytes_per_step": W * H * 16,
                     "device_ms": {"kernels": e2e_stats.kernel_ms, "kernels_plus_copy": e2e_stats.total_ms},
+                    "nvlink_gather_variant": e2e_gather,
+                    "path": "rt_render into the caller's pinned frame" if world == 1 else
+                            "every rank rt_render()s its row-blocks into one shared, page-locked host frame (own PCIe link per GPU)",
                     "ctor_plus_first_render_ms": cold_ms, "scene_h2d_bytes_once": int(len(objs)) * 276 + int(len(lights)) * 64,
                     "note": "rt_render == IRaytracer::Render(): launch + blocking readback (bands of rows, copy overlapped with the next "
                             "band's kernels); scene/camera resident as in the reference ctor, whose one-off cost is ctor_plus_first_render_ms"},
             "gpu_launches": args.steps * launches_per_step,
+            "rank_ms": rank_ms or None,
             "clocks": clocks,
             "roofline": roofline,
         }
@@ -455,7 +499,8 @@ def main():
             out["cpu_baseline"] = cpu
         if ref_ocl:
             out["reference_opencl_gpu"] = ref_ocl
-        print(json.dumps(out))
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(out) + "\n").encode())
     if world > 1:
         if target:
             ctx.ipc_close(target)

@@ -185,6 +185,10 @@ int rt_ipc_close(rt_ctx* ctx, void* dev_ptr);
  * a pinned one makes the readback a single DMA. */
 int rt_host_alloc(void** out, uint64_t bytes);
 int rt_host_free(void* p);
+/* Page-lock an existing host range (e.g. a POSIX shared-memory segment that every rank of a multi-GPU job maps, so that
+ * each GPU copies its own rows of the frame straight into the one host frame over its own PCIe link). */
+int rt_host_register(void* p, uint64_t bytes);
+int rt_host_unregister(void* p);
 
 /* Register-only FFMA loop: measured FP32 peak of this device in TFLOP/s (roofline denominator). */
 int rt_measure_fp32_peak(rt_ctx* ctx, float* tflops, float* sm_mhz_hint);

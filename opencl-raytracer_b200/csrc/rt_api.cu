@@ -774,6 +774,17 @@ int rt_host_alloc(void** out, uint64_t bytes) {
     return RT_OK;
 }
 
+int rt_host_register(void* p, uint64_t bytes) {
+    if (!p || !bytes) return fail(RT_ERR_INVALID, "null argument");
+    RT_CUDA(cudaHostRegister(p, bytes, cudaHostRegisterPortable));
+    return RT_OK;
+}
+
+int rt_host_unregister(void* p) {
+    if (p) RT_CUDA(cudaHostUnregister(p));
+    return RT_OK;
+}
+
 int rt_host_free(void* p) {
     if (p) RT_CUDA(cudaFreeHost(p));
     return RT_OK;

@@ -21,7 +21,7 @@ OPT_PIPELINE, OPT_COUNT_RAYS, OPT_BVH_LEAF, OPT_SKIP_DEAD_RAYS, OPT_READBACK_BAN
 ABI_SYMBOLS = (
     "rt_last_error", "rt_abi_version", "rt_create", "rt_destroy", "rt_set_option", "rt_upload_scene", "rt_set_rays",
     "rt_set_camera", "rt_set_shard", "rt_render", "rt_render_device", "rt_framebuffer", "rt_render_aov", "rt_trace",
-    "rt_get_stats", "rt_quantize_rgb8", "rt_host_alloc", "rt_host_free", "rt_measure_fp32_peak", "rt_fp32_peak_detail",
+    "rt_get_stats", "rt_quantize_rgb8", "rt_host_alloc", "rt_host_free", "rt_host_register", "rt_host_unregister", "rt_measure_fp32_peak", "rt_fp32_peak_detail",
     "rt_ipc_export_framebuffer", "rt_ipc_open", "rt_ipc_close", "rt_readback",
 )
 
@@ -80,6 +80,8 @@ def load():
             "rt_quantize_rgb8": [vp, vp, u64, vp],
             "rt_host_alloc": [C.POINTER(vp), u64],
             "rt_host_free": [vp],
+            "rt_host_register": [vp, u64],
+            "rt_host_unregister": [vp],
             "rt_measure_fp32_peak": [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)],
             "rt_fp32_peak_detail": [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)],
             "rt_ipc_export_framebuffer": [vp, vp],
@@ -107,6 +109,41 @@ def _check(rc):
 
 def _ptr(a):
     return a.ctypes.data_as(C.c_void_p) if a is not None and a.size else None
+
+
+class SharedFrame:
+    """One host frame shared by every rank of a multi-GPU job: a POSIX shared-memory segment, page-locked in each
+    process (rt_host_register), so that every GPU copies its own rows into it over its own PCIe link."""
+
+    def __init__(self, n_pixels: int, name: str | None = None):
+        from multiprocessing import shared_memory
+
+        self.nbytes = int(n_pixels) * 16
+        self.owner = name is None
+        self.shm = shared_memory.SharedMemory(create=self.owner, size=self.nbytes) if self.owner else shared_memory.SharedMemory(name=name)
+        self.name = self.shm.name
+        if not self.owner:  # Python < 3.13 registers attached segments too; only the creating rank may unlink
+            try:
+                from multiprocessing import resource_tracker
+
+                resource_tracker.unregister(self.shm._name, "shared_memory")
+            except Exception:
+                pass
+        self.array = np.ndarray((int(n_pixels), 4), dtype=np.float32, buffer=self.shm.buf)
+        self._addr = C.c_void_p(self.array.ctypes.data)
+        _check(load().rt_host_register(self._addr, self.nbytes))
+
+    def close(self):
+        if self.shm is not None:
+            load().rt_host_unregister(self._addr)
+            self.array = None
+            try:
+                self.shm.close()
+                if self.owner:
+                    self.shm.unlink()
+            except Exception:
+                pass
+            self.shm = None
 
 
 class PinnedBuffer:

@@ -234,6 +234,32 @@ def test_banded_readback_equals_plain_render(rt, ctx):
         assert (s1.rays_primary, s1.rays_shadow, s1.rays_reflect, s1.traced_shadow, s1.traced_reflect, s1.hit_pixels, s1.pixels) == ref_counts
 
 
+def test_shared_host_frame_collects_every_shard(rt):
+    """Multi-GPU end-to-end path: one page-locked shared-memory frame, every shard's rt_render copies its own row-blocks
+    into it (here: four shards rendered one after the other on the same GPU)."""
+    objs, lights = S.synthetic_scene(3000, 300)
+    W, H = 256, 150
+    z = T.camera_zdir(H)
+    with rt.Context(0) as c:
+        c.upload_scene(objs, lights)
+        c.set_camera(W, H, z)
+        whole = c.render(4, 2, 2).copy()
+    owner = rt.SharedFrame(W * H)
+    try:
+        owner.array[:] = -5.0
+        for s in range(4):
+            peer = rt.SharedFrame(W * H, name=owner.name)  # what another rank does with the broadcast name
+            with rt.Context(0) as c:
+                c.upload_scene(objs, lights)
+                c.set_camera(W, H, z)
+                c.set_shard(16, s, 4)
+                c.render(4, 2, 2, out=peer.array)
+            peer.close()
+        assert np.array_equal(owner.array, whole)
+    finally:
+        owner.close()
+
+
 def test_quantize_is_byte_identical_to_ppm_rule(rt, ctx):
     rng = np.random.Generator(np.random.PCG64(1))
     rgba = rng.uniform(-0.2, 1.3, size=(50000, 4)).astype(np.float32)
