@@ -172,6 +172,7 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=0, help="side of the pixel lattice of the CPU sample (0 = auto)")
     ap.add_argument("--leaf", type=int, default=0, help="BVH leaf size (0 = library default)")
     ap.add_argument("--pipeline", type=int, default=-1, help="-1 auto, 0 megakernel, 1 wavefront")
+    ap.add_argument("--builder", type=int, default=0, help="BVH builder: 0 host SAH, 1 device LBVH")
     ap.add_argument("--bands", type=int, default=0, help="readback bands of rt_render (0 = library default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-brute-leg", action="store_true")
@@ -232,6 +233,8 @@ def main():
         ctx.set_option(lib.OPT_PIPELINE, args.pipeline)
     if args.bands:
         ctx.set_option(lib.OPT_READBACK_BANDS, args.bands)
+    if args.builder:
+        ctx.set_option(lib.OPT_BVH_BUILDER, args.builder)
     t_up0 = time.perf_counter()
     ctx.upload_scene(objs, lights)
     ctx.set_camera(W, H, zdir)
@@ -474,7 +477,7 @@ def main():
                            sharding="row-blocks of %d rows round-robin over %d ranks, peer stores into rank 0 (CUDA IPC)" % (args.block_rows, world)
                            if world > 1 else "single GPU",
                            l2="framebuffer %d MB > L2; 256 MB memset between steps flushes L2 (scene is re-read from HBM each step)" % (W * H * 16 >> 20),
-                           scene_upload_ms=upload_ms),
+                           scene_upload_ms=upload_ms, bvh_builder=["host SAH", "device LBVH"][args.builder]),
             "rays": {"traced": rays_traced, "reference": rays_reference, "primary": r_prim, "shadow_traced": t_shadow,
                      "shadow_reference": r_shadow, "reflect_traced": t_refl, "reflect_reference": r_refl, "hit_pixels": hit_pixels,
                      "pair_tests": pair_tests, "exact_tests": exact_tests, "node_visits": node_visits,

@@ -121,6 +121,8 @@ typedef enum rt_option {
     RT_OPT_COUNT_RAYS = 2, /* 1: fill the ray/test counters of rt_stats (small atomics cost) */
     RT_OPT_BVH_LEAF = 3,   /* max objects per BVH leaf (1..16) */
     RT_OPT_SKIP_DEAD_RAYS = 4, /* 1 (default): do not trace rays whose result is dead; 0: trace every ray the reference traces */
+    RT_OPT_BVH_BUILDER = 6,    /* 0 (default): binned SAH on the host in rt_upload_scene; 1: Morton-order radix tree built on the
+                                  device (scenes that change every frame: ~1 ms instead of ~150 ms per 10^5 objects, a looser tree) */
     RT_OPT_READBACK_BANDS = 5  /* rt_render of a large whole frame: bands of rows whose readback overlaps the next band's kernels
                                   (geometrically shrinking, default 2; 1 = render the frame, then copy it) */
 } rt_option;

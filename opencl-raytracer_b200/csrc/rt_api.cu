@@ -12,6 +12,7 @@
 
 #include "../../include/rt_b200.h"
 #include "rt_kernels.cuh"
+#include "rt_lbvh.cuh"
 #include "rt_scene.hpp"
 #include "rt_wavefront.cuh"
 
@@ -74,6 +75,8 @@ struct rt_ctx {
     DevBuf<rt::CullRec> d_cull, d_leaf_cull;
     DevBuf<rt::BvhNode> d_nodes;
     DevBuf<uint32_t> d_leaf_obj;
+    DevBuf<rt::LbvhLeaf> d_lbvh_leaves;  // device tree builder (RT_OPT_BVH_BUILDER = 1): input records and scratch
+    DevBuf<char> d_lbvh_scratch;
     rt::Scene scene;
 
     // rays / camera
@@ -101,7 +104,7 @@ struct rt_ctx {
     uint32_t last_launches = 1;
 
     // options
-    int opt_pipeline = -1, opt_count = 0, opt_leaf = 1, opt_skip_dead = 1, opt_bands = 2;
+    int opt_pipeline = -1, opt_count = 0, opt_leaf = 1, opt_skip_dead = 1, opt_bands = 2, opt_builder = 0;
 
     rt_stats stats;
     float fp32_peak_tf[2] = {0.f, 0.f};  // last rt_measure_fp32_peak: scalar FFMA loop, packed FFMA2 loop
@@ -133,16 +136,31 @@ int sync_scene(rt_ctx* c) {
     if (!c->scene_dirty && need_omax <= c->hs.omax) return RT_OK;
     std::string err;
     const int rc = rt::build_scene(c->objs.data(), (uint32_t)c->objs.size(), c->lights.data(), (uint32_t)c->lights.size(),
-                                   c->omax_user, c->opt_leaf, c->hs, err);
+                                   c->omax_user, c->opt_builder == 1 ? 0 : c->opt_leaf, c->hs, err);
     if (rc != RT_OK) return fail(rc, err);
+    const bool device_tree = !c->hs.lbvh_leaves.empty();
     RT_CUDA(c->d_minv.upload(c->hs.minv, c->stream));
     RT_CUDA(c->d_mv.upload(c->hs.mv, c->stream));
     RT_CUDA(c->d_mat.upload(c->hs.mat, c->stream));
     RT_CUDA(c->d_lights.upload(c->hs.lights, c->stream));
     RT_CUDA(c->d_cull.upload(c->hs.cull, c->stream));
-    RT_CUDA(c->d_leaf_cull.upload(c->hs.leaf_cull, c->stream));
-    RT_CUDA(c->d_nodes.upload(c->hs.nodes, c->stream));
-    RT_CUDA(c->d_leaf_obj.upload(c->hs.leaf_obj, c->stream));
+    uint32_t n_nodes = (uint32_t)c->hs.nodes.size();
+    if (device_tree) {  // bounds came from the host, the tree is built here: Morton sort, radix tree, refit (rt_lbvh.cu)
+        const uint32_t n = (uint32_t)c->hs.lbvh_leaves.size();
+        RT_CUDA(c->d_lbvh_leaves.upload(c->hs.lbvh_leaves, c->stream));
+        const size_t sb = rt::lbvh_scratch_bytes(n);
+        RT_CUDA(c->d_lbvh_scratch.ensure(sb));
+        RT_CUDA(c->d_nodes.ensure(n - 1));
+        RT_CUDA(c->d_leaf_obj.ensure(n));
+        RT_CUDA(c->d_leaf_cull.ensure(n));
+        RT_CUDA(rt::build_lbvh_device(c->d_lbvh_leaves.p, n, c->d_cull.p, c->hs.lbvh_lo, c->hs.lbvh_hi, c->hs.omax, c->d_lbvh_scratch.p, sb,
+                                      c->d_nodes.p, c->d_leaf_obj.p, c->d_leaf_cull.p, c->stream));
+        n_nodes = n - 1;
+    } else {
+        RT_CUDA(c->d_leaf_cull.upload(c->hs.leaf_cull, c->stream));
+        RT_CUDA(c->d_nodes.upload(c->hs.nodes, c->stream));
+        RT_CUDA(c->d_leaf_obj.upload(c->hs.leaf_obj, c->stream));
+    }
     RT_CUDA(cudaStreamSynchronize(c->stream));
     rt::Scene& s = c->scene;
     s.minv = reinterpret_cast<const float4*>(c->d_minv.p);
@@ -155,7 +173,7 @@ int sync_scene(rt_ctx* c) {
     s.lights = reinterpret_cast<const rt::Light*>(c->d_lights.p);
     s.n_objs = c->hs.n_objs;
     s.n_lights = c->hs.n_lights;
-    s.n_nodes = (uint32_t)c->hs.nodes.size();
+    s.n_nodes = n_nodes;
     s.root = c->hs.root;
     s.root_f = c->hs.f_global;
     s.filter_h = c->hs.h_min;
@@ -403,7 +421,7 @@ int rt_destroy(rt_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     c->d_minv.release(); c->d_mv.release(); c->d_mat.release(); c->d_lights.release();
-    c->d_cull.release(); c->d_leaf_cull.release(); c->d_nodes.release(); c->d_leaf_obj.release();
+    c->d_cull.release(); c->d_leaf_cull.release(); c->d_nodes.release(); c->d_lbvh_leaves.release(); c->d_lbvh_scratch.release(); c->d_leaf_obj.release();
     c->d_rays.release(); c->d_fb.release(); c->d_hit_id.release(); c->d_hit_t.release(); c->d_counters.release();
     c->d_sink.release();
     c->w_acc.release(); c->w_refl.release(); c->w_P.release(); c->w_Nm.release(); c->w_Rc.release(); c->w_out.release();
@@ -431,6 +449,11 @@ int rt_set_option(rt_ctx* c, int option, int64_t value) {
             c->scene_dirty = true;
             return RT_OK;
         case RT_OPT_SKIP_DEAD_RAYS: c->opt_skip_dead = value ? 1 : 0; return RT_OK;
+        case RT_OPT_BVH_BUILDER:
+            if (value != 0 && value != 1) return fail(RT_ERR_INVALID, "builder must be 0 (host SAH) or 1 (device LBVH)");
+            c->opt_builder = (int)value;
+            c->scene_dirty = true;
+            return RT_OK;
         case RT_OPT_READBACK_BANDS:
             if (value < 1 || value > rt_ctx::kMaxBands) return fail(RT_ERR_INVALID, "readback bands must be 1..16");
             c->opt_bands = (int)value;

@@ -275,6 +275,7 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
         err = "too many objects";
         return RT_ERR_INVALID;
     }
+    const bool device_tree = leaf_size == 0;
     leaf_size = std::min(std::max(leaf_size, 1), 16);
 
     out.minv.resize(4 * (size_t)n_objs);
@@ -460,6 +461,29 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
     }
     std::vector<ObjBound> lob(live.size());
     for (size_t i = 0; i < live.size(); ++i) lob[i] = ob[live[i]];
+    if (device_tree && live.size() > 1) {  // the tree is built on the device (rt_lbvh.cu) from these records
+        out.lbvh_leaves.resize(live.size());
+        for (int k = 0; k < 3; ++k) {
+            out.lbvh_lo[k] = INFINITY;
+            out.lbvh_hi[k] = -INFINITY;
+        }
+        double fmax = 0;
+        for (size_t i = 0; i < live.size(); ++i) {
+            LbvhLeaf& l = out.lbvh_leaves[i];
+            for (int k = 0; k < 3; ++k) {
+                l.c[k] = (float)lob[i].c[k];
+                l.half[k] = up(lob[i].half[k] + fabs(lob[i].c[k] - (double)l.c[k]));  // the centre moved by its rounding
+                out.lbvh_lo[k] = std::min(out.lbvh_lo[k], l.c[k]);
+                out.lbvh_hi[k] = std::max(out.lbvh_hi[k], l.c[k]);
+            }
+            l.f = up(lob[i].f);
+            l.obj = live[i];
+            fmax = std::max(fmax, lob[i].f);
+        }
+        out.f_global = up(fmax);
+        out.root = 0;
+        return RT_OK;
+    }
     Builder bld(lob, leaf_size);
     bld.bn.reserve(2 * live.size());
     const int root = bld.build(0, (uint32_t)live.size(), 0);

@@ -17,6 +17,15 @@ struct F4 {
     float x, y, z, w;
 };
 
+// Input of the device-side tree builder (rt_lbvh.cu): one record per live object, bounds already padded and rounded
+// outwards to binary32.
+struct LbvhLeaf {  // 32 B
+    float c[3];     // centre
+    float half[3];  // padded half extents
+    float f;        // noise coefficient (box inflation per unit distance)
+    uint32_t obj;   // object index
+};
+
 struct HostScene {
     std::vector<F4> minv;  // 4 per object (columns of mvInverse)
     std::vector<F4> mv;    // 4 per object
@@ -33,10 +42,14 @@ struct HostScene {
     uint32_t bvh_depth = 0;
     float h_min = 1.f;     // smallest filter coefficient h = 1 - g over the live objects
     float f_global = 0.f;  // largest noise coefficient of the scene (per-child values are in the nodes)
+    // leaf_size == 0 ("no host tree"): the records for the device builder and the bounds of their centres
+    std::vector<LbvhLeaf> lbvh_leaves;
+    float lbvh_lo[3] = {0.f, 0.f, 0.f}, lbvh_hi[3] = {0.f, 0.f, 0.f};
 };
 
 // Returns RT_OK or RT_ERR_UNSUPPORTED / RT_ERR_INVALID with a message in err.
 // omax_user: largest |origin| of caller-supplied rays (0 for the pinhole camera).
+// leaf_size: objects per BVH leaf of the host SAH builder (1..16); 0 = build no tree, fill lbvh_leaves instead.
 int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, uint32_t n_lights, float omax_user,
                 int leaf_size, HostScene& out, std::string& err);
 

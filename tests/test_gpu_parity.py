@@ -234,6 +234,53 @@ def test_banded_readback_equals_plain_render(rt, ctx):
         assert (s1.rays_primary, s1.rays_shadow, s1.rays_reflect, s1.traced_shadow, s1.traced_reflect, s1.hit_pixels, s1.pixels) == ref_counts
 
 
+@pytest.mark.parametrize("second_type", [T.BOX, T.TRIANGLE])
+def test_device_built_tree_equals_oracle(rt, ctx, oracle_mod, second_type):
+    """RT_OPT_BVH_BUILDER = 1: Morton-order radix tree built on the device (rt_lbvh.cu).  A different tree, the same hits."""
+    objs, lights = S.synthetic_scene(6000, 500, second_type=second_type)
+    W, H = 160, 90
+    z, rays = frame_rays(W, H)
+    ref, hid, ht, st = oracle_mod.port_render(2, 4, objs, lights, rays)
+    ctx.set_option(rt.OPT_BVH_BUILDER, 1)
+    ctx.set_option(rt.OPT_COUNT_RAYS, 1)
+    ctx.upload_scene(objs, lights)
+    ctx.set_camera(W, H, z)
+    for pipeline in (0, 1):
+        ctx.set_option(rt.OPT_PIPELINE, pipeline)
+        out = ctx.render(4, 2, 2)
+        assert_colours_close(out, ref)
+        s = ctx.stats()
+        assert s.node_visits > 0 and s.pipeline_used == pipeline
+        assert (s.rays_primary, s.rays_shadow, s.rays_reflect) == (st.rays_primary, st.rays_shadow, st.rays_reflect)
+    gid, gt = ctx.render_aov(2)
+    assert np.array_equal(gid, hid) and np.array_equal(gt, ht)
+    rr = random_rays(20000, 5)
+    rid, rtt = oracle_mod.port_trace(objs, rr)
+    gid, gt = ctx.trace(rr, 2)
+    assert np.array_equal(gid, rid) and np.array_equal(gt, rtt)
+    # two objects: the smallest tree the device builder makes (one inner node, two leaves)
+    ctx.upload_scene(objs[:2], lights)
+    gid, gt = ctx.trace(rr, 2)
+    rid, rtt = oracle_mod.port_trace(objs[:2], rr)
+    assert np.array_equal(gid, rid) and np.array_equal(gt, rtt)
+
+
+def test_device_built_tree_full_size(rt, ctx):
+    """cfg5 geometry: the device-built tree and the host SAH tree give the same frame, bit for bit."""
+    objs, lights = S.synthetic_scene()
+    W, H = 512, 288
+    z = T.camera_zdir(H)
+    ctx.upload_scene(objs, lights)
+    ctx.set_camera(W, H, z)
+    a = ctx.render(4, 2, 2).copy()
+    ida, ta = ctx.render_aov(2)
+    ctx.set_option(rt.OPT_BVH_BUILDER, 1)
+    ctx.upload_scene(objs, lights)
+    b = ctx.render(4, 2, 2)
+    idb, tb = ctx.render_aov(2)
+    assert np.array_equal(ida, idb) and np.array_equal(ta, tb) and np.array_equal(a, b)
+
+
 def test_shared_host_frame_collects_every_shard(rt):
     """Multi-GPU end-to-end path: one page-locked shared-memory frame, every shard's rt_render copies its own row-blocks
     into it (here: four shards rendered one after the other on the same GPU)."""
