@@ -117,16 +117,6 @@ __device__ __noinline__ void exact_pair_call(const Scene& sc, const float4 s, co
     exact_pair(sc, r, obj, type, best, btype);
 }
 
-// The same arithmetic for an arbitrary (ray, object) pair, result only: t of the candidate or -1 (no candidate).
-__device__ __noinline__ float exact_t_call(const Scene& sc, const float4 rs, const float4 rd, uint32_t obj, uint32_t type) {
-    const float4* mi = sc.minv + 4 * (size_t)obj;
-    const float4 c0 = __ldg(mi + 0), c1 = __ldg(mi + 1), c2 = __ldg(mi + 2), c3 = __ldg(mi + 3);
-    const float4 s = ex::xform(c0, c1, c2, c3, rs);
-    const float4 d = ex::xform(c0, c1, c2, c3, rd);
-    float t = 0.f;
-    return ex::candidate(type, s, d, t) ? t : -1.f;
-}
-
 // Persistent warps.  Every lane owns one ray of the queue and is in one of four states:
 //   T  traversing (stands on an inner node)           S  traversing, but its candidate buffer is nearly full
 //   F  traversal finished, candidates still queued    I  idle (no ray)
@@ -140,17 +130,17 @@ __device__ __noinline__ float exact_t_call(const Scene& sc, const float4 rs, con
 // (thresholds swept on the B200 with tools/sweep_sched.sh; RT_WAVE_MIN_T / _DRAIN / _REFILL override them)
 // Deferring exact tests never changes the result: every queued candidate is tested before its ray retires, and
 // pruning against the best t found so far only ever skips nodes that cannot contain a better hit.
+#ifndef RT_BVH_MINB
+#define RT_BVH_MINB 3  // resident CTAs per SM of the persistent trace kernel (80 registers)
+#endif
 template <bool COUNT>
-__global__ void __launch_bounds__(kBlock, 3) wave_trace_bvh(const Scene sc, const TaskQueue q, const uint32_t* __restrict__ n_ptr,
+__global__ void __launch_bounds__(kBlock, RT_BVH_MINB) wave_trace_bvh(const Scene sc, const TaskQueue q, const uint32_t* __restrict__ n_ptr,
                                                             uint32_t* __restrict__ fetch, float* __restrict__ res_t,
                                                             int32_t* __restrict__ res_id, const int min_t, const int drain_t,
-                                                            const int refill_t, const int dense, Counters* ctr) {
+                                                            const int refill_t, Counters* ctr) {
     const uint32_t n = *n_ptr;
     if (n == 0u) return;
     __shared__ uint32_t pend[kPendCap][kBlock];
-    __shared__ float bt_t[kBlock];      // one dense batch of exact tests: t, object, type per lane
-    __shared__ uint32_t bt_obj[kBlock];
-    __shared__ uint32_t bt_type[kBlock];
     const unsigned lane = threadIdx.x & 31u, tid = threadIdx.x;
     LocalCounters lc;
 
@@ -264,67 +254,9 @@ __global__ void __launch_bounds__(kBlock, 3) wave_trace_bvh(const Scene sc, cons
             }
         }
 
-        // ---- exact tests, dense: ALL queued candidates of the warp, 32 per batch, whichever lane owns them -- a lane
-        // computes the exact t of some ray's candidate, the owner then merges its results (ex::replaces is order
-        // independent).  Lanes that queued several candidates no longer cost one sparse round each.
-        if (dense) {
-            const bool has = have && npend > 0;
-            const unsigned P = __ballot_sync(kFull, has);
-            const unsigned T = __ballot_sync(kFull, have && !tdone && npend == 0);
-            if (P != 0u && (__popc(P) >= drain_t || T == 0u)) {
-                int incl = has ? npend : 0;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const int v = __shfl_up_sync(kFull, incl, o);
-                    if ((int)lane >= o) incl += v;
-                }
-                const int total = __shfl_sync(kFull, incl, 31);
-                const int excl = incl - (has ? npend : 0);
-                const unsigned wbase = tid & ~31u;
-                for (int b0 = 0; b0 < total; b0 += 32) {
-                    const int gidx = b0 + (int)lane;
-                    int owner = 0;  // number of lanes whose inclusive count is <= gidx
-#pragma unroll
-                    for (int step = 16; step >= 1; step >>= 1) {
-                        const int v = __shfl_sync(kFull, incl, owner + step - 1);
-                        if (v <= gidx) owner += step;
-                    }
-                    owner = min(owner, 31);
-                    const int oexcl = __shfl_sync(kFull, excl, owner);
-                    const uint32_t otask = __shfl_sync(kFull, task, owner);
-                    if (gidx < total) {
-                        const uint32_t slot = pend[gidx - oexcl][wbase + owner];
-                        const uint32_t obj = __ldg(sc.leaf_obj + slot), type = __ldg(&sc.leaf_cull[slot].type);
-                        bt_t[tid] = exact_t_call(sc, q.s[otask], q.d[otask], obj, type);
-                        bt_obj[tid] = obj;
-                        bt_type[tid] = type;
-                        if (COUNT) lc.exact_tests++;
-                    }
-                    __syncwarp();
-                    if (has) {
-                        const int k0 = max(excl, b0), k1 = min(incl, b0 + 32);
-                        for (int k = k0; k < k1; ++k) {
-                            const float tc = bt_t[wbase + (k - b0)];
-                            if (!(tc < 0.f)) {
-                                const int32_t c = (int32_t)bt_obj[wbase + (k - b0)];
-                                const uint32_t ty = bt_type[wbase + (k - b0)];
-                                if (ex::replaces(tc, c, ty, best.t, best.id, btype)) {
-                                    best.t = tc;
-                                    best.id = c;
-                                    btype = ty;
-                                }
-                            }
-                        }
-                    }
-                    __syncwarp();
-                }
-                if (has) {
-                    npend = 0;
-                    if (anyhit && best.t < 1.f) tdone = true;  // the shadow ray is decided (SAR:229)
-                }
-            }
-        } else
-        // ---- exact tests, one candidate per lane and round
+        // ---- exact tests: one queued candidate per lane and round (a dense variant -- all candidates of the warp spread
+        // over its 32 lanes, owners merging the results -- was measured 1.5 % slower: the scan, the owner search and the
+        // staging through shared memory cost more than the idle lanes)
         for (;;) {
             const bool has = have && npend > 0;
             const unsigned P = __ballot_sync(kFull, has);
@@ -689,8 +621,7 @@ static int env_int(const char* name, int dflt) {
 cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb, int accel, uint32_t leaf_max, int sm_count,
                         uint32_t* launches, cudaStream_t stream) {
     // warp-scheduler thresholds of wave_trace_bvh (tunable for experiments)
-    static const int min_t = env_int("RT_WAVE_MIN_T", 16), drain_t = env_int("RT_WAVE_DRAIN", 8), refill_t = env_int("RT_WAVE_REFILL", 12),
-                     dense = env_int("RT_WAVE_DENSE", 1);
+    static const int min_t = env_int("RT_WAVE_MIN_T", 16), drain_t = env_int("RT_WAVE_DRAIN", 8), refill_t = env_int("RT_WAVE_REFILL", 12);
     (void)leaf_max;
     const uint32_t gens = wave_max_generations(fr.max_bounces, sc.n_lights, fr.mode);
     if (gens + 1 > wb.n_counts) return cudaErrorInvalidValue;
@@ -715,7 +646,7 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
     WaveParams wp;
     wp.max_bounces = fr.max_bounces;
     wp.mode = fr.mode;
-    const unsigned pgrid = (unsigned)sm_count * 3u;    // persistent trace: 3 CTAs of 8 warps per SM
+    const unsigned pgrid = (unsigned)sm_count * RT_BVH_MINB;  // persistent trace: RT_BVH_MINB CTAs of 8 warps per SM
     const unsigned sgrid = (unsigned)sm_count * 8u;    // grid-stride kernels
     const bool count = fr.counters != nullptr;
     for (uint32_t g = 0; g < gens; ++g) {
@@ -723,9 +654,9 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
         const TaskQueue& qout = wb.q[(g + 1u) & 1u];
         if (accel == 2) {
             if (count)
-                wave_trace_bvh<true><<<pgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, fetch + g, wb.res_t, wb.res_id, min_t, drain_t, refill_t, dense, fr.counters);
+                wave_trace_bvh<true><<<pgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, fetch + g, wb.res_t, wb.res_id, min_t, drain_t, refill_t, fr.counters);
             else
-                wave_trace_bvh<false><<<pgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, fetch + g, wb.res_t, wb.res_id, min_t, drain_t, refill_t, dense, fr.counters);
+                wave_trace_bvh<false><<<pgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, fetch + g, wb.res_t, wb.res_id, min_t, drain_t, refill_t, fr.counters);
         } else if (accel == 1) {
             // 4 rays per thread x 4 objects per iteration, 2 blocks per SM, 2048-object tiles: the fastest of the
             // configurations swept on the B200 (tools/sweep_filter.sh history in DESIGN.md)
