@@ -105,7 +105,10 @@ __global__ void __launch_bounds__(kBlock) wave_gen(const Frame fr, const TaskQue
 }
 
 // ------------------------------------------------------------------------------------------------ trace: BVH
-constexpr int kPendCap = 8;
+#ifndef RT_PEND_CAP
+#define RT_PEND_CAP 8
+#endif
+constexpr int kPendCap = RT_PEND_CAP;  // queued candidates per lane (a lane stops traversing while it holds one)
 
 // The reference arithmetic for one (ray, object) pair, kept out of line: it is long (two 4x4 transforms,
 // IEEE divides and a square root) and rare, and inlining it into the hot loops thrashes the instruction cache.
@@ -563,8 +566,11 @@ cudaError_t launch_filter(const Scene& sc, const TaskQueue& qin, const uint32_t*
 }
 
 // ------------------------------------------------------------------------------------------------ advance
+#ifndef RT_ADV_MINB
+#define RT_ADV_MINB 3  // resident CTAs per SM the advance kernel is compiled for (80 registers; 2 and 4 measured slower)
+#endif
 template <bool COUNT>
-__global__ void __launch_bounds__(kBlock) wave_advance(const Scene sc, const WaveParams wp, const PathArrays pa, const TaskQueue qin,
+__global__ void __launch_bounds__(kBlock, RT_ADV_MINB) wave_advance(const Scene sc, const WaveParams wp, const PathArrays pa, const TaskQueue qin,
                                                        const TaskQueue qout, const uint32_t* __restrict__ n_in, uint32_t* __restrict__ n_out,
                                                        const float* __restrict__ res_t, const int32_t* __restrict__ res_id,
                                                        const int first, float4* __restrict__ fb, int32_t* __restrict__ aov_id,
@@ -646,6 +652,16 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
     WaveParams wp;
     wp.max_bounces = fr.max_bounces;
     wp.mode = fr.mode;
+    {  // shared-memory carve-out of the trace kernel (percent of the SM's 228 KB; the rest is L1 for the BVH nodes)
+        static const cudaError_t carve = [] {
+            const int pct = env_int("RT_WAVE_CARVEOUT", -1);
+            if (pct < 0) return cudaSuccess;
+            cudaError_t a = cudaFuncSetAttribute(wave_trace_bvh<true>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+            if (a == cudaSuccess) a = cudaFuncSetAttribute(wave_trace_bvh<false>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+            return a;
+        }();
+        if (carve != cudaSuccess) return carve;
+    }
     const unsigned pgrid = (unsigned)sm_count * RT_BVH_MINB;  // persistent trace: RT_BVH_MINB CTAs of 8 warps per SM
     const unsigned sgrid = (unsigned)sm_count * 8u;    // grid-stride kernels
     const bool count = fr.counters != nullptr;
