@@ -130,6 +130,8 @@ typedef enum rt_option {
 const char* rt_last_error(void);
 int rt_abi_version(void);
 
+/* Number of CUDA devices this library can use (compute capability 10.x). */
+int rt_device_count(int* count);
 /* device < 0 selects the current CUDA device. */
 int rt_create(rt_ctx** out, int device);
 int rt_destroy(rt_ctx* ctx);

@@ -383,6 +383,18 @@ extern "C" {
 const char* rt_last_error(void) { return g_last_error.c_str(); }
 int rt_abi_version(void) { return RT_B200_ABI_VERSION; }
 
+int rt_device_count(int* count) {
+    if (!count) return fail(RT_ERR_INVALID, "null argument");
+    *count = 0;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return RT_OK;
+    for (int d = 0; d < n; ++d) {
+        cudaDeviceProp prop;
+        if (cudaGetDeviceProperties(&prop, d) == cudaSuccess && prop.major == 10) ++*count;
+    }
+    return RT_OK;
+}
+
 int rt_create(rt_ctx** out, int device) {
     if (!out) return fail(RT_ERR_INVALID, "null out pointer");
     *out = nullptr;

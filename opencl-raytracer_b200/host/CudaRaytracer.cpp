@@ -4,6 +4,7 @@
 #include <cstring>
 #include <stdexcept>
 #include <string>
+#include <thread>
 
 #include <glm/gtc/type_ptr.hpp>
 
@@ -50,10 +51,10 @@ CudaRaytracer::CudaRaytracer(const std::vector<ObjectData>& objects, const std::
     static_assert(sizeof(cl_float4) == 4 * sizeof(float), "cl_float4 layout");
     check(rt_create(&ctx_, -1), "rt_create");
     try {
-        std::vector<rt_object> objArr;
+        std::vector<rt_object>& objArr = objArr_;
         objArr.reserve(objects.size());
         for (const ObjectData& o : objects) objArr.push_back(marshal(o));
-        std::vector<rt_light> lightArr;
+        std::vector<rt_light>& lightArr = lightArr_;
         lightArr.reserve(lights.size());
         for (const Light& l : lights) lightArr.push_back(marshal(l));
         check(rt_upload_scene(ctx_, objArr.data(), (uint32_t)objArr.size(), lightArr.data(), (uint32_t)lightArr.size()),
@@ -74,16 +75,58 @@ CudaRaytracer::CudaRaytracer(const std::vector<ObjectData>& objects, const std::
 }
 
 CudaRaytracer::~CudaRaytracer() {
+    for (rt_ctx* c : extra_) rt_destroy(c);
     if (pixelDataArr) rt_host_free(pixelDataArr);
     if (ctx_) rt_destroy(ctx_);
 }
 
 cl_float4* CudaRaytracer::Render() {
-    check(rt_render(ctx_, MAX_BOUNCES, mode_, accel_, reinterpret_cast<float*>(pixelDataArr)), "rt_render");
+    float* out = reinterpret_cast<float*>(pixelDataArr);
+    if (extra_.empty()) {
+        check(rt_render(ctx_, MAX_BOUNCES, mode_, accel_, out), "rt_render");
+        return pixelDataArr;
+    }
+    // one host thread per device: each rt_render traces its own row-blocks and copies them into the shared pinned frame
+    std::vector<int> rc(extra_.size() + 1, RT_OK);
+    std::vector<std::string> msg(extra_.size() + 1);
+    std::vector<std::thread> pool;
+    auto run = [&](size_t i) {
+        rt_ctx* c = i == 0 ? ctx_ : extra_[i - 1];
+        rc[i] = rt_render(c, MAX_BOUNCES, mode_, accel_, out);
+        if (rc[i] != RT_OK) msg[i] = rt_last_error();  // the message is thread-local
+    };
+    for (size_t i = 1; i <= extra_.size(); ++i) pool.emplace_back(run, i);
+    run(0);
+    for (std::thread& t : pool) t.join();
+    for (size_t i = 0; i < rc.size(); ++i)
+        if (rc[i] != RT_OK) throw std::runtime_error("CudaRaytracer: rt_render on device " + std::to_string(i) + ": " + msg[i]);
     return pixelDataArr;
 }
 
-void CudaRaytracer::SetOption(rt_option option, long long value) { check(rt_set_option(ctx_, option, value), "rt_set_option"); }
+void CudaRaytracer::SetOption(rt_option option, long long value) {
+    check(rt_set_option(ctx_, option, value), "rt_set_option");
+    for (rt_ctx* c : extra_) check(rt_set_option(c, option, value), "rt_set_option");
+}
+
+unsigned CudaRaytracer::UseDevices(unsigned n) {
+    if (camW_ == 0) throw std::runtime_error("CudaRaytracer: UseDevices needs the pinhole camera (UseCameraIfPinhole) first");
+    int avail = 0;
+    check(rt_device_count(&avail), "rt_device_count");
+    if (n < 1) n = 1;
+    if ((int)n > avail) n = (unsigned)avail;
+    for (rt_ctx* c : extra_) rt_destroy(c);
+    extra_.clear();
+    for (unsigned d = 1; d < n; ++d) {
+        rt_ctx* c = nullptr;
+        check(rt_create(&c, (int)d), "rt_create");
+        extra_.push_back(c);
+        check(rt_upload_scene(c, objArr_.data(), (uint32_t)objArr_.size(), lightArr_.data(), (uint32_t)lightArr_.size()), "rt_upload_scene");
+        check(rt_set_camera(c, camW_, camH_, camZ_), "rt_set_camera");
+        check(rt_set_shard(c, 16, d, n), "rt_set_shard");
+    }
+    check(rt_set_shard(ctx_, n > 1 ? 16 : 1, 0, n), "rt_set_shard");
+    return n;
+}
 
 bool CudaRaytracer::UseCameraIfPinhole(unsigned width, unsigned height) {
     if ((size_t)width * height != rays.size() || rays.empty()) return false;
@@ -98,11 +141,25 @@ bool CudaRaytracer::UseCameraIfPinhole(unsigned width, unsigned height) {
                 return false;
         }
     check(rt_set_camera(ctx_, width, height, zdir), "rt_set_camera");
+    camW_ = width;
+    camH_ = height;
+    camZ_ = zdir;
     return true;
 }
 
 rt_stats CudaRaytracer::Stats() const {
     rt_stats st;
     check(rt_get_stats(ctx_, &st), "rt_get_stats");
+    for (rt_ctx* c : extra_) {
+        rt_stats s;
+        check(rt_get_stats(c, &s), "rt_get_stats");
+        st.rays_primary += s.rays_primary; st.rays_shadow += s.rays_shadow; st.rays_reflect += s.rays_reflect;
+        st.traced_shadow += s.traced_shadow; st.traced_reflect += s.traced_reflect;
+        st.pair_tests += s.pair_tests; st.exact_tests += s.exact_tests; st.node_visits += s.node_visits;
+        st.pixels += s.pixels; st.hit_pixels += s.hit_pixels;
+        st.kernel_launches += s.kernel_launches;
+        if (s.kernel_ms > st.kernel_ms) st.kernel_ms = s.kernel_ms;
+        if (s.total_ms > st.total_ms) st.total_ms = s.total_ms;
+    }
     return st;
 }

@@ -15,6 +15,7 @@
 // extern "C" layer of include/rt_b200.h.
 #pragma once
 
+#include <string>
 #include <vector>
 
 #include "IRaytracer.hpp"
@@ -38,11 +39,21 @@ public:
     // If `rays` is exactly the pinhole grid main() builds (OpenCL-Raytracer.cpp:68-72) for width x height, the rays
     // are generated on the device instead of being uploaded (bit-identical, saves 32 B/ray of HBM and PCIe).
     bool UseCameraIfPinhole(unsigned width, unsigned height);
-    rt_stats Stats() const;
+    // Shard the camera frame over the first n CUDA devices of this process (row-blocks of 16 rows dealt round-robin,
+    // SURVEY.md 8(e)): one context and one host thread per device, every device renders its rows and copies them into
+    // the one pinned frame Render() returns.  Needs UseCameraIfPinhole() first; n = 1 undoes it.  Returns the number of
+    // devices actually used (at most rt_device_count()).  The reference has no multi-device path.
+    unsigned UseDevices(unsigned n);
+    rt_stats Stats() const;  // ray counts summed over the devices, times of the slowest device
     size_t PixelCount() const { return rays.size(); }
 
 private:
     rt_ctx* ctx_ = nullptr;
+    std::vector<rt_ctx*> extra_;  // contexts of devices 1 .. n-1 (UseDevices)
+    std::vector<rt_object> objArr_;  // marshalled scene, kept for UseDevices
+    std::vector<rt_light> lightArr_;
+    unsigned camW_ = 0, camH_ = 0;
+    float camZ_ = 0.f;
     cl_float4* pixelDataArr = nullptr;  // pinned, rays.size() entries
     const unsigned int MAX_BOUNCES;
     rt_mode mode_ = RT_MODE_SHADE_AND_REFLECT;

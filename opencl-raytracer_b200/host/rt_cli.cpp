@@ -32,14 +32,14 @@ static Ray3D screenSpaceToViewSpace(float width, float height, glm::vec2 pos, fl
 static void usage() {
     std::puts("usage: rt_cli --scene file.txt [--width 2560] [--height 1440] [--fov 60] [--bounces 30]\n"
               "              [--mode hittest|shade|sar] [--accel auto|brute|filter|bvh] [--frames 1]\n"
-              "              [--out render.ppm] [--fast-ppm] [--upload-rays]");
+              "              [--gpus 1] [--out render.ppm] [--fast-ppm] [--upload-rays]");
 }
 
 int main(int argc, char** argv) {
     int width = 2560, height = 1440;  // OpenCL-Raytracer.cpp:31
     float fovDeg = 60.f;              // :32
     unsigned bounces = 30;            // :75
-    int frames = 1;
+    int frames = 1, gpus = 1;
     std::string scene, out = "render.ppm";  // :35
     rt_mode mode = RT_MODE_SHADE_AND_REFLECT;
     rt_accel accel = RT_ACCEL_AUTO;
@@ -59,6 +59,7 @@ int main(int argc, char** argv) {
         else if (a == "--fov") fovDeg = (float)std::atof(next());
         else if (a == "--bounces") bounces = (unsigned)std::atoi(next());
         else if (a == "--frames") frames = std::atoi(next());
+        else if (a == "--gpus") gpus = std::atoi(next());
         else if (a == "--out") out = next();
         else if (a == "--fast-ppm") fastPpm = true;
         else if (a == "--upload-rays") uploadRays = true;
@@ -103,9 +104,11 @@ int main(int argc, char** argv) {
         CudaRaytracer tracer(objects, lights, rays, bounces);
         tracer.SetMode(mode);
         tracer.SetAccel(accel);
-        tracer.SetOption(RT_OPT_COUNT_RAYS, 1);
-        if (!uploadRays && tracer.UseCameraIfPinhole((unsigned)width, (unsigned)height))
+        if (!uploadRays && tracer.UseCameraIfPinhole((unsigned)width, (unsigned)height)) {
             std::cout << "Primary rays are the pinhole grid: generated on the device.\n";
+            if (gpus > 1) std::cout << "Frame sharded over " << tracer.UseDevices((unsigned)gpus) << " GPU(s).\n";
+        }
+        tracer.SetOption(RT_OPT_COUNT_RAYS, 1);
         IRaytracer* raytracer = &tracer;
         cl_float4* pixelData = nullptr;
         for (int f = 0; f < frames; ++f) {

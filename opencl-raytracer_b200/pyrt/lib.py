@@ -19,7 +19,7 @@ OPT_PIPELINE, OPT_COUNT_RAYS, OPT_BVH_LEAF, OPT_SKIP_DEAD_RAYS, OPT_READBACK_BAN
 
 # every symbol include/rt_b200.h declares (tests check the library exports all of them)
 ABI_SYMBOLS = (
-    "rt_last_error", "rt_abi_version", "rt_create", "rt_destroy", "rt_set_option", "rt_upload_scene", "rt_set_rays",
+    "rt_last_error", "rt_abi_version", "rt_device_count", "rt_create", "rt_destroy", "rt_set_option", "rt_upload_scene", "rt_set_rays",
     "rt_set_camera", "rt_set_shard", "rt_render", "rt_render_device", "rt_framebuffer", "rt_render_aov", "rt_trace",
     "rt_get_stats", "rt_quantize_rgb8", "rt_host_alloc", "rt_host_free", "rt_host_register", "rt_host_unregister", "rt_measure_fp32_peak", "rt_fp32_peak_detail",
     "rt_ipc_export_framebuffer", "rt_ipc_open", "rt_ipc_close", "rt_readback",
@@ -63,6 +63,7 @@ def load():
         lib.rt_abi_version.restype = C.c_int
         vp, u32, u64, i32, i64 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int, C.c_int64
         sigs = {
+            "rt_device_count": [C.POINTER(i32)],
             "rt_create": [C.POINTER(vp), i32],
             "rt_destroy": [vp],
             "rt_set_option": [vp, i32, i64],

@@ -54,3 +54,25 @@ def test_cli_reports_errors(tmp_path):
     bad.write_text("material m\n===\nprimative cone m\n")
     r = subprocess.run([CLI, "--scene", str(bad), "--out", "none"], capture_output=True, text=True, timeout=60)
     assert r.returncode == 1
+
+
+def test_cli_multi_gpu_equals_single_gpu(rt, tmp_path):
+    """--gpus N: one process, one context and host thread per device, row-blocks of 16 rows round-robin, every device
+    copies its rows into the one pinned frame.  Byte-identical PPM to the 1-GPU run (needs >= 2 GPUs in the box)."""
+    import ctypes
+
+    n = ctypes.c_int(0)
+    assert rt.load().rt_device_count(ctypes.byref(n)) == 0
+    scene = os.path.join(ROOT, "baseline", "_ref", "roundedCube.txt")
+    if n.value < 2 or not (os.path.exists(CLI) and os.path.exists(scene)):
+        pytest.skip("needs two GPUs, build/rt_cli and the staged scene files")
+    outs = []
+    for gpus in (1, min(n.value, 8)):
+        out = str(tmp_path / ("render_%d.ppm" % gpus))
+        r = subprocess.run([CLI, "--scene", scene, "--width", "640", "--height", "356", "--bounces", "30", "--accel", "bvh",
+                            "--gpus", str(gpus), "--fast-ppm", "--out", out], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stdout + r.stderr
+        if gpus > 1:
+            assert "Frame sharded over %d GPU(s)." % gpus in r.stdout
+        outs.append(open(out, "rb").read())
+    assert outs[0] == outs[1]
