@@ -122,6 +122,25 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
+def ncu_traffic(name):
+    """dram__bytes_read + dram__bytes_write of the FIRST launch in a committed ncu summary (profiles/<name>, written by
+    tools/ncu_summary.py from one `ncu --set full` capture of this bench command); (None, None) when it is not there."""
+    path = os.path.join(ROOT, "profiles", name)
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    try:
+        tot, seen = 0.0, 0
+        for line in open(path):
+            f = line.split()
+            if len(f) >= 3 and f[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                tot += float(f[1]) * unit[f[2]]
+                seen += 1
+                if seen == 2:
+                    return tot, "profiles/%s: first wave_trace_bvh launch of the frame (primary rays, the longest of the trace launches)" % name
+    except Exception:
+        pass
+    return None, None
+
+
 def sample_rays(width, height, zdir, n_side=64):
     """A bounded, frame-covering pixel sample: an n_side x n_side lattice of pixels of the full frame."""
     jj = np.linspace(0, height - 1, n_side).astype(np.int64)
@@ -379,16 +398,18 @@ def main():
     else:
         flops = pair_tests * FLOPS_EXACT + shades * FLOPS_SHADE
     achieved_tf = flops / world / (ms_dev * 1e-3) / 1e12
+    traffic, traffic_src = (ncu_traffic("r1_e_wave_trace_bvh_cfg5_8k.txt") if accel_used == 2 and pipeline_used == 1 and args.workload == "cfg5-box"
+                            else (None, None))
     roofline = {
         "kernel": kernel_names[accel_used], "bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
-        "frac": achieved_tf / peak_tf if peak_tf else None, "traffic": None,
+        "frac": achieved_tf / peak_tf if peak_tf else None, "traffic": traffic, "traffic_source": traffic_src,
         "peak_source": "rt_measure_fp32_peak (register-only loops, this GPU, this run: scalar FFMA %.1f, packed FFMA2 %.1f TFLOP/s; "
                        "the larger is the peak and implies %.0f MHz)" % (peak_scalar, peak_packed, peak_mhz),
         "flops_per_launch": flops / world,
         "hbm": {"framebuffer_bytes_per_launch": pixels * 16 / world, "achieved_gbs": pixels * 16 / world / (ms_dev * 1e-3) / 1e9,
                 "peak_gbs": peaks.get("hbm_gbs")},
-        "note": "BVH traversal is bound by divergent node fetches, not by FP32: ncu (profiles/r1_d_wave_trace_bvh_v4_cfg5small.txt, "
-                "1080p frame) shows the L1 data pipe at 67 % of its wavefront peak and the issue slots at 63 %, FMA pipe 23 %; "
+        "note": "BVH traversal is bound by divergent node fetches, not by FP32: ncu (profiles/r1_e_wave_trace_bvh_cfg5_8k.txt, "
+                "this frame, primary-ray launch) shows the L1 data pipe at 63 % of its wavefront peak and the issue slots at 69 %; "
                 "the FP32 fraction is reported for completeness, see roofline_brute for the FP32-bound kernel"
         if accel_used == 2 else "",
     }

@@ -16,3 +16,6 @@ F="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-brute-leg --workl
 $F > $O/${TAG}_bench_filter.json 2>&1 || { echo "filter bench failed"; exit 1; }
 ncu --set full --clock-control none --import-source on -k regex:wave_trace_filter -c 1 -f -o $O/${TAG}_trace_filter $F > $O/${TAG}_ncu_filter.log 2>&1
 ls -la $O | tail -20
+# the dominant kernel on the headline workload itself (8K frame): first two generations (primary rays, shadow rays)
+ncu --set full --clock-control none --import-source on -k regex:wave_trace_bvh -c 2 -f -o $O/${TAG}_trace_bvh_8k $B > $O/${TAG}_ncu_bvh_8k.log 2>&1
+ls -la $O | tail -8
