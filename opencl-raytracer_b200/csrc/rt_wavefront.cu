@@ -54,15 +54,32 @@ __device__ void flush_local(const LocalCounters& lc, Counters* c) {
 #undef RT_FLUSH
 }
 
-// Append one entry per participating lane to a queue: one atomic per warp, order within the warp kept.
-__device__ __forceinline__ uint32_t warp_append(bool emit, uint32_t* counter) {
+// Append one entry per participating thread of the block to a queue: ONE atomic per block, slots of a block
+// contiguous, order within the block kept.  (One atomic per warp -- ballot + popc -- put 1 M same-address atomics per
+// 8K generation on a single counter; they serialise in L2 and cost 6 ms of the 67 ms frame.)  Every thread of the
+// block must call it; sh holds kBlock/32 words.
+__device__ __forceinline__ uint32_t block_append(bool emit, uint32_t* counter, uint32_t* sh) {
+    constexpr unsigned kWarps = kBlock / 32;
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const unsigned m = __ballot_sync(kFull, emit);
-    if (m == 0u) return 0u;
-    const unsigned lane = threadIdx.x & 31u;
-    uint32_t base = 0;
-    if (lane == (unsigned)(__ffs(m) - 1)) base = atomicAdd(counter, (uint32_t)__popc(m));
-    base = __shfl_sync(kFull, base, __ffs(m) - 1);
-    return base + (uint32_t)__popc(m & lanemask_lt());
+    if (lane == 0) sh[warp] = (uint32_t)__popc(m);
+    __syncthreads();
+    if (warp == 0) {
+        const uint32_t c = lane < kWarps ? sh[lane] : 0u;
+        uint32_t incl = c;
+#pragma unroll
+        for (unsigned o = 1; o < kWarps; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(kFull, incl, o);
+            if (lane >= o) incl += v;
+        }
+        const uint32_t total = __shfl_sync(kFull, incl, kWarps - 1);
+        uint32_t base = 0;
+        if (lane == 0 && total) base = atomicAdd(counter, total);
+        base = __shfl_sync(kFull, base, 0);
+        if (lane < kWarps) sh[lane] = base + incl - c;
+    }
+    __syncthreads();
+    return sh[warp] + (uint32_t)__popc(m & lanemask_lt());
 }
 
 // ------------------------------------------------------------------------------------------------ generation 0
@@ -95,7 +112,8 @@ __global__ void __launch_bounds__(kBlock) wave_gen(const Frame fr, const TaskQue
             }
         }
     }
-    const uint32_t slot = warp_append(active, count);
+    __shared__ uint32_t sh_append[kBlock / 32];
+    const uint32_t slot = block_append(active, count, sh_append);
     if (active) {
         q.s[slot] = ray.s;
         q.d[slot] = ray.d;
@@ -165,6 +183,8 @@ __global__ void __launch_bounds__(kBlock, RT_BVH_MINB) wave_trace_bvh(const Scen
             const unsigned idle = __ballot_sync(kFull, !have);
             const unsigned trav = __ballot_sync(kFull, have && !tdone);
             if (idle && !exhausted && (__popc(idle) >= refill_t || trav == 0u)) {
+                // (one same-address atomic per refill; reserving 32..256-ray chunks per warp instead -- guided
+                // self-scheduling -- was measured equal on the 8K frame, fixed chunks slower by their tails)
                 uint32_t base = 0;
                 if (lane == 0) base = atomicAdd(fetch, (uint32_t)__popc(idle));
                 base = __shfl_sync(kFull, base, 0);
@@ -578,8 +598,9 @@ __global__ void __launch_bounds__(kBlock, RT_ADV_MINB) wave_advance(const Scene 
     const uint32_t n = *n_in;
     if (n == 0u) return;
     LocalCounters lc;
-    const uint32_t n_round = (n + 31u) & ~31u;  // whole warps take part in the ballots
-    for (uint32_t i = blockIdx.x * kBlock + threadIdx.x; i < n_round; i += gridDim.x * kBlock) {
+    __shared__ uint32_t sh_append[kBlock / 32];
+    const uint64_t n_round = ((uint64_t)n + kBlock - 1u) / kBlock * kBlock;  // whole blocks take part in the append
+    for (uint64_t i = (uint64_t)blockIdx.x * kBlock + threadIdx.x; i < n_round; i += (uint64_t)gridDim.x * kBlock) {
         StepOut o;
         o.emit = o.write = o.anyhit = false;
         uint32_t p = 0;
@@ -598,7 +619,7 @@ __global__ void __launch_bounds__(kBlock, RT_ADV_MINB) wave_advance(const Scene 
             }
             wave::step<COUNT>(sc, wp, pa, p, first != 0, ray, res, o, lc);
         }
-        const uint32_t slot = warp_append(o.emit, n_out);
+        const uint32_t slot = block_append(o.emit, n_out, sh_append);
         if (o.emit) {
             qout.s[slot] = o.ray.s;
             qout.d[slot] = o.ray.d;
@@ -664,6 +685,8 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
     }
     const unsigned pgrid = (unsigned)sm_count * RT_BVH_MINB;  // persistent trace: RT_BVH_MINB CTAs of 8 warps per SM
     const unsigned sgrid = (unsigned)sm_count * 8u;    // grid-stride kernels
+    static const int adv_mult = env_int("RT_ADV_GRID", 3);  // = resident CTAs per SM; 3..32 measured within 1 %
+    const unsigned agrid = (unsigned)sm_count * (unsigned)adv_mult;  // wave_advance
     const bool count = fr.counters != nullptr;
     for (uint32_t g = 0; g < gens; ++g) {
         const TaskQueue& qin = wb.q[g & 1u];
@@ -686,10 +709,10 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
                 wave_trace_brute<false><<<sgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, wb.res_t, wb.res_id, fr.counters);
         }
         if (count)
-            wave_advance<true><<<sgrid, kBlock, 0, stream>>>(sc, wp, wb.pa, qin, qout, qcount + g, qcount + g + 1, wb.res_t, wb.res_id,
+            wave_advance<true><<<agrid, kBlock, 0, stream>>>(sc, wp, wb.pa, qin, qout, qcount + g, qcount + g + 1, wb.res_t, wb.res_id,
                                                              g == 0 ? 1 : 0, fr.out, fr.hit_id, fr.hit_t, fr.counters);
         else
-            wave_advance<false><<<sgrid, kBlock, 0, stream>>>(sc, wp, wb.pa, qin, qout, qcount + g, qcount + g + 1, wb.res_t, wb.res_id,
+            wave_advance<false><<<agrid, kBlock, 0, stream>>>(sc, wp, wb.pa, qin, qout, qcount + g, qcount + g + 1, wb.res_t, wb.res_id,
                                                               g == 0 ? 1 : 0, fr.out, fr.hit_id, fr.hit_t, fr.counters);
         nl += 2;
     }
