@@ -83,7 +83,7 @@ __device__ __forceinline__ uint32_t block_append(bool emit, uint32_t* counter, u
 }
 
 // ------------------------------------------------------------------------------------------------ generation 0
-__global__ void __launch_bounds__(kBlock) wave_gen(const Frame fr, const TaskQueue q, const PathArrays pa, uint32_t* __restrict__ count) {
+__global__ void __launch_bounds__(kBlock) wave_gen(const Frame fr, const TaskQueue q, const PathArrays pa, uint32_t* __restrict__ count, const uint32_t strip) {
     bool active;
     uint64_t oi = 0;
     Ray ray;
@@ -97,7 +97,14 @@ __global__ void __launch_bounds__(kBlock) wave_gen(const Frame fr, const TaskQue
         }
     } else {
         const uint32_t tiles_x = (fr.width + kTileW - 1) / kTileW;
-        const uint32_t tx = blockIdx.x % tiles_x, ty = blockIdx.x / tiles_x;
+        uint32_t tx = blockIdx.x % tiles_x, ty = blockIdx.x / tiles_x;
+        if (strip > 1u) {  // tiles run down columns inside strips of `strip` tile rows: the queue order is compact in 2-D
+            const uint32_t tiles_y = (fr.local_rows + kTileH - 1) / kTileH;
+            const uint32_t per = tiles_x * strip, st = blockIdx.x / per, in = blockIdx.x % per;
+            const uint32_t h = min(strip, tiles_y - st * strip);
+            tx = in / h;
+            ty = st * strip + in % h;
+        }
         const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
         const uint32_t lx = tx * kTileW + (warp & 3u) * 8u + (lane & 7u);
         const uint32_t ly = ty * kTileH + (warp >> 2) * 4u + (lane >> 3);
@@ -668,7 +675,8 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
         if (launches) *launches = 0;
         return cudaSuccess;
     }
-    wave_gen<<<grid0, kBlock, 0, stream>>>(fr, wb.q[0], wb.pa, qcount + 0);
+    static const int gen_strip = env_int("RT_GEN_STRIP", 64);
+    wave_gen<<<grid0, kBlock, 0, stream>>>(fr, wb.q[0], wb.pa, qcount + 0, (uint32_t)gen_strip);
     ++nl;
     WaveParams wp;
     wp.max_bounces = fr.max_bounces;
