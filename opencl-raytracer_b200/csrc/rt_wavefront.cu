@@ -410,6 +410,53 @@ __device__ __noinline__ void filter_flush(const Scene& sc, const TaskQueue& q, F
     __syncwarp();
 }
 
+template <int OPI, int P>
+struct FilterSurvivors {
+    float2 l[OPI][P];
+    float thr[OPI];
+};
+
+// The rare path of the filter loop: queue the (ray, object) pairs that passed the filter, run full 32-wide batches.
+// obj0: scene index of the iteration's first object; n_valid: objects of the iteration that are not padding.
+template <int RPT, int OPI, int CAP>
+__device__ __noinline__ uint32_t filter_collect(const Scene& sc, const TaskQueue& q, FilterShared<CAP>& fs, float (*best_t)[kBlock],
+                                            int32_t (*best_i)[kBlock], uint32_t warp_base, const FilterSurvivors<OPI, RPT / 2> sv,
+                                            uint32_t obj0, uint32_t n_valid) {
+    constexpr int P = RPT / 2;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    uint32_t batches = 0;  // returned for the exact-test counter (counted per lane, as filter_flush works per lane)
+#pragma unroll
+    for (int o = 0; o < OPI; ++o) {
+        if ((uint32_t)o >= n_valid) continue;  // padding of the last iteration
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            if (sv.l[o][p].x >= sv.thr[o]) {
+                const uint32_t slot = atomicAdd(&fs.cand_n[warp], 1u);
+                fs.cand_obj[warp][slot] = obj0 + o;
+                fs.cand_who[warp][slot] = (uint16_t)((lane << 3) | (2 * p));
+            }
+            if (sv.l[o][p].y >= sv.thr[o]) {
+                const uint32_t slot = atomicAdd(&fs.cand_n[warp], 1u);
+                fs.cand_obj[warp][slot] = obj0 + o;
+                fs.cand_who[warp][slot] = (uint16_t)((lane << 3) | (2 * p + 1));
+            }
+        }
+        __syncwarp();
+        uint32_t have = fs.cand_n[warp];
+        if (have >= 32u) {  // full batches from the tail of the list (the list holds at most CAP entries)
+            do {
+                filter_flush<RPT, CAP>(sc, q, fs, best_t, best_i, warp_base, have - 32u, 32u);
+                ++batches;
+                have -= 32u;
+            } while (have >= 32u);
+            __syncwarp();
+            if (lane == 0) fs.cand_n[warp] = have;
+        }
+        __syncwarp();
+    }
+    return batches;
+}
+
 // RPT rays per thread (even), OPI objects per loop iteration (independent FMA chains for latency hiding), MINB resident
 // blocks per SM, TILE objects per shared-memory tile.
 template <int RPT, int OPI, int MINB, int TILE, bool COUNT>
@@ -488,59 +535,47 @@ __global__ void __launch_bounds__(kBlock, MINB) wave_trace_filter(const Scene sc
                 tile[2 * j + 1] = make_float4(a.z, a.z, e, e);
             }
             __syncthreads();
-            for (uint32_t j = 0; j < cnt_pad; j += OPI) {
+            for (uint32_t j = 0; j < cnt_pad;) {
                 float2 l[OPI][P];
                 float thr[OPI];
-                bool mine = false;
-#pragma unroll
-                for (int o = 0; o < OPI; ++o) {
-                    const float4 A = tile[2 * (j + o)], B = tile[2 * (j + o) + 1];
-                    const float2 ax = make_float2(A.x, A.y), ay = make_float2(A.z, A.w), az = make_float2(B.x, B.y);
-                    thr[o] = B.z;
-#pragma unroll
-                    for (int p = 0; p < P; ++p) {
-                        const float2 dt = __ffma2_rn(ax, UX[p], __ffma2_rn(ay, UY[p], __ffma2_rn(az, UZ[p], NQ[p])));
-                        const float2 w = __ffma2_rn(ax, PX[p], __ffma2_rn(ay, PY[p], __ffma2_rn(az, PZ[p], OO[p])));
-                        l[o][p] = __ffma2_rn(dt, dt, w);
-                    }
-                }
-#pragma unroll
-                for (int o = 0; o < OPI; ++o) {
-                    float m = fmaxf(l[o][0].x, l[o][0].y);
-#pragma unroll
-                    for (int p = 1; p < P; ++p) m = fmaxf(fmaxf(m, l[o][p].x), l[o][p].y);
-                    mine |= m >= thr[o];
-                }
-                if (__any_sync(kFull, mine)) {  // warp-uniform: somebody has a survivor
+                bool any;
+                // The hot loop: OPI objects against the RPT rays of every lane, until somebody in the warp has a survivor
+                // (rare: a few percent of the iterations) or the tile ends -- straight-line code with ONE branch, the
+                // backward one; the survivors are dealt with outside.
+                do {
+                    bool mine = false;
 #pragma unroll
                     for (int o = 0; o < OPI; ++o) {
-                        if (j + o >= cnt) continue;  // padding of the last iteration
+                        const float4 A = tile[2 * (j + o)], B = tile[2 * (j + o) + 1];
+                        const float2 ax = make_float2(A.x, A.y), ay = make_float2(A.z, A.w), az = make_float2(B.x, B.y);
+                        thr[o] = B.z;
 #pragma unroll
                         for (int p = 0; p < P; ++p) {
-                            if (l[o][p].x >= thr[o]) {
-                                const uint32_t slot = atomicAdd(&fs.cand_n[warp], 1u);
-                                fs.cand_obj[warp][slot] = t0 + j + o;
-                                fs.cand_who[warp][slot] = (uint16_t)((lane << 3) | (2 * p));
-                            }
-                            if (l[o][p].y >= thr[o]) {
-                                const uint32_t slot = atomicAdd(&fs.cand_n[warp], 1u);
-                                fs.cand_obj[warp][slot] = t0 + j + o;
-                                fs.cand_who[warp][slot] = (uint16_t)((lane << 3) | (2 * p + 1));
-                            }
+                            const float2 dt = __ffma2_rn(ax, UX[p], __ffma2_rn(ay, UY[p], __ffma2_rn(az, UZ[p], NQ[p])));
+                            const float2 w = __ffma2_rn(ax, PX[p], __ffma2_rn(ay, PY[p], __ffma2_rn(az, PZ[p], OO[p])));
+                            l[o][p] = __ffma2_rn(dt, dt, w);
                         }
-                        __syncwarp();
-                        uint32_t have = fs.cand_n[warp];
-                        if (have >= 32u) {  // full batches from the tail of the list (the list holds at most CAP entries)
-                            do {
-                                filter_flush<RPT, CAP>(sc, q, fs, best_t, best_i, warp_base, have - 32u, 32u);
-                                if (COUNT) lc.exact_tests++;
-                                have -= 32u;
-                            } while (have >= 32u);
-                            __syncwarp();
-                            if (lane == 0) fs.cand_n[warp] = have;
-                        }
-                        __syncwarp();
                     }
+#pragma unroll
+                    for (int o = 0; o < OPI; ++o) {
+                        float m = fmaxf(l[o][0].x, l[o][0].y);
+#pragma unroll
+                        for (int p = 1; p < P; ++p) m = fmaxf(fmaxf(m, l[o][p].x), l[o][p].y);
+                        mine |= m >= thr[o];
+                    }
+                    any = __any_sync(kFull, mine);
+                    j += OPI;
+                } while (!any && j < cnt_pad);
+                if (any) {  // the iteration that just ran (objects j - OPI ...) left survivors
+                    FilterSurvivors<OPI, P> sv;
+#pragma unroll
+                    for (int o = 0; o < OPI; ++o) {
+                        sv.thr[o] = thr[o];
+#pragma unroll
+                        for (int p = 0; p < P; ++p) sv.l[o][p] = l[o][p];
+                    }
+                    const uint32_t batches = filter_collect<RPT, OPI, CAP>(sc, q, fs, best_t, best_i, warp_base, sv, t0 + j - OPI, cnt - (j - OPI));
+                    if (COUNT) lc.exact_tests += batches;
                 }
             }
         }
