@@ -457,6 +457,12 @@ __device__ __noinline__ uint32_t filter_collect(const Scene& sc, const TaskQueue
     return batches;
 }
 
+#ifndef RT_FILTER_RPT  // the configuration wave_render launches (build-time knobs for the A/B sweeps)
+#define RT_FILTER_RPT 4
+#define RT_FILTER_OPI 4
+#define RT_FILTER_MINB 2
+#define RT_FILTER_TILE 2048
+#endif
 // RPT rays per thread (even), OPI objects per loop iteration (independent FMA chains for latency hiding), MINB resident
 // blocks per SM, TILE objects per shared-memory tile.
 template <int RPT, int OPI, int MINB, int TILE, bool COUNT>
@@ -742,7 +748,8 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
         } else if (accel == 1) {
             // 4 rays per thread x 4 objects per iteration, 2 blocks per SM, 2048-object tiles: the fastest of the
             // configurations swept on the B200 (tools/sweep_filter.sh history in DESIGN.md)
-            const cudaError_t fe = launch_filter<4, 4, 2, 2048>(sc, qin, qcount + g, wb.res_t, wb.res_id, fr.counters, count, sm_count, stream);
+            const cudaError_t fe = launch_filter<RT_FILTER_RPT, RT_FILTER_OPI, RT_FILTER_MINB, RT_FILTER_TILE>(sc, qin, qcount + g, wb.res_t, wb.res_id,
+                                                                                                          fr.counters, count, sm_count, stream);
             if (fe != cudaSuccess) return fe;
             ++nl;
         } else {
