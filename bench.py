@@ -398,7 +398,7 @@ def main():
     else:
         flops = pair_tests * FLOPS_EXACT + shades * FLOPS_SHADE
     achieved_tf = flops / world / (ms_dev * 1e-3) / 1e12
-    traffic, traffic_src = (ncu_traffic("r1_e_wave_trace_bvh_cfg5_8k.txt") if accel_used == 2 and pipeline_used == 1 and args.workload == "cfg5-box"
+    traffic, traffic_src = (ncu_traffic("r1_g_wave_trace_bvh_cfg5_8k.txt") if accel_used == 2 and pipeline_used == 1 and args.workload == "cfg5-box"
                             else (None, None))
     roofline = {
         "kernel": kernel_names[accel_used], "bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
@@ -408,8 +408,8 @@ def main():
         "flops_per_launch": flops / world,
         "hbm": {"framebuffer_bytes_per_launch": pixels * 16 / world, "achieved_gbs": pixels * 16 / world / (ms_dev * 1e-3) / 1e9,
                 "peak_gbs": peaks.get("hbm_gbs")},
-        "note": "BVH traversal is bound by divergent node fetches, not by FP32: ncu (profiles/r1_e_wave_trace_bvh_cfg5_8k.txt, "
-                "this frame, primary-ray launch) shows the L1 data pipe at 63 % of its wavefront peak and the issue slots at 69 %; "
+        "note": "BVH traversal is bound by divergent node fetches, not by FP32: ncu (profiles/r1_g_wave_trace_bvh_cfg5_8k.txt, "
+                "this frame, primary-ray launch) shows the L1 data pipe at 64 % of its wavefront peak and the issue slots at 74 %; "
                 "the FP32 fraction is reported for completeness, see roofline_brute for the FP32-bound kernel"
         if accel_used == 2 else "",
     }
