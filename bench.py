@@ -193,6 +193,7 @@ def main():
     ap.add_argument("--pipeline", type=int, default=-1, help="-1 auto, 0 megakernel, 1 wavefront")
     ap.add_argument("--builder", type=int, default=0, help="BVH builder: 0 host SAH, 1 device LBVH")
     ap.add_argument("--bands", type=int, default=0, help="readback bands of rt_render (0 = library default)")
+    ap.add_argument("--lanes", type=int, default=0, help="1: one launch sequence per frame, 2: two half-frames on two streams (0 = library default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-brute-leg", action="store_true")
     args = ap.parse_args()
@@ -252,6 +253,8 @@ def main():
         ctx.set_option(lib.OPT_PIPELINE, args.pipeline)
     if args.bands:
         ctx.set_option(lib.OPT_READBACK_BANDS, args.bands)
+    if args.lanes:
+        ctx.set_option(lib.OPT_LANES, args.lanes)
     if args.builder:
         ctx.set_option(lib.OPT_BVH_BUILDER, args.builder)
     t_up0 = time.perf_counter()

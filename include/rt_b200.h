@@ -123,8 +123,12 @@ typedef enum rt_option {
     RT_OPT_SKIP_DEAD_RAYS = 4, /* 1 (default): do not trace rays whose result is dead; 0: trace every ray the reference traces */
     RT_OPT_BVH_BUILDER = 6,    /* 0 (default): binned SAH on the host in rt_upload_scene; 1: Morton-order radix tree built on the
                                   device (scenes that change every frame: ~1 ms instead of ~150 ms per 10^5 objects, a looser tree) */
-    RT_OPT_READBACK_BANDS = 5  /* rt_render of a large whole frame: bands of rows whose readback overlaps the next band's kernels
-                                  (geometrically shrinking, default 2; 1 = render the frame, then copy it) */
+    RT_OPT_LANES = 7,      /* 2 (default): camera launches of the wavefront pipeline run as two halves on two streams, each filling the
+                              thin generation tails of the other; 1: one launch sequence */
+    RT_OPT_READBACK_BANDS = 5  /* rt_render of a large camera frame (or shard of one): bands of rows / row-blocks whose readback
+                                  overlaps the next band's kernels, shrinking geometrically by the measured kernel : copy time
+                                  ratio of the previous frame.  0 (default) = 1..4 bands chosen from the measured times, n = n bands,
+                                  1 = render everything, then copy it */
 } rt_option;
 
 const char* rt_last_error(void);

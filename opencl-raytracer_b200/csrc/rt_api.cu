@@ -61,7 +61,8 @@ struct DevBuf {
 
 struct rt_ctx {
     int device = 0;
-    cudaStream_t stream = nullptr, copy_stream = nullptr;
+    cudaStream_t stream = nullptr, copy_stream = nullptr, lane_stream = nullptr;
+    cudaEvent_t lane_go = nullptr, lane_done = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
     static const int kMaxBands = 16;
     cudaEvent_t band_done[kMaxBands] = {};
@@ -104,7 +105,10 @@ struct rt_ctx {
     uint32_t last_launches = 1;
 
     // options
-    int opt_pipeline = -1, opt_count = 0, opt_leaf = 1, opt_skip_dead = 1, opt_bands = 2, opt_builder = 0;
+    int opt_pipeline = -1, opt_count = 0, opt_leaf = 1, opt_skip_dead = 1, opt_bands = 0, opt_builder = 0, opt_lanes = 2;
+    // banded readback: kernel time : copy time of the same rows, measured on the previous banded frame
+    double band_ratio = 7.0, band_copy_ms = 0.0, band_kernel_ms = 0.0;  // copy / kernel time of the whole local frame
+    cudaEvent_t copy_ev[2] = {};
 
     rt_stats stats;
     float fp32_peak_tf[2] = {0.f, 0.f};  // last rt_measure_fp32_peak: scalar FFMA loop, packed FFMA2 loop
@@ -200,47 +204,82 @@ int check_render_args(rt_ctx* c, int mode, int accel) {
 }
 
 uint64_t n_pixels(const rt_ctx* c) { return c->use_camera ? (uint64_t)c->width * c->height : c->n_rays; }
+uint64_t local_pixels(const rt_ctx* c) { return c->use_camera ? (uint64_t)shard_rows(c) * c->width : c->n_rays; }
 
-// band >= 0 (whole-frame camera renders only): the frame is cut into n_bands contiguous bands of rows so that the
-// readback of a finished band overlaps the next band's kernels.  Every band costs the pipeline its ramp-up and its
-// thin last generations again, and the copy is ~7x faster than the kernels of the same rows, so the bands shrink
-// geometrically (7 : 1 for two bands): only the last, small band's copy is left exposed.
-void band_range(const rt_ctx* c, int band, int n_bands, uint32_t* r0, uint32_t* r1) {
+// band >= 0 (camera renders on the wavefront pipeline): the context's part of the frame is cut into n_bands
+// contiguous bands so that the readback of a finished band (copy stream) overlaps the next band's kernels.  The unit
+// is one row (whole frame) or one owned row-block (sharded frame).  Every band costs the pipeline its ramp-up and its
+// thin last generations again, and the copy is faster than the kernels of the same rows, so the bands shrink
+// geometrically by band_ratio = kernel time : copy time, measured on the previous frame (7 : 1 on one GPU over an
+// idle PCIe link, < 2 : 1 when 8 ranks share the host's ingest bandwidth): only the last, small band's copy is exposed.
+uint32_t band_units(const rt_ctx* c) {
+    if (c->n_shards <= 1) return c->height;
+    const uint32_t n_blocks = (c->height + c->block_rows - 1) / c->block_rows;
+    return n_blocks > c->shard ? (n_blocks - c->shard + c->n_shards - 1) / c->n_shards : 0u;
+}
+void band_range(const rt_ctx* c, int band, int n_bands, uint32_t* u0, uint32_t* u1) {
+    const uint32_t units = band_units(c);
+    const double q = 1.0 / c->band_ratio;
     double total = 0.0, w = 1.0;
-    for (int i = 0; i < n_bands; ++i, w /= 7.0) total += w;
+    for (int i = 0; i < n_bands; ++i, w *= q) total += w;
     double acc = 0.0;
     w = 1.0;
     uint32_t start = 0, end = 0;
-    for (int i = 0; i <= band; ++i, w /= 7.0) {
+    for (int i = 0; i <= band; ++i, w *= q) {
         start = end;
         acc += w;
-        end = i == n_bands - 1 ? c->height : std::min(c->height, (uint32_t)(acc / total * c->height + 0.5));
+        end = i == n_bands - 1 ? units : std::min(units, (uint32_t)(acc / total * units + 0.5));
         if (end < start) end = start;
     }
-    *r0 = start;
-    *r1 = end;
+    *u0 = start;
+    *u1 = end;
 }
-uint32_t band_rows(const rt_ctx* c, int n_bands) {  // rows of the largest band (the first)
-    uint32_t r0, r1;
-    band_range(c, 0, n_bands, &r0, &r1);
-    return r1 - r0;
+// Number of bands when the caller leaves it open: the exposed copy (the last band's) against the cost of one more band
+// (its ramp-up and thin last generations: measured 0.8 ms at one GPU per 8K frame, 1.4 ms per band at 8 GPUs).
+int auto_bands(const rt_ctx* c) {
+    if (c->opt_bands > 0) return c->opt_bands;
+    if (!(c->band_copy_ms > 0.0)) return 2;  // nothing measured yet
+    const double per_band = std::max(1.2, 0.03 * c->band_kernel_ms), q = 1.0 / c->band_ratio;
+    int best = 1;
+    double best_cost = c->band_copy_ms, total = 1.0, w = 1.0;
+    for (int n = 2; n <= 4; ++n) {
+        w *= q;
+        total += w;
+        const double cost = (n - 1) * per_band + c->band_copy_ms * w / total;
+        if (cost < best_cost) {
+            best_cost = cost;
+            best = n;
+        }
+    }
+    return best;
 }
-
-void fill_frame_desc(rt_ctx* c, rt::Frame& fr, uint32_t max_bounces, int mode, float4* out, int band = -1, int n_bands = 1) {
+// Frame descriptor.  Camera frames are described by a range [u0, u1) of the context's units (band_units(): rows of the
+// whole frame, or owned row-blocks of a shard); u1 == 0 means "everything" (and is the only form for explicit rays).
+void fill_frame_desc(rt_ctx* c, rt::Frame& fr, uint32_t max_bounces, int mode, float4* out, uint32_t u0 = 0, uint32_t u1 = 0) {
     memset(&fr, 0, sizeof fr);
     fr.rays = c->use_camera ? nullptr : c->d_rays.p;
     fr.width = c->width;
     fr.height = c->height;
     fr.zdir = c->zdir;
-    if (band >= 0) {
-        uint32_t r0, r1;
-        band_range(c, band, n_bands, &r0, &r1);
-        fr.block_rows = std::max(r1 - r0, 1u);
+    if (c->use_camera && u1 > 0 && c->n_shards <= 1) {  // rows u0 .. u1
+        fr.block_rows = std::max(u1 - u0, 1u);
         fr.shard = 0;
         fr.n_shards = 1;
-        fr.row0 = r0;
-        fr.local_rows = r1 - r0;
-        fr.n_local = (uint64_t)(r1 - r0) * c->width;
+        fr.row0 = u0;
+        fr.local_rows = u1 - u0;
+        fr.n_local = (uint64_t)(u1 - u0) * c->width;
+    } else if (c->use_camera && u1 > 0) {  // owned row-blocks u0 .. u1 of the shard
+        fr.block_rows = c->block_rows;
+        fr.shard = c->shard;
+        fr.n_shards = c->n_shards;
+        fr.lrow0 = u0 * c->block_rows;
+        fr.local_rows = (u1 - u0) * c->block_rows;
+        uint64_t rows = 0;
+        for (uint32_t u = u0; u < u1; ++u) {
+            const uint32_t g = (c->shard + u * c->n_shards) * c->block_rows;
+            rows += g < c->height ? std::min(c->block_rows, c->height - g) : 0u;
+        }
+        fr.n_local = rows * c->width;
     } else {
         fr.block_rows = c->use_camera ? c->block_rows : 1;
         fr.shard = c->use_camera ? c->shard : 0;
@@ -287,7 +326,9 @@ int pick_pipeline(const rt_ctx* c, int accel) {
     return (accel != RT_ACCEL_BRUTE && c->objs.size() > 48) ? 1 : 0;
 }
 
-int ensure_wave_buffers(rt_ctx* c, uint64_t capacity, uint32_t gens, rt::WaveBuffers& wb) {
+// Wavefront buffers for `capacity` paths, handed out as two halves (lanes) that run on two streams; lane 0 alone may
+// use everything (wb[0].capacity == capacity).
+int ensure_wave_buffers(rt_ctx* c, uint64_t capacity, uint32_t gens, rt::WaveBuffers wb[2]) {
     if (capacity >= (1ull << 31)) return fail(RT_ERR_INVALID, "too many rays for one wavefront context");
     RT_CUDA(c->w_acc.ensure(capacity));
     RT_CUDA(c->w_refl.ensure(capacity));
@@ -302,72 +343,106 @@ int ensure_wave_buffers(rt_ctx* c, uint64_t capacity, uint32_t gens, rt::WaveBuf
     }
     RT_CUDA(c->w_res_t.ensure(capacity));
     RT_CUDA(c->w_res_id.ensure(capacity));
-    RT_CUDA(c->w_counts.ensure(2 * (size_t)(gens + 2)));
-    wb.pa.acc = c->w_acc.p;
-    wb.pa.refl = c->w_refl.p;
-    wb.pa.P = c->w_P.p;
-    wb.pa.Nm = c->w_Nm.p;
-    wb.pa.Rc = c->w_Rc.p;
-    wb.pa.out = c->w_out.p;
-    for (int i = 0; i < 2; ++i) {
-        wb.q[i].s = c->w_qs[i].p;
-        wb.q[i].d = c->w_qd[i].p;
-        wb.q[i].path = c->w_qpath[i].p;
+    const size_t per_lane = 2 * (size_t)(gens + 2);
+    RT_CUDA(c->w_counts.ensure(2 * per_lane));
+    const uint64_t half = (capacity / 2) & ~(uint64_t)255;  // lane 1 starts here
+    for (int l = 0; l < 2; ++l) {
+        const uint64_t o = l ? half : 0;
+        wb[l].pa.acc = c->w_acc.p + o;
+        wb[l].pa.refl = c->w_refl.p + o;
+        wb[l].pa.P = c->w_P.p + o;
+        wb[l].pa.Nm = c->w_Nm.p + o;
+        wb[l].pa.Rc = c->w_Rc.p + o;
+        wb[l].pa.out = c->w_out.p + o;
+        for (int i = 0; i < 2; ++i) {
+            wb[l].q[i].s = c->w_qs[i].p + o;
+            wb[l].q[i].d = c->w_qd[i].p + o;
+            wb[l].q[i].path = c->w_qpath[i].p + o;
+        }
+        wb[l].res_t = c->w_res_t.p + o;
+        wb[l].res_id = c->w_res_id.p + o;
+        wb[l].counts = c->w_counts.p + l * per_lane;
+        wb[l].n_counts = (uint32_t)(per_lane / 2);
+        wb[l].capacity = l ? capacity - half : capacity;
     }
-    wb.res_t = c->w_res_t.p;
-    wb.res_id = c->w_res_id.p;
-    wb.counts = c->w_counts.p;
-    wb.n_counts = (uint32_t)(c->w_counts.n / 2);
-    wb.capacity = capacity;
     return RT_OK;
 }
 
-// kernels of one render on c->stream, bracketed by ev0/ev1
+// Kernels of one render, bracketed by ev0/ev1 on c->stream.  band >= 0: band `band` of n_bands of a banded render (ev0
+// stays at the start of band 0).  On the wavefront pipeline a camera launch is split into two halves (lanes) that run
+// on two streams with their own queues: every kernel of the pipeline is followed by the same kernel of the other lane,
+// whose blocks move in as the first one's persistent blocks retire -- the thin tail of every generation (and the
+// latency of the nearly empty last generations) is filled with the other lane's work.  RT_OPT_LANES = 1 turns it off.
 int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float4* out, int* accel_used, bool aov_only = false,
                      int band = -1, int n_bands = 1) {
     int rc = sync_scene(c);
     if (rc != RT_OK) return rc;
     accel = pick_accel(c, accel);
     *accel_used = accel;
-    rt::Frame fr;
-    fill_frame_desc(c, fr, max_bounces, mode, out, band, n_bands);
-    if (aov_only) {
-        fr.hit_id = c->d_hit_id.p;
-        fr.hit_t = c->d_hit_t.p;
-    }
+    const int pipeline = pick_pipeline(c, accel);
+    c->last_pipeline = pipeline;
     if (c->opt_count) {
         RT_CUDA(c->d_counters.ensure(1));
         if (band <= 0) RT_CUDA(cudaMemsetAsync(c->d_counters.p, 0, sizeof(rt::Counters), c->stream));
-        fr.counters = c->d_counters.p;
     }
-    const int pipeline = pick_pipeline(c, accel);
-    c->last_pipeline = pipeline;
     if (band <= 0) c->last_launches = 0;
-    if (band > 0) {  // later bands of a banded render: kernels only, ev0 stays at the start of band 0
-        if (fr.n_local == 0) return RT_OK;
-        uint32_t gens = rt::wave_max_generations(max_bounces, c->scene.n_lights, mode);
-        rt::WaveBuffers wb;
-        rc = ensure_wave_buffers(c, (uint64_t)band_rows(c, n_bands) * c->width, gens, wb);
+
+    if (pipeline == 1) {
+        const uint32_t gens = rt::wave_max_generations(max_bounces, c->scene.n_lights, mode);
+        if (gens > 4096) return fail(RT_ERR_INVALID, "max_bounces x lights too large for the wavefront pipeline; use RT_OPT_PIPELINE 0");
+        // unit range of this launch
+        uint32_t u0 = 0, u1 = 0;
+        if (c->use_camera) {
+            if (band >= 0)
+                band_range(c, band, n_bands, &u0, &u1);
+            else
+                u1 = band_units(c);
+            if (u1 == u0) {
+                if (band <= 0) {
+                    RT_CUDA(cudaEventRecord(c->ev0, c->stream));
+                    RT_CUDA(cudaEventRecord(c->ev1, c->stream));
+                }
+                return RT_OK;
+            }
+        }
+        const uint64_t unit_px = (uint64_t)c->width * (c->n_shards <= 1 ? 1u : c->block_rows);
+        rt::WaveBuffers wb[2];
+        // sized for the whole local frame (the band split moves from frame to frame), + slack for the lane split
+        rc = ensure_wave_buffers(c, c->use_camera ? local_pixels(c) + 2 * unit_px + 512 : c->n_rays, gens, wb);
         if (rc != RT_OK) return rc;
-        uint32_t nl = 0;
-        RT_CUDA(rt::wave_render(c->scene, fr, wb, accel, (uint32_t)c->opt_leaf, c->sm_count, &nl, c->stream));
-        c->last_launches += nl;
+        rt::Frame fr[2];
+        const bool lanes = c->use_camera && !aov_only && c->opt_lanes > 1 && u1 - u0 >= 8 && (uint64_t)(u1 - u0) * unit_px >= (1ull << 20);
+        const uint32_t um = lanes ? u0 + (u1 - u0 + 1) / 2 : u1;
+        fill_frame_desc(c, fr[0], max_bounces, mode, out, u0, um);
+        if (lanes) fill_frame_desc(c, fr[1], max_bounces, mode, out, um, u1);
+        if (aov_only) {
+            fr[0].hit_id = c->d_hit_id.p;
+            fr[0].hit_t = c->d_hit_t.p;
+        }
+        if (fr[0].n_local > wb[0].capacity || (lanes && (fr[0].n_local > wb[0].capacity - wb[1].capacity || fr[1].n_local > wb[1].capacity)))
+            return fail(RT_ERR_INVALID, "internal: wavefront buffers too small for the launch");
+        if (band <= 0) RT_CUDA(cudaEventRecord(c->ev0, c->stream));
+        uint32_t nl = 0, nl1 = 0;
+        if (lanes) {
+            RT_CUDA(cudaEventRecord(c->lane_go, c->stream));  // lane 1 starts after everything queued before this launch
+            RT_CUDA(cudaStreamWaitEvent(c->lane_stream, c->lane_go, 0));
+        }
+        if (fr[0].n_local > 0) RT_CUDA(rt::wave_render(c->scene, fr[0], wb[0], accel, (uint32_t)c->opt_leaf, c->sm_count, &nl, c->stream));
+        if (lanes) {
+            if (fr[1].n_local > 0)
+                RT_CUDA(rt::wave_render(c->scene, fr[1], wb[1], accel, (uint32_t)c->opt_leaf, c->sm_count, &nl1, c->lane_stream));
+            RT_CUDA(cudaEventRecord(c->lane_done, c->lane_stream));
+            RT_CUDA(cudaStreamWaitEvent(c->stream, c->lane_done, 0));
+        }
+        c->last_launches += nl + nl1;
         RT_CUDA(cudaEventRecord(c->ev1, c->stream));
         return RT_OK;
     }
-    if (pipeline == 1 && fr.n_local > 0) {
-        uint32_t gens = rt::wave_max_generations(max_bounces, c->scene.n_lights, mode);
-        if (gens > 4096) return fail(RT_ERR_INVALID, "max_bounces x lights too large for the wavefront pipeline; use RT_OPT_PIPELINE 0");
-        rt::WaveBuffers wb;
-        // camera tiles may include a ragged edge; capacity counts real pixels only
-        rc = ensure_wave_buffers(c, band == 0 ? (uint64_t)band_rows(c, n_bands) * c->width : fr.n_local, gens, wb);
-        if (rc != RT_OK) return rc;
-        RT_CUDA(cudaEventRecord(c->ev0, c->stream));
-        uint32_t nl = 0;
-        RT_CUDA(rt::wave_render(c->scene, fr, wb, accel, (uint32_t)c->opt_leaf, c->sm_count, &nl, c->stream));
-        c->last_launches = nl;
-        RT_CUDA(cudaEventRecord(c->ev1, c->stream));
-        return RT_OK;
+    rt::Frame fr;
+    fill_frame_desc(c, fr, max_bounces, mode, out);
+    if (aov_only) {
+        fr.hit_id = c->d_hit_id.p;
+        fr.hit_t = c->d_hit_t.p;
     }
     c->last_launches = 1;
     RT_CUDA(cudaEventRecord(c->ev0, c->stream));
@@ -419,6 +494,10 @@ int rt_create(rt_ctx** out, int device) {
     bool bands_ok = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) == cudaSuccess;
     for (int i = 0; i < rt_ctx::kMaxBands && bands_ok; ++i)
         bands_ok = cudaEventCreateWithFlags(&c->band_done[i], cudaEventDisableTiming) == cudaSuccess;
+    bands_ok = bands_ok && cudaEventCreate(&c->copy_ev[0]) == cudaSuccess && cudaEventCreate(&c->copy_ev[1]) == cudaSuccess;
+    bands_ok = bands_ok && cudaStreamCreateWithFlags(&c->lane_stream, cudaStreamNonBlocking) == cudaSuccess &&
+               cudaEventCreateWithFlags(&c->lane_go, cudaEventDisableTiming) == cudaSuccess &&
+               cudaEventCreateWithFlags(&c->lane_done, cudaEventDisableTiming) == cudaSuccess;
     if (!bands_ok || cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&c->ev0) != cudaSuccess ||
         cudaEventCreate(&c->ev1) != cudaSuccess || cudaEventCreate(&c->ev2) != cudaSuccess) {
         delete c;
@@ -442,8 +521,13 @@ int rt_destroy(rt_ctx* c) {
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->ev2) cudaEventDestroy(c->ev2);
+    for (int i = 0; i < 2; ++i)
+        if (c->copy_ev[i]) cudaEventDestroy(c->copy_ev[i]);
     for (int i = 0; i < rt_ctx::kMaxBands; ++i)
         if (c->band_done[i]) cudaEventDestroy(c->band_done[i]);
+    if (c->lane_go) cudaEventDestroy(c->lane_go);
+    if (c->lane_done) cudaEventDestroy(c->lane_done);
+    if (c->lane_stream) cudaStreamDestroy(c->lane_stream);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -467,8 +551,12 @@ int rt_set_option(rt_ctx* c, int option, int64_t value) {
             c->scene_dirty = true;
             return RT_OK;
         case RT_OPT_READBACK_BANDS:
-            if (value < 1 || value > rt_ctx::kMaxBands) return fail(RT_ERR_INVALID, "readback bands must be 1..16");
+            if (value < 0 || value > rt_ctx::kMaxBands) return fail(RT_ERR_INVALID, "readback bands must be 0 (auto) or 1..16");
             c->opt_bands = (int)value;
+            return RT_OK;
+        case RT_OPT_LANES:
+            if (value < 1 || value > 2) return fail(RT_ERR_INVALID, "lanes must be 1 or 2");
+            c->opt_lanes = (int)value;
             return RT_OK;
         default: return fail(RT_ERR_INVALID, "unknown option");
     }
@@ -556,34 +644,57 @@ int rt_render(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float* host_
     if (!host_out) return fail(RT_ERR_INVALID, "null output buffer");
     RT_CUDA(cudaSetDevice(c->device));
     int used = 0;
-    // Whole-frame camera renders on the wavefront pipeline are cut into bands of rows: the device->host copy of a
-    // finished band (copy stream) overlaps the kernels of the next one (compute stream).
-    const bool banded = c->use_camera && c->n_shards == 1 && c->opt_bands > 1 && (uint64_t)c->width * c->height >= (1ull << 22) &&
-                        c->height >= (uint32_t)c->opt_bands && c->have_scene && pick_pipeline(c, pick_accel(c, accel)) == 1;
+    // Camera renders on the wavefront pipeline are cut into bands (rows, or the shard's row-blocks): the device->host
+    // copy of a finished band (copy stream) overlaps the kernels of the next one (compute stream).
+    const int nb = auto_bands(c);
+    const bool banded = c->use_camera && nb > 1 && local_pixels(c) >= (1ull << 21) && band_units(c) >= (uint32_t)(4 * nb) &&
+                        c->have_scene && pick_pipeline(c, pick_accel(c, accel)) == 1;
     if (banded) {
-        const int nb = c->opt_bands;
+        uint32_t units0 = 0;  // units of the first band: its copy is timed for the next frame's split
         for (int b = 0; b < nb; ++b) {
             rc = render_on_device(c, max_bounces, mode, accel, c->d_fb.p, &used, false, b, nb);
             if (rc != RT_OK) return rc;
-            uint32_t r0, r1;
-            band_range(c, b, nb, &r0, &r1);
-            if (r1 == r0) continue;
+            uint32_t u0, u1;
+            band_range(c, b, nb, &u0, &u1);
+            if (u1 == u0) continue;
             RT_CUDA(cudaEventRecord(c->band_done[b], c->stream));
             RT_CUDA(cudaStreamWaitEvent(c->copy_stream, c->band_done[b], 0));
-            const uint64_t first = (uint64_t)r0 * c->width, cnt = (uint64_t)(r1 - r0) * c->width;
-            RT_CUDA(cudaMemcpyAsync(host_out + 4 * first, c->d_fb.p + first, cnt * sizeof(float4), cudaMemcpyDeviceToHost, c->copy_stream));
+            if (b == 0) RT_CUDA(cudaEventRecord(c->copy_ev[0], c->copy_stream));
+            if (c->n_shards <= 1) {
+                const uint64_t first = (uint64_t)u0 * c->width, cnt = (uint64_t)(u1 - u0) * c->width;
+                RT_CUDA(cudaMemcpyAsync(host_out + 4 * first, c->d_fb.p + first, cnt * sizeof(float4), cudaMemcpyDeviceToHost, c->copy_stream));
+            } else {
+                for (uint32_t u = u0; u < u1; ++u) {
+                    const uint32_t row = (c->shard + u * c->n_shards) * c->block_rows;
+                    if (row >= c->height) break;
+                    const uint64_t first = (uint64_t)row * c->width, cnt = (uint64_t)std::min(c->block_rows, c->height - row) * c->width;
+                    RT_CUDA(cudaMemcpyAsync(host_out + 4 * first, c->d_fb.p + first, cnt * sizeof(float4), cudaMemcpyDeviceToHost, c->copy_stream));
+                }
+            }
+            if (b == 0) {
+                RT_CUDA(cudaEventRecord(c->copy_ev[1], c->copy_stream));
+                units0 = u1 - u0;
+            }
         }
         RT_CUDA(cudaEventRecord(c->band_done[0], c->copy_stream));
         RT_CUDA(cudaStreamWaitEvent(c->stream, c->band_done[0], 0));  // ev2 on the compute stream, after the last copy
         RT_CUDA(cudaEventRecord(c->ev2, c->stream));
         RT_CUDA(cudaStreamSynchronize(c->stream));
-        rc = collect_stats(c, used, n_pixels(c), 1);
+        rc = collect_stats(c, used, local_pixels(c), 1);
         if (rc != RT_OK) return rc;
-        float ms = 0.f, ms2 = 0.f;
+        float ms = 0.f, ms2 = 0.f, cp = 0.f;
         RT_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
         RT_CUDA(cudaEventElapsedTime(&ms2, c->ev0, c->ev2));
         c->stats.kernel_ms = ms;  // kernels of all bands (copies of earlier bands run underneath)
         c->stats.total_ms = ms2;
+        // next frame's split: kernel time per unit : copy time per unit (the first band's copy, as fast as the link and
+        // the other ranks' copies let it be)
+        if (units0 && cudaEventElapsedTime(&cp, c->copy_ev[0], c->copy_ev[1]) == cudaSuccess && cp > 0.f && ms > 0.f) {
+            const double r = ((double)ms / band_units(c)) / ((double)cp / units0);
+            c->band_ratio = std::min(16.0, std::max(1.25, 0.5 * c->band_ratio + 0.5 * r));
+            c->band_copy_ms = (double)cp / units0 * band_units(c);
+            c->band_kernel_ms = ms;
+        }
         return RT_OK;
     }
     rc = render_on_device(c, max_bounces, mode, accel, c->d_fb.p, &used);

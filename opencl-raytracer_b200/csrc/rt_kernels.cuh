@@ -27,7 +27,8 @@ struct Frame {
     // shard: row-blocks of block_rows rows dealt round-robin; this context owns b % n_shards == shard
     uint32_t block_rows, shard, n_shards;
     uint32_t row0;            // added to every row (a band of a banded whole-frame render; 0 otherwise)
-    uint32_t local_rows;      // rows of this shard (camera) -- local image is width x local_rows
+    uint32_t lrow0;           // first local row of this launch (a band of a banded sharded render; 0 otherwise)
+    uint32_t local_rows;      // rows of this shard (camera) handled by this launch -- local image is width x local_rows
     uint64_t n_local;         // pixels / rays handled by this launch
     uint32_t max_bounces;
     int mode;                 // rt_mode

@@ -110,7 +110,8 @@ __global__ void __launch_bounds__(kBlock) wave_gen(const Frame fr, const TaskQue
         const uint32_t ly = ty * kTileH + (warp >> 2) * 4u + (lane >> 3);
         active = lx < fr.width && ly < fr.local_rows;
         if (active) {
-            const uint32_t blk = ly / fr.block_rows, rib = ly % fr.block_rows;
+            const uint32_t lrow = fr.lrow0 + ly;
+            const uint32_t blk = lrow / fr.block_rows, rib = lrow % fr.block_rows;
             const uint32_t row = fr.row0 + (blk * fr.n_shards + fr.shard) * fr.block_rows + rib;
             active = row < fr.height;
             if (active) {

@@ -234,6 +234,69 @@ def test_banded_readback_equals_plain_render(rt, ctx):
         assert (s1.rays_primary, s1.rays_shadow, s1.rays_reflect, s1.traced_shadow, s1.traced_reflect, s1.hit_pixels, s1.pixels) == ref_counts
 
 
+def test_two_lanes_equal_one_launch_sequence(rt, ctx, oracle_mod):
+    """RT_OPT_LANES: a large camera launch runs as two halves on two streams with separate queues.  Same frame, same
+    ray counts as the single launch sequence -- whole frame, ragged odd row count, and as a shard; a pixel lattice of
+    the frame is also checked against the oracle."""
+    objs, lights = S.synthetic_scene(3000, 300)
+    W, H = 2048, 1537
+    z = T.camera_zdir(H)
+    ctx.set_option(rt.OPT_COUNT_RAYS, 1)
+    ctx.set_option(rt.OPT_READBACK_BANDS, 1)
+    ctx.upload_scene(objs, lights)
+    ctx.set_camera(W, H, z)
+    res = {}
+    for lanes in (1, 2):
+        ctx.set_option(rt.OPT_LANES, lanes)
+        out = ctx.render(4, 2, 2).copy()
+        s = ctx.stats()
+        res[lanes] = (out, (s.rays_primary, s.rays_shadow, s.rays_reflect, s.traced_shadow, s.traced_reflect, s.hit_pixels, s.pixels))
+        ctx.set_shard(16, 1, 2)
+        part = np.full((W * H, 4), -2.0, dtype=np.float32)
+        ctx.render(4, 2, 2, out=part)
+        res[lanes] += (part,)
+        ctx.set_shard(1, 0, 1)
+    assert res[1][1] == res[2][1] and res[2][1][-1] == W * H
+    assert np.array_equal(res[1][0], res[2][0])
+    assert np.array_equal(res[1][2], res[2][2])
+    rows = np.arange(3, H, 97)
+    rays = T.camera_rays(W, H, z, rows=rows)[::53]
+    idx = (rows[:, None] * W + np.arange(W)[None, :]).reshape(-1)[::53]
+    ref, *_ = oracle_mod.port_render(2, 4, objs, lights, rays)
+    assert_colours_close(res[2][0][idx], ref)
+
+
+def test_banded_readback_of_a_sharded_frame(rt):
+    """The multi-GPU end-to-end path bands too: a shard's row-blocks are rendered and copied in bands (split adapted from
+    the previous frame's kernel : copy time).  Two shards, every band count incl. auto, two frames each (the second one
+    uses the adapted split): together they must reproduce the unsharded, unbanded frame bit for bit."""
+    objs, lights = S.synthetic_scene(3000, 300)
+    W, H = 2048, 2069  # 130 row-blocks of 16, the last one ragged; each shard >= 2 Mpixel
+    z = T.camera_zdir(H)
+    with rt.Context(0) as c:
+        c.set_option(rt.OPT_READBACK_BANDS, 1)
+        c.upload_scene(objs, lights)
+        c.set_camera(W, H, z)
+        whole = c.render(4, 2, 2).copy()
+    for bands in (0, 3, 8):
+        out = np.full((W * H, 4), -7.0, dtype=np.float32)
+        total = 0
+        for s in range(2):
+            with rt.Context(0) as c:
+                c.set_option(rt.OPT_READBACK_BANDS, bands)
+                c.set_option(rt.OPT_COUNT_RAYS, 1)
+                c.upload_scene(objs, lights)
+                c.set_camera(W, H, z)
+                c.set_shard(16, s, 2)
+                c.render(4, 2, 2, out=out)
+                first = out.copy()
+                c.render(4, 2, 2, out=out)  # second frame: split adapted to the measured copy time
+                assert np.array_equal(out, first)
+                total += c.stats().pixels
+        assert total == W * H
+        assert np.array_equal(out, whole)
+
+
 @pytest.mark.parametrize("second_type", [T.BOX, T.TRIANGLE])
 def test_device_built_tree_equals_oracle(rt, ctx, oracle_mod, second_type):
     """RT_OPT_BVH_BUILDER = 1: Morton-order radix tree built on the device (rt_lbvh.cu).  A different tree, the same hits."""
