@@ -127,7 +127,7 @@ typedef enum rt_option {
                               thin generation tails of the other; 1: one launch sequence */
     RT_OPT_READBACK_BANDS = 5  /* rt_render of a large camera frame (or shard of one): bands of rows / row-blocks whose readback
                                   overlaps the next band's kernels, shrinking geometrically by the measured kernel : copy time
-                                  ratio of the previous frame.  0 (default) = 1..4 bands chosen from the measured times, n = n bands,
+                                  ratio of the previous frame.  0 (default) = 2 bands, n = n bands,
                                   1 = render everything, then copy it */
 } rt_option;
 

@@ -107,7 +107,7 @@ struct rt_ctx {
     // options
     int opt_pipeline = -1, opt_count = 0, opt_leaf = 1, opt_skip_dead = 1, opt_bands = 0, opt_builder = 0, opt_lanes = 2;
     // banded readback: kernel time : copy time of the same rows, measured on the previous banded frame
-    double band_ratio = 7.0, band_copy_ms = 0.0, band_kernel_ms = 0.0;  // copy / kernel time of the whole local frame
+    double band_ratio = 7.0;
     cudaEvent_t copy_ev[2] = {};
 
     rt_stats stats;
@@ -234,25 +234,12 @@ void band_range(const rt_ctx* c, int band, int n_bands, uint32_t* u0, uint32_t* 
     *u0 = start;
     *u1 = end;
 }
-// Number of bands when the caller leaves it open: the exposed copy (the last band's) against the cost of one more band
-// (its ramp-up and thin last generations: measured 0.8 ms at one GPU per 8K frame, 1.4 ms per band at 8 GPUs).
-int auto_bands(const rt_ctx* c) {
-    if (c->opt_bands > 0) return c->opt_bands;
-    if (!(c->band_copy_ms > 0.0)) return 2;  // nothing measured yet
-    const double per_band = std::max(1.2, 0.03 * c->band_kernel_ms), q = 1.0 / c->band_ratio;
-    int best = 1;
-    double best_cost = c->band_copy_ms, total = 1.0, w = 1.0;
-    for (int n = 2; n <= 4; ++n) {
-        w *= q;
-        total += w;
-        const double cost = (n - 1) * per_band + c->band_copy_ms * w / total;
-        if (cost < best_cost) {
-            best_cost = cost;
-            best = n;
-        }
-    }
-    return best;
-}
+// Number of bands when the caller leaves it open: two.  One more band costs its ramp-up and thin last generations
+// again (0.8 ms of an 8K frame on one GPU, 1.4 ms at 8 GPUs) and hides less than that in every configuration measured
+// (1, 2, 4, 8 GPUs); a cost model on the measured copy time is not robust, because that time depends on how many ranks
+// copy at the same moment, i.e. on the decision itself.
+int auto_bands(const rt_ctx* c) { return c->opt_bands > 0 ? c->opt_bands : 2; }
+
 // Frame descriptor.  Camera frames are described by a range [u0, u1) of the context's units (band_units(): rows of the
 // whole frame, or owned row-blocks of a shard); u1 == 0 means "everything" (and is the only form for explicit rays).
 void fill_frame_desc(rt_ctx* c, rt::Frame& fr, uint32_t max_bounces, int mode, float4* out, uint32_t u0 = 0, uint32_t u1 = 0) {
@@ -692,8 +679,6 @@ int rt_render(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float* host_
         if (units0 && cudaEventElapsedTime(&cp, c->copy_ev[0], c->copy_ev[1]) == cudaSuccess && cp > 0.f && ms > 0.f) {
             const double r = ((double)ms / band_units(c)) / ((double)cp / units0);
             c->band_ratio = std::min(16.0, std::max(1.25, 0.5 * c->band_ratio + 0.5 * r));
-            c->band_copy_ms = (double)cp / units0 * band_units(c);
-            c->band_kernel_ms = ms;
         }
         return RT_OK;
     }
