@@ -687,9 +687,9 @@ int rt_render(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float* host_
     // readback: the shard's row-blocks (or everything)
     uint64_t pixels;
     if (c->use_camera && c->n_shards > 1) {
-        const uint32_t br = c->block_rows, nb = (c->height + br - 1) / br;
+        const uint32_t br = c->block_rows, n_blocks = (c->height + br - 1) / br;
         pixels = 0;
-        for (uint32_t b = c->shard; b < nb; b += c->n_shards) {
+        for (uint32_t b = c->shard; b < n_blocks; b += c->n_shards) {
             const uint64_t first = (uint64_t)b * br * c->width;
             const uint64_t cnt = (uint64_t)std::min(br, c->height - b * br) * c->width;
             RT_CUDA(cudaMemcpyAsync(host_out + 4 * first, c->d_fb.p + first, cnt * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));

@@ -748,7 +748,7 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
                 wave_trace_bvh<false><<<pgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, fetch + g, wb.res_t, wb.res_id, min_t, drain_t, refill_t, fr.counters);
         } else if (accel == 1) {
             // 4 rays per thread x 4 objects per iteration, 2 blocks per SM, 2048-object tiles: the fastest of the
-            // configurations swept on the B200 (tools/sweep_filter.sh history in DESIGN.md)
+            // configurations swept on the B200 (tools/build_filter_variants.sh; history in DESIGN.md)
             const cudaError_t fe = launch_filter<RT_FILTER_RPT, RT_FILTER_OPI, RT_FILTER_MINB, RT_FILTER_TILE>(sc, qin, qcount + g, wb.res_t, wb.res_id,
                                                                                                           fr.counters, count, sm_count, stream);
             if (fe != cudaSuccess) return fe;
