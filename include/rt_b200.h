@@ -198,6 +198,22 @@ int rt_host_free(void* p);
 int rt_host_register(void* p, uint64_t bytes);
 int rt_host_unregister(void* p);
 
+/* Host-only, no GPU needed: the scene builder that rt_upload_scene runs (conservative per-object bounds + binned-SAH tree,
+ * what OpenCLRaytracer.cpp:13-33 marshals minus the tree, which the reference does not have), with the result copied out --
+ * for tests of the builder on a machine without a GPU and for timing it.  nodes_out: n_nodes x 64 bytes, per node
+ * float ctr0[3] ext0[3] ctr1[3] ext1[3]; int32 c0 c1 (>= 0 inner node, < 0 leaf: ~c = first << 4 | count - 1); float f0 f1.
+ * leaf_obj_out: object indices in leaf order.  Either may be NULL; info always reports the sizes.  threads: 0 = all
+ * host threads (at most 16); the tree does not depend on it. */
+typedef struct rt_bvh_info {
+    uint32_t n_nodes, n_leaf_objs, depth;
+    int32_t root;         /* child-style reference */
+    float omax, scene_radius;
+    double build_ms;
+} rt_bvh_info;
+int rt_host_build_bvh(const rt_object* objs, uint32_t n_objs, const rt_light* lights, uint32_t n_lights, float omax_user, int leaf_size,
+                      int threads, rt_bvh_info* info, void* nodes_out, uint64_t nodes_capacity_bytes, uint32_t* leaf_obj_out,
+                      uint64_t leaf_capacity);
+
 /* Register-only FFMA loop: measured FP32 peak of this device in TFLOP/s (roofline denominator). */
 int rt_measure_fp32_peak(rt_ctx* ctx, float* tflops, float* sm_mhz_hint);
 /* The two loops of the last rt_measure_fp32_peak separately: scalar FFMA, packed FFMA2 (its result is their maximum). */

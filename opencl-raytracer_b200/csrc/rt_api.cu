@@ -7,6 +7,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <chrono>
 #include <string>
 #include <vector>
 
@@ -833,6 +834,36 @@ int rt_quantize_rgb8(rt_ctx* c, const float* host_rgba, uint64_t n, int32_t* hos
     in.release();
     outb.release();
     if (e != cudaSuccess) return fail(RT_ERR_CUDA, std::string("rt_quantize_rgb8: ") + cudaGetErrorString(e));
+    return RT_OK;
+}
+
+int rt_host_build_bvh(const rt_object* objs, uint32_t n_objs, const rt_light* lights, uint32_t n_lights, float omax_user, int leaf_size,
+                      int threads, rt_bvh_info* info, void* nodes_out, uint64_t nodes_capacity_bytes, uint32_t* leaf_obj_out,
+                      uint64_t leaf_capacity) {
+    if (!info) return fail(RT_ERR_INVALID, "null info");
+    if (leaf_size < 1 || leaf_size > 16) return fail(RT_ERR_INVALID, "leaf size must be 1..16");
+    rt::HostScene hs;
+    std::string err;
+    const auto t0 = std::chrono::steady_clock::now();
+    const int rc = rt::build_scene(objs, n_objs, lights, n_lights, omax_user, leaf_size, hs, err, threads);
+    const auto t1 = std::chrono::steady_clock::now();
+    if (rc != RT_OK) return fail(rc, err);
+    memset(info, 0, sizeof *info);
+    info->n_nodes = (uint32_t)hs.nodes.size();
+    info->n_leaf_objs = (uint32_t)hs.leaf_obj.size();
+    info->depth = hs.bvh_depth;
+    info->root = hs.root;
+    info->omax = hs.omax;
+    info->scene_radius = hs.scene_radius;
+    info->build_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+    if (nodes_out) {
+        if (nodes_capacity_bytes < hs.nodes.size() * sizeof(rt::BvhNode)) return fail(RT_ERR_INVALID, "nodes_out too small");
+        memcpy(nodes_out, hs.nodes.data(), hs.nodes.size() * sizeof(rt::BvhNode));
+    }
+    if (leaf_obj_out) {
+        if (leaf_capacity < hs.leaf_obj.size()) return fail(RT_ERR_INVALID, "leaf_obj_out too small");
+        memcpy(leaf_obj_out, hs.leaf_obj.data(), hs.leaf_obj.size() * sizeof(uint32_t));
+    }
     return RT_OK;
 }
 

@@ -23,6 +23,8 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
+#include <chrono>
 #include <numeric>
 #include <thread>
 
@@ -111,10 +113,28 @@ float down(double v) {
 
 // Runs body(i, worker) for i in [0, n) on up to 16 host threads (contiguous chunks); returns the smallest index whose
 // body returned non-zero (with that code), or n.  The bounds of 10^5 objects are a Jacobi SVD each: ~90 ms on one core.
+// RT_BUILD_TIMING=1: stage times of build_scene on stderr
+struct StageTimer {
+    bool on = getenv("RT_BUILD_TIMING") != nullptr;
+    std::chrono::steady_clock::time_point t = std::chrono::steady_clock::now();
+    void lap(const char* what) {
+        if (!on) return;
+        const auto n = std::chrono::steady_clock::now();
+        fprintf(stderr, "build_scene: %-28s %7.2f ms\n", what, std::chrono::duration<double, std::milli>(n - t).count());
+        t = n;
+    }
+};
+
+int g_build_threads = 0;  // 0: as many as the host has, at most 16 (set through build_scene's `threads`)
+int worker_count() {
+    unsigned hw = std::thread::hardware_concurrency();
+    const int dflt = (int)std::min<unsigned>(hw ? hw : 1u, 16u);
+    return g_build_threads > 0 ? std::min(g_build_threads, 16) : dflt;
+}
+
 template <typename Body>
 uint32_t parallel_objects(uint32_t n, int* code_out, Body body, int* n_workers_out) {
-    unsigned hw = std::thread::hardware_concurrency();
-    int nw = (int)std::min<unsigned>(hw ? hw : 1u, 16u);
+    int nw = worker_count();
     if (n < 4096u) nw = 1;
     *n_workers_out = nw;
     std::vector<uint32_t> first_bad(nw, n);
@@ -163,29 +183,94 @@ struct BuildNode {
     int depth = 0;
 };
 
+// What the builder needs to know about a set of objects: the box around their padded boxes, the box around their
+// centres, the largest noise coefficient, the count.  Unions of these are exact (min / max / sum), so a child's record
+// taken from the parent's bins equals the one a pass over the child's objects would give.
+struct Extent {
+    double lo[3], hi[3], clo[3], chi[3], f;
+    uint32_t n;
+    Extent() { reset(); }
+    void reset() {
+        for (int k = 0; k < 3; ++k) {
+            lo[k] = clo[k] = INFINITY;
+            hi[k] = chi[k] = -INFINITY;
+        }
+        f = 0;
+        n = 0;
+    }
+    void add(const ObjBound& b) {
+        for (int k = 0; k < 3; ++k) {
+            lo[k] = std::min(lo[k], b.c[k] - b.half[k]);
+            hi[k] = std::max(hi[k], b.c[k] + b.half[k]);
+            clo[k] = std::min(clo[k], b.c[k]);
+            chi[k] = std::max(chi[k], b.c[k]);
+        }
+        f = std::max(f, b.f);
+        ++n;
+    }
+    void merge(const Extent& o) {
+        for (int k = 0; k < 3; ++k) {
+            lo[k] = std::min(lo[k], o.lo[k]);
+            hi[k] = std::max(hi[k], o.hi[k]);
+            clo[k] = std::min(clo[k], o.clo[k]);
+            chi[k] = std::max(chi[k], o.chi[k]);
+        }
+        f = std::max(f, o.f);
+        n += o.n;
+    }
+};
+
+// A subtree whose construction was put off: node `node` of the builder that deferred it covers idx[first, first+count).
+struct BuildTask {
+    int node;
+    uint32_t first, count;
+    int depth;
+    Extent ext;
+};
+
+constexpr int kBins = 16;
+struct BinSet {
+    Extent bin[3][kBins];
+};
+
+// Binned-SAH builder (16 bins per axis over the centres).  One pass over a node's objects fills the bins of all three
+// axes; the children's records come out of the bins, so every object is touched once per tree level.
 struct Builder {
     const std::vector<ObjBound>& ob;
-    std::vector<uint32_t> idx;
+    std::vector<uint32_t>& idx;  // object permutation, shared by all builders of a tree (they work on disjoint ranges)
     std::vector<BuildNode> bn;
     int leaf_size;
     uint32_t max_depth = 0;
+    int workers = 1;  // > 1: passes over >= 32768 objects are split over this many threads (top builder only)
+    // top builder only: subtrees at this depth (or smaller than defer_count objects) are recorded, not built
+    std::vector<BuildTask>* defer = nullptr;
+    int defer_depth = 0;
+    uint32_t defer_count = 0;
 
-    Builder(const std::vector<ObjBound>& o, int ls) : ob(o), idx(o.size()), leaf_size(ls) { std::iota(idx.begin(), idx.end(), 0u); }
+    Builder(const std::vector<ObjBound>& o, std::vector<uint32_t>& ix, int ls) : ob(o), idx(ix), leaf_size(ls) {}
 
-    void bounds(uint32_t first, uint32_t count, BuildNode& n) const {
-        for (int a = 0; a < 3; ++a) {
-            n.lo[a] = INFINITY;
-            n.hi[a] = -INFINITY;
+    template <typename Acc, typename Body>
+    void pass(uint32_t first, uint32_t count, Acc& total, Body body) const {  // body(acc, object); total.merge(acc) per chunk
+        const int nw = (workers > 1 && count >= 32768u) ? workers : 1;
+        if (nw == 1) {
+            for (uint32_t i = first; i < first + count; ++i) body(total, ob[idx[i]]);
+            return;
         }
-        n.f = 0;
-        for (uint32_t i = first; i < first + count; ++i) {
-            const ObjBound& b = ob[idx[i]];
-            for (int a = 0; a < 3; ++a) {
-                n.lo[a] = std::min(n.lo[a], b.c[a] - b.half[a]);
-                n.hi[a] = std::max(n.hi[a], b.c[a] + b.half[a]);
-            }
-            n.f = std::max(n.f, b.f);
-        }
+        std::vector<Acc> part(nw);
+        std::vector<std::thread> pool;
+        for (int w = 0; w < nw; ++w)
+            pool.emplace_back([&, w] {
+                const uint32_t b = first + (uint32_t)((uint64_t)count * w / nw), e = first + (uint32_t)((uint64_t)count * (w + 1) / nw);
+                for (uint32_t i = b; i < e; ++i) body(part[w], ob[idx[i]]);
+            });
+        for (auto& t : pool) t.join();
+        for (int w = 0; w < nw; ++w) total.merge(part[w]);
+    }
+
+    Extent measure(uint32_t first, uint32_t count) const {
+        Extent e;
+        pass(first, count, e, [](Extent& acc, const ObjBound& o) { acc.add(o); });
+        return e;
     }
 
     static double area(const double* lo, const double* hi) {
@@ -193,12 +278,16 @@ struct Builder {
         return 2.0 * (x * y + y * z + z * x);
     }
 
-    int build(uint32_t first, uint32_t count, int depth) {
+    int build(uint32_t first, uint32_t count, int depth, const Extent& e) {
         const int me = (int)bn.size();
         bn.emplace_back();
         {
             BuildNode n;
-            bounds(first, count, n);
+            for (int k = 0; k < 3; ++k) {
+                n.lo[k] = e.lo[k];
+                n.hi[k] = e.hi[k];
+            }
+            n.f = e.f;
             n.first = first;
             n.count = count;
             n.depth = depth;
@@ -206,54 +295,50 @@ struct Builder {
         }
         max_depth = std::max<uint32_t>(max_depth, (uint32_t)depth);
         if (count <= (uint32_t)leaf_size) return me;
+        if (defer && (depth >= defer_depth || count <= defer_count)) {
+            defer->push_back(BuildTask{me, first, count, depth, e});
+            return me;
+        }
 
-        // binned SAH over centroids
-        double clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
-        for (uint32_t i = first; i < first + count; ++i)
-            for (int a = 0; a < 3; ++a) {
-                clo[a] = std::min(clo[a], ob[idx[i]].c[a]);
-                chi[a] = std::max(chi[a], ob[idx[i]].c[a]);
+        // bins of all three axes in one pass
+        double scale[3];
+        bool splittable[3];
+        for (int a = 0; a < 3; ++a) {
+            const double ext = e.chi[a] - e.clo[a];
+            splittable[a] = ext > 0;
+            scale[a] = splittable[a] ? kBins / ext : 0.0;
+        }
+        struct Bins : BinSet {
+            void merge(const Bins& o) {
+                for (int a = 0; a < 3; ++a)
+                    for (int b = 0; b < kBins; ++b) bin[a][b].merge(o.bin[a][b]);
             }
-        const int NB = 16;
+        } bins;
+        pass(first, count, bins, [&](Bins& acc, const ObjBound& o) {
+            for (int a = 0; a < 3; ++a) {
+                if (!splittable[a]) continue;
+                int b = (int)((o.c[a] - e.clo[a]) * scale[a]);
+                b = std::min(std::max(b, 0), kBins - 1);
+                acc.bin[a][b].add(o);
+            }
+        });
         int best_axis = -1, best_bin = -1;
         double best_cost = INFINITY;
         for (int a = 0; a < 3; ++a) {
-            const double ext = chi[a] - clo[a];
-            if (!(ext > 0)) continue;
-            struct Bin {
-                double lo[3], hi[3];
-                uint32_t n;
-            } bins[NB];
-            for (int b = 0; b < NB; ++b) {
-                bins[b].n = 0;
-                for (int k = 0; k < 3; ++k) {
-                    bins[b].lo[k] = INFINITY;
-                    bins[b].hi[k] = -INFINITY;
-                }
-            }
-            const double scale = NB / ext;
-            for (uint32_t i = first; i < first + count; ++i) {
-                const ObjBound& o = ob[idx[i]];
-                int b = (int)((o.c[a] - clo[a]) * scale);
-                b = std::min(std::max(b, 0), NB - 1);
-                bins[b].n++;
-                for (int k = 0; k < 3; ++k) {
-                    bins[b].lo[k] = std::min(bins[b].lo[k], o.c[k] - o.half[k]);
-                    bins[b].hi[k] = std::max(bins[b].hi[k], o.c[k] + o.half[k]);
-                }
-            }
-            double rl[NB][3], rh[NB][3];
-            uint32_t rn[NB];
+            if (!splittable[a]) continue;
+            const Extent* bin = bins.bin[a];
+            double rl[kBins][3], rh[kBins][3];
+            uint32_t rn[kBins];
             double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
             uint32_t n = 0;
-            for (int b = NB - 1; b > 0; --b) {
+            for (int b = kBins - 1; b > 0; --b) {
                 for (int k = 0; k < 3; ++k) {
-                    lo[k] = std::min(lo[k], bins[b].lo[k]);
-                    hi[k] = std::max(hi[k], bins[b].hi[k]);
+                    lo[k] = std::min(lo[k], bin[b].lo[k]);
+                    hi[k] = std::max(hi[k], bin[b].hi[k]);
                     rl[b][k] = lo[k];
                     rh[b][k] = hi[k];
                 }
-                n += bins[b].n;
+                n += bin[b].n;
                 rn[b] = n;
             }
             for (int k = 0; k < 3; ++k) {
@@ -261,12 +346,12 @@ struct Builder {
                 hi[k] = -INFINITY;
             }
             n = 0;
-            for (int b = 0; b < NB - 1; ++b) {
+            for (int b = 0; b < kBins - 1; ++b) {
                 for (int k = 0; k < 3; ++k) {
-                    lo[k] = std::min(lo[k], bins[b].lo[k]);
-                    hi[k] = std::max(hi[k], bins[b].hi[k]);
+                    lo[k] = std::min(lo[k], bin[b].lo[k]);
+                    hi[k] = std::max(hi[k], bin[b].hi[k]);
                 }
-                n += bins[b].n;
+                n += bin[b].n;
                 if (n == 0 || rn[b + 1] == 0) continue;
                 const double cost = area(lo, hi) * n + area(rl[b + 1], rh[b + 1]) * rn[b + 1];
                 if (cost < best_cost) {
@@ -277,22 +362,33 @@ struct Builder {
             }
         }
         uint32_t mid;
+        Extent el, er;
+        bool have_extents = false;
         if (best_axis < 0 || depth >= 32) {  // depth cap: median splits from here on keep the tree below RT_BVH_STACK
             mid = first + count / 2;  // (also when all centroids coincide)
         } else {
-            const double ext = chi[best_axis] - clo[best_axis];
-            const double scale = NB / ext;
             const int a = best_axis;
+            const double clo_a = e.clo[a], sc = scale[a];
             auto it = std::partition(idx.begin() + first, idx.begin() + first + count, [&](uint32_t id) {
-                int b = (int)((ob[id].c[a] - clo[a]) * scale);
-                b = std::min(std::max(b, 0), NB - 1);
+                int b = (int)((ob[id].c[a] - clo_a) * sc);
+                b = std::min(std::max(b, 0), kBins - 1);
                 return b <= best_bin;
             });
             mid = (uint32_t)(it - idx.begin());
-            if (mid == first || mid == first + count) mid = first + count / 2;
+            if (mid == first || mid == first + count) {
+                mid = first + count / 2;
+            } else {
+                for (int b = 0; b <= best_bin; ++b) el.merge(bins.bin[a][b]);
+                for (int b = best_bin + 1; b < kBins; ++b) er.merge(bins.bin[a][b]);
+                have_extents = true;
+            }
         }
-        const int l = build(first, mid - first, depth + 1);
-        const int r = build(mid, first + count - mid, depth + 1);
+        if (!have_extents) {
+            el = measure(first, mid - first);
+            er = measure(mid, first + count - mid);
+        }
+        const int l = build(first, mid - first, depth + 1, el);
+        const int r = build(mid, first + count - mid, depth + 1, er);
         bn[me].left = l;
         bn[me].right = r;
         return me;
@@ -302,7 +398,8 @@ struct Builder {
 }  // namespace
 
 int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, uint32_t n_lights, float omax_user,
-                int leaf_size, HostScene& out, std::string& err) {
+                int leaf_size, HostScene& out, std::string& err, int threads) {
+    g_build_threads = threads;
     out = HostScene();
     out.n_objs = n_objs;
     out.n_lights = n_lights;
@@ -331,6 +428,8 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
         out.lights[4 * i + 3] = F4{l.position[0], l.position[1], l.position[2], l.position[3]};
     }
 
+    StageTimer timer;
+    timer.lap("repack lights, resize");
     // ---- pass 1: geometry of every object in double precision
     struct Geo {
         double c[3], ext[3], R, smin, smax, wdev;
@@ -445,6 +544,7 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
     out.omax = (float)omax;
     out.scene_radius = (float)r0;
 
+    timer.lap("pass 1 (geometry, SVD)");
     // ---- pass 2: padded bounds
     std::vector<ObjBound> ob(n_objs);
     std::vector<uint32_t> live;
@@ -518,6 +618,7 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
             if (objs[i].type <= 2u) live.push_back(i);
     }
 
+    timer.lap("pass 2 (padded bounds)");
     // ---- BVH over the live objects
     out.root = 0;
     if (live.empty()) {
@@ -530,7 +631,7 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
         memset(&dead, 0, sizeof dead);
         dead.r2 = -1.f;
         dead.h = 1.f;
-        dead.type = 2u;
+        dead.type = 0xffffffffu;  // no primitive: the kernels' switch skips it (n_objs may be > 0 with unknown types only)
         out.leaf_cull.push_back(dead);
         return RT_OK;
     }
@@ -559,22 +660,71 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
         out.root = 0;
         return RT_OK;
     }
-    Builder bld(lob, leaf_size);
+    // The top levels are built here, the subtrees below them on worker threads (private node lists, spliced in
+    // afterwards); the node numbering below is a preorder walk, so the result does not depend on the thread count.
+    std::vector<uint32_t> perm(live.size());
+    std::iota(perm.begin(), perm.end(), 0u);
+    Builder bld(lob, perm, leaf_size);
     bld.bn.reserve(2 * live.size());
-    const int root = bld.build(0, (uint32_t)live.size(), 0);
+    std::vector<BuildTask> tasks;
+    const int nw = live.size() >= 8192 ? worker_count() : 1;
+    if (nw > 1) {
+        bld.defer = &tasks;
+        bld.defer_depth = 5;  // up to 32 subtrees
+        bld.defer_count = 2048;
+    }
+    bld.workers = nw;
+    const int root = bld.build(0, (uint32_t)live.size(), 0, bld.measure(0, (uint32_t)live.size()));
+    if (!tasks.empty()) {
+        std::vector<Builder> sub;
+        sub.reserve(tasks.size());
+        for (size_t t = 0; t < tasks.size(); ++t) sub.emplace_back(lob, perm, leaf_size);
+        std::atomic<size_t> next{0};
+        auto run = [&]() {
+            for (size_t t; (t = next.fetch_add(1)) < tasks.size();) sub[t].build(tasks[t].first, tasks[t].count, tasks[t].depth, tasks[t].ext);
+        };
+        std::vector<std::thread> pool;
+        for (int w = 0; w < std::min<int>(nw, (int)tasks.size()); ++w) pool.emplace_back(run);
+        for (auto& th : pool) th.join();
+        for (size_t t = 0; t < tasks.size(); ++t) {  // splice: local node 0 is the deferred node itself
+            const int base = (int)bld.bn.size() - 1;
+            auto remap = [&](int j) { return j < 0 ? j : (j == 0 ? tasks[t].node : base + j); };
+            const std::vector<BuildNode>& l = sub[t].bn;
+            bld.bn[tasks[t].node].left = remap(l[0].left);
+            bld.bn[tasks[t].node].right = remap(l[0].right);
+            for (size_t j = 1; j < l.size(); ++j) {
+                BuildNode n = l[j];
+                n.left = remap(n.left);
+                n.right = remap(n.right);
+                bld.bn.push_back(n);
+            }
+            bld.max_depth = std::max(bld.max_depth, sub[t].max_depth);
+        }
+    }
     out.bvh_depth = bld.max_depth;
 
     out.leaf_obj.resize(live.size());
     out.leaf_cull.resize(live.size());
     for (size_t i = 0; i < live.size(); ++i) {
-        out.leaf_obj[i] = live[bld.idx[i]];
+        out.leaf_obj[i] = live[perm[i]];
         out.leaf_cull[i] = out.cull[out.leaf_obj[i]];
     }
-    // flatten: inner BuildNodes get consecutive indices in DFS order
+    timer.lap("SAH build");
+    // flatten: inner BuildNodes get consecutive indices in preorder (node, left subtree, right subtree)
     std::vector<int32_t> inner_index(bld.bn.size(), -1);
     int32_t n_inner = 0;
-    for (size_t i = 0; i < bld.bn.size(); ++i)
-        if (bld.bn[i].left >= 0) inner_index[i] = n_inner++;
+    {
+        std::vector<int> todo;
+        todo.push_back(root);
+        while (!todo.empty()) {
+            const int i = todo.back();
+            todo.pop_back();
+            if (bld.bn[i].left < 0) continue;
+            inner_index[i] = n_inner++;
+            todo.push_back(bld.bn[i].right);
+            todo.push_back(bld.bn[i].left);
+        }
+    }
     out.nodes.resize(std::max(n_inner, 1));
     memset(out.nodes.data(), 0, out.nodes.size() * sizeof(BvhNode));
     auto ref_of = [&](int bi) -> int32_t {
@@ -605,15 +755,21 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
         // static part of the inflation f * |farthest point - origin|_1 = f * sum(|c - o|) + f * sum(half extents)
         for (int k = 0; k < 3; ++k) ext[k] = up(h[k] + (double)f * hsum * (1.0 + 1e-6));
     };
-    for (size_t i = 0; i < bld.bn.size(); ++i) {
-        const BuildNode& n = bld.bn[i];
-        if (n.left < 0) continue;
-        BvhNode& d = out.nodes[inner_index[i]];
-        child(n.left, d.ctr0, d.ext0, d.f0);
-        child(n.right, d.ctr1, d.ext1, d.f1);
-        d.c0 = ref_of(n.left);
-        d.c1 = ref_of(n.right);
+    {
+        auto record = [&](uint32_t i, int) -> int {
+            const BuildNode& n = bld.bn[i];
+            if (n.left < 0) return 0;
+            BvhNode& d = out.nodes[inner_index[i]];
+            child(n.left, d.ctr0, d.ext0, d.f0);
+            child(n.right, d.ctr1, d.ext1, d.f1);
+            d.c0 = ref_of(n.left);
+            d.c1 = ref_of(n.right);
+            return 0;
+        };
+        int code = 0, nw_rec = 1;
+        parallel_objects((uint32_t)bld.bn.size(), &code, record, &nw_rec);
     }
+    timer.lap("flatten + node records");
     out.root = ref_of(root);
     out.f_global = up(bld.bn[root].f);
     return RT_OK;

@@ -50,7 +50,9 @@ struct HostScene {
 // Returns RT_OK or RT_ERR_UNSUPPORTED / RT_ERR_INVALID with a message in err.
 // omax_user: largest |origin| of caller-supplied rays (0 for the pinhole camera).
 // leaf_size: objects per BVH leaf of the host SAH builder (1..16); 0 = build no tree, fill lbvh_leaves instead.
+// threads: host threads for the per-object bounds and the subtrees of the SAH build (0 = all, at most 16); the result does
+// not depend on it.
 int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, uint32_t n_lights, float omax_user,
-                int leaf_size, HostScene& out, std::string& err);
+                int leaf_size, HostScene& out, std::string& err, int threads = 0);
 
 }  // namespace rt

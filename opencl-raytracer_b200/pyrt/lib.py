@@ -22,7 +22,7 @@ ABI_SYMBOLS = (
     "rt_last_error", "rt_abi_version", "rt_device_count", "rt_create", "rt_destroy", "rt_set_option", "rt_upload_scene", "rt_set_rays",
     "rt_set_camera", "rt_set_shard", "rt_render", "rt_render_device", "rt_framebuffer", "rt_render_aov", "rt_trace",
     "rt_get_stats", "rt_quantize_rgb8", "rt_host_alloc", "rt_host_free", "rt_host_register", "rt_host_unregister", "rt_measure_fp32_peak", "rt_fp32_peak_detail",
-    "rt_ipc_export_framebuffer", "rt_ipc_open", "rt_ipc_close", "rt_readback",
+    "rt_ipc_export_framebuffer", "rt_ipc_open", "rt_ipc_close", "rt_readback", "rt_host_build_bvh",
 )
 
 
@@ -48,6 +48,15 @@ class Stats(C.Structure):
     def rays_reference(self):
         return self.rays_primary + self.rays_shadow + self.rays_reflect
 
+
+class BvhInfo(C.Structure):
+    _fields_ = [("n_nodes", C.c_uint32), ("n_leaf_objs", C.c_uint32), ("depth", C.c_uint32), ("root", C.c_int32),
+                ("omax", C.c_float), ("scene_radius", C.c_float), ("build_ms", C.c_double)]
+
+
+# rt::BvhNode (csrc/rt_layout.h), 64 bytes
+BVH_NODE_DTYPE = np.dtype([("ctr0", "<f4", 3), ("ext0", "<f4", 3), ("ctr1", "<f4", 3), ("ext1", "<f4", 3),
+                           ("c0", "<i4"), ("c1", "<i4"), ("f0", "<f4"), ("f1", "<f4")])
 
 _lib = None
 
@@ -88,6 +97,7 @@ def load():
             "rt_ipc_export_framebuffer": [vp, vp],
             "rt_ipc_open": [vp, vp, C.POINTER(vp)],
             "rt_ipc_close": [vp, vp],
+            "rt_host_build_bvh": [vp, u32, vp, u32, C.c_float, i32, i32, C.POINTER(BvhInfo), vp, u64, vp, u64],
         }
         for name, args in sigs.items():
             fn = getattr(lib, name)
@@ -110,6 +120,21 @@ def _check(rc):
 
 def _ptr(a):
     return a.ctypes.data_as(C.c_void_p) if a is not None and a.size else None
+
+
+def host_build_bvh(objs: np.ndarray, lights: np.ndarray, omax_user: float = 0.0, leaf_size: int = 1, threads: int = 0):
+    """The host scene builder of rt_upload_scene without a GPU (rt_host_build_bvh): (info, nodes, leaf_obj)."""
+    from .types import LIGHT_DTYPE, OBJECT_DTYPE
+    objs = np.ascontiguousarray(objs, dtype=OBJECT_DTYPE)
+    lights = np.ascontiguousarray(lights, dtype=LIGHT_DTYPE)
+    info = BvhInfo()
+    lib = load()
+    _check(lib.rt_host_build_bvh(_ptr(objs), len(objs), _ptr(lights), len(lights), omax_user, leaf_size, threads, C.byref(info), None, 0, None, 0))
+    nodes = np.zeros(info.n_nodes, dtype=BVH_NODE_DTYPE)
+    leaf = np.zeros(info.n_leaf_objs, dtype=np.uint32)
+    _check(lib.rt_host_build_bvh(_ptr(objs), len(objs), _ptr(lights), len(lights), omax_user, leaf_size, threads, C.byref(info),
+                                 _ptr(nodes), nodes.nbytes, _ptr(leaf), len(leaf)))
+    return info, nodes, leaf
 
 
 class SharedFrame:

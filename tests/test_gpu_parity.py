@@ -388,6 +388,14 @@ def test_edge_cases(rt, ctx, oracle_mod):
     ctx.upload_scene(objs[:0], lights)  # zero objects
     out = ctx.render(4, 2, -1)
     assert np.all(out == np.array([0, 0, 0, 1], dtype=np.float32))
+    unknown = objs.copy()
+    unknown["type"] = 7  # objects of unknown type only: the reference's switch skips them all (SAR:87,112)
+    ctx.upload_scene(unknown, lights)
+    for accel in (0, 1, 2):
+        for pipeline in (0, 1):
+            ctx.set_option(rt.OPT_PIPELINE, pipeline)
+            assert np.all(ctx.render(4, 2, accel) == np.array([0, 0, 0, 1], dtype=np.float32))
+    ctx.set_option(rt.OPT_PIPELINE, -1)
     ctx.upload_scene(objs, lights)
     for mb in (0, 1, 2):  # uint wrap of `bounces`
         ref, *_ = oracle_mod.port_render(2, mb, objs, lights, rays)
