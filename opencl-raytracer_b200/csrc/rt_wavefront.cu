@@ -153,10 +153,11 @@ __device__ __noinline__ void exact_pair_call(const Scene& sc, const float4 s, co
 // the lane's candidate buffer (shared memory), without a per-object filter: with the default one object per leaf
 // the child box IS the object's padded bounding box -- so the traversal loop consists of node steps only.  The warp
 // then schedules whole-warp rounds of the three activities so that each runs with most lanes taking part:
-//   node steps   while >= 16 lanes are in T (or nothing else is worth doing)
-//   exact tests  when >= 8 lanes have a candidate queued or nobody can traverse
-//   refill       when >= 12 lanes are idle (or nobody is traversing) and the queue is not exhausted
-// (thresholds swept on the B200 with tools/sweep_sched.sh; RT_WAVE_MIN_T / _DRAIN / _REFILL override them)
+//   node steps   while >= 12 lanes are in T (or nothing else is worth doing)
+//   exact tests  when >= 4 lanes have a candidate queued or nobody can traverse
+//   refill       when >= 16 lanes are idle (or nobody is traversing) and the queue is not exhausted
+// (thresholds swept on the B200 with tools/sweep_sched.sh, again after the queue became tile-contiguous: 16/8/12 ->
+// 12/4/16, 58.8 -> 57.6 ms per 8K frame; RT_WAVE_MIN_T / _DRAIN / _REFILL override them)
 // Deferring exact tests never changes the result: every queued candidate is tested before its ray retires, and
 // pruning against the best t found so far only ever skips nodes that cannot contain a better hit.
 #ifndef RT_BVH_MINB
@@ -697,7 +698,7 @@ static int env_int(const char* name, int dflt) {
 cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb, int accel, uint32_t leaf_max, int sm_count,
                         uint32_t* launches, cudaStream_t stream) {
     // warp-scheduler thresholds of wave_trace_bvh (tunable for experiments)
-    static const int min_t = env_int("RT_WAVE_MIN_T", 16), drain_t = env_int("RT_WAVE_DRAIN", 8), refill_t = env_int("RT_WAVE_REFILL", 12);
+    static const int min_t = env_int("RT_WAVE_MIN_T", 12), drain_t = env_int("RT_WAVE_DRAIN", 4), refill_t = env_int("RT_WAVE_REFILL", 16);
     (void)leaf_max;
     const uint32_t gens = wave_max_generations(fr.max_bounces, sc.n_lights, fr.mode);
     if (gens + 1 > wb.n_counts) return cudaErrorInvalidValue;
