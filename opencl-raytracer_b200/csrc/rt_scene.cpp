@@ -241,7 +241,7 @@ struct Builder {
     std::vector<BuildNode> bn;
     int leaf_size;
     uint32_t max_depth = 0;
-    int workers = 1;  // > 1: passes over >= 32768 objects are split over this many threads (top builder only)
+    int workers = 1;  // > 1: passes over >= 16384 objects are split over this many threads (top builder only)
     // top builder only: subtrees at this depth (or smaller than defer_count objects) are recorded, not built
     std::vector<BuildTask>* defer = nullptr;
     int defer_depth = 0;
@@ -251,7 +251,7 @@ struct Builder {
 
     template <typename Acc, typename Body>
     void pass(uint32_t first, uint32_t count, Acc& total, Body body) const {  // body(acc, object); total.merge(acc) per chunk
-        const int nw = (workers > 1 && count >= 32768u) ? workers : 1;
+        const int nw = (workers > 1 && count >= 16384u) ? workers : 1;
         if (nw == 1) {
             for (uint32_t i = first; i < first + count; ++i) body(total, ob[idx[i]]);
             return;
@@ -660,25 +660,38 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
         out.root = 0;
         return RT_OK;
     }
-    // The top levels are built here, the subtrees below them on worker threads (private node lists, spliced in
-    // afterwards); the node numbering below is a preorder walk, so the result does not depend on the thread count.
+    // The tree is built in rounds of three levels: the root's three levels here (their passes over the objects split
+    // over the host threads), then every subtree that was put off as a task of the next round, all tasks of a round in
+    // parallel on worker threads with private node lists that are spliced in afterwards.  The node numbering below is a
+    // preorder walk, so the result does not depend on the thread count.
     std::vector<uint32_t> perm(live.size());
     std::iota(perm.begin(), perm.end(), 0u);
     Builder bld(lob, perm, leaf_size);
     bld.bn.reserve(2 * live.size());
-    std::vector<BuildTask> tasks;
+    std::vector<BuildTask> frontier;
     const int nw = live.size() >= 8192 ? worker_count() : 1;
     if (nw > 1) {
-        bld.defer = &tasks;
-        bld.defer_depth = 5;  // up to 32 subtrees
+        bld.defer = &frontier;
+        bld.defer_depth = 3;
         bld.defer_count = 2048;
     }
     bld.workers = nw;
     const int root = bld.build(0, (uint32_t)live.size(), 0, bld.measure(0, (uint32_t)live.size()));
-    if (!tasks.empty()) {
+    bld.workers = 1;
+    while (!frontier.empty()) {
+        std::vector<BuildTask> tasks;
+        tasks.swap(frontier);
         std::vector<Builder> sub;
         sub.reserve(tasks.size());
-        for (size_t t = 0; t < tasks.size(); ++t) sub.emplace_back(lob, perm, leaf_size);
+        std::vector<std::vector<BuildTask>> more(tasks.size());
+        for (size_t t = 0; t < tasks.size(); ++t) {
+            sub.emplace_back(lob, perm, leaf_size);
+            if (tasks[t].count > 4096u) {  // large: three more levels, the rest next round
+                sub[t].defer = &more[t];
+                sub[t].defer_depth = tasks[t].depth + 3;
+                sub[t].defer_count = 2048;
+            }
+        }
         std::atomic<size_t> next{0};
         auto run = [&]() {
             for (size_t t; (t = next.fetch_add(1)) < tasks.size();) sub[t].build(tasks[t].first, tasks[t].count, tasks[t].depth, tasks[t].ext);
@@ -699,6 +712,10 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
                 bld.bn.push_back(n);
             }
             bld.max_depth = std::max(bld.max_depth, sub[t].max_depth);
+            for (BuildTask m : more[t]) {
+                m.node = remap(m.node);
+                frontier.push_back(m);
+            }
         }
     }
     out.bvh_depth = bld.max_depth;
