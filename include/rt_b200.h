@@ -214,6 +214,10 @@ int rt_host_build_bvh(const rt_object* objs, uint32_t n_objs, const rt_light* li
                       int threads, rt_bvh_info* info, void* nodes_out, uint64_t nodes_capacity_bytes, uint32_t* leaf_obj_out,
                       uint64_t leaf_capacity);
 
+/* Host-only: how rt_render cuts a camera frame (n_shards == 1: its rows; else the row-blocks shard owns) into n_bands readback
+ * bands shrinking by `ratio` (RT_OPT_READBACK_BANDS).  bounds[0 .. n_bands]: band b covers units bounds[b] .. bounds[b+1]. */
+int rt_plan_bands(uint32_t height, uint32_t block_rows, uint32_t shard, uint32_t n_shards, int n_bands, double ratio, uint32_t* bounds);
+
 /* Register-only FFMA loop: measured FP32 peak of this device in TFLOP/s (roofline denominator). */
 int rt_measure_fp32_peak(rt_ctx* ctx, float* tflops, float* sm_mhz_hint);
 /* The two loops of the last rt_measure_fp32_peak separately: scalar FFMA, packed FFMA2 (its result is their maximum). */

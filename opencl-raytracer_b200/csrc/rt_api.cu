@@ -213,14 +213,13 @@ uint64_t local_pixels(const rt_ctx* c) { return c->use_camera ? (uint64_t)shard_
 // thin last generations again, and the copy is faster than the kernels of the same rows, so the bands shrink
 // geometrically by band_ratio = kernel time : copy time, measured on the previous frame (7 : 1 on one GPU over an
 // idle PCIe link, < 2 : 1 when 8 ranks share the host's ingest bandwidth): only the last, small band's copy is exposed.
-uint32_t band_units(const rt_ctx* c) {
-    if (c->n_shards <= 1) return c->height;
-    const uint32_t n_blocks = (c->height + c->block_rows - 1) / c->block_rows;
-    return n_blocks > c->shard ? (n_blocks - c->shard + c->n_shards - 1) / c->n_shards : 0u;
+uint32_t plan_units(uint32_t height, uint32_t block_rows, uint32_t shard, uint32_t n_shards) {
+    if (n_shards <= 1) return height;
+    const uint32_t n_blocks = (height + block_rows - 1) / block_rows;
+    return n_blocks > shard ? (n_blocks - shard + n_shards - 1) / n_shards : 0u;
 }
-void band_range(const rt_ctx* c, int band, int n_bands, uint32_t* u0, uint32_t* u1) {
-    const uint32_t units = band_units(c);
-    const double q = 1.0 / c->band_ratio;
+void plan_band(uint32_t units, int band, int n_bands, double ratio, uint32_t* u0, uint32_t* u1) {
+    const double q = 1.0 / ratio;
     double total = 0.0, w = 1.0;
     for (int i = 0; i < n_bands; ++i, w *= q) total += w;
     double acc = 0.0;
@@ -234,6 +233,10 @@ void band_range(const rt_ctx* c, int band, int n_bands, uint32_t* u0, uint32_t* 
     }
     *u0 = start;
     *u1 = end;
+}
+uint32_t band_units(const rt_ctx* c) { return plan_units(c->height, c->block_rows, c->shard, c->n_shards); }
+void band_range(const rt_ctx* c, int band, int n_bands, uint32_t* u0, uint32_t* u1) {
+    plan_band(band_units(c), band, n_bands, c->band_ratio, u0, u1);
 }
 // Number of bands when the caller leaves it open: two.  One more band costs its ramp-up and thin last generations
 // again (0.8 ms of an 8K frame on one GPU, 1.4 ms at 8 GPUs) and hides less than that in every configuration measured
@@ -834,6 +837,19 @@ int rt_quantize_rgb8(rt_ctx* c, const float* host_rgba, uint64_t n, int32_t* hos
     in.release();
     outb.release();
     if (e != cudaSuccess) return fail(RT_ERR_CUDA, std::string("rt_quantize_rgb8: ") + cudaGetErrorString(e));
+    return RT_OK;
+}
+
+int rt_plan_bands(uint32_t height, uint32_t block_rows, uint32_t shard, uint32_t n_shards, int n_bands, double ratio, uint32_t* bounds) {
+    if (!bounds || n_bands < 1 || n_bands > rt_ctx::kMaxBands || !(ratio >= 1.0) || block_rows == 0 || n_shards == 0 || shard >= n_shards)
+        return fail(RT_ERR_INVALID, "bad band plan arguments");
+    const uint32_t units = plan_units(height, block_rows, shard, n_shards);
+    bounds[0] = 0;
+    for (int b = 0; b < n_bands; ++b) {
+        uint32_t u0, u1;
+        plan_band(units, b, n_bands, ratio, &u0, &u1);
+        bounds[b + 1] = u1;
+    }
     return RT_OK;
 }
 

@@ -22,7 +22,7 @@ ABI_SYMBOLS = (
     "rt_last_error", "rt_abi_version", "rt_device_count", "rt_create", "rt_destroy", "rt_set_option", "rt_upload_scene", "rt_set_rays",
     "rt_set_camera", "rt_set_shard", "rt_render", "rt_render_device", "rt_framebuffer", "rt_render_aov", "rt_trace",
     "rt_get_stats", "rt_quantize_rgb8", "rt_host_alloc", "rt_host_free", "rt_host_register", "rt_host_unregister", "rt_measure_fp32_peak", "rt_fp32_peak_detail",
-    "rt_ipc_export_framebuffer", "rt_ipc_open", "rt_ipc_close", "rt_readback", "rt_host_build_bvh",
+    "rt_ipc_export_framebuffer", "rt_ipc_open", "rt_ipc_close", "rt_readback", "rt_host_build_bvh", "rt_plan_bands",
 )
 
 
@@ -98,6 +98,7 @@ def load():
             "rt_ipc_open": [vp, vp, C.POINTER(vp)],
             "rt_ipc_close": [vp, vp],
             "rt_host_build_bvh": [vp, u32, vp, u32, C.c_float, i32, i32, C.POINTER(BvhInfo), vp, u64, vp, u64],
+            "rt_plan_bands": [u32, u32, u32, u32, i32, C.c_double, vp],
         }
         for name, args in sigs.items():
             fn = getattr(lib, name)
@@ -135,6 +136,13 @@ def host_build_bvh(objs: np.ndarray, lights: np.ndarray, omax_user: float = 0.0,
     _check(lib.rt_host_build_bvh(_ptr(objs), len(objs), _ptr(lights), len(lights), omax_user, leaf_size, threads, C.byref(info),
                                  _ptr(nodes), nodes.nbytes, _ptr(leaf), len(leaf)))
     return info, nodes, leaf
+
+
+def plan_bands(height: int, block_rows: int, shard: int, n_shards: int, n_bands: int, ratio: float) -> np.ndarray:
+    """Band boundaries (in rows, or owned row-blocks of a shard) of a banded rt_render (rt_plan_bands)."""
+    b = np.zeros(n_bands + 1, dtype=np.uint32)
+    _check(load().rt_plan_bands(height, block_rows, shard, n_shards, n_bands, ratio, _ptr(b)))
+    return b
 
 
 class SharedFrame:

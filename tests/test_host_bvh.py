@@ -126,3 +126,22 @@ def test_builder_edge_cases_and_errors(rt):
     assert "object 2" in str(e.value)
     with pytest.raises(rt.RtError):
         rt.host_build_bvh(objs, lights, leaf_size=17)
+
+
+def test_readback_band_plan_partitions_the_frame(rt):
+    """rt_plan_bands: the split rt_render uses for its readback bands -- contiguous, complete, largest band first."""
+    for height, br, ns in ((4320, 1, 1), (4320, 16, 8), (2069, 16, 2), (37, 16, 3), (5, 16, 1)):
+        for shard in range(ns):
+            n_blocks = -(-height // br)
+            units = height if ns == 1 else len(range(shard, n_blocks, ns))
+            for nb in (1, 2, 3, 16):
+                for ratio in (1.25, 1.85, 7.0, 16.0):
+                    b = rt.plan_bands(height, br, shard, ns, nb, ratio)
+                    assert b[0] == 0 and b[-1] == units and np.all(np.diff(b.astype(np.int64)) >= 0)
+                    sizes = np.diff(b.astype(np.int64))
+                    if units >= 64 * nb and nb <= 3:
+                        assert np.all(sizes[:-1] >= sizes[1:]) and sizes[-1] > 0
+                    if nb == 2 and units >= 64:
+                        assert abs(sizes[0] / max(sizes[1], 1) - ratio) < 0.1 * ratio + 0.6
+    with pytest.raises(rt.RtError):
+        rt.plan_bands(100, 16, 3, 2, 2, 7.0)
