@@ -391,10 +391,12 @@ def main():
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
-    kernel_names = ({0: "wave_trace_brute", 1: "wave_trace_filter", 2: "wave_trace_bvh"} if pipeline_used == 1 else
+    kernel_names = ({0: "wave_trace_brute", 1: "wave_trace_filter", 2: "wave_trace_bvh", 3: "wave_trace_bvh"} if pipeline_used == 1 else
                     {0: "render_mega<brute>", 1: "render_mega<filter>", 2: "render_mega<bvh>"})
     shades = t_shadow  # one Phong evaluation per traced shadow ray
-    if accel_used == 2:
+    if accel_used == 3:  # perspective grids (filter tests per list entry) + BVH for the rays without a common apex
+        flops = node_visits * FLOPS_NODE + pair_tests * FLOPS_FILTER + exact_tests * FLOPS_EXACT + shades * FLOPS_SHADE
+    elif accel_used == 2:
         flops = node_visits * FLOPS_NODE + exact_tests * (FLOPS_EXACT + FLOPS_FILTER) + shades * FLOPS_SHADE
     elif accel_used == 1:
         flops = pair_tests * FLOPS_FILTER + exact_tests * FLOPS_EXACT + shades * FLOPS_SHADE
@@ -414,7 +416,7 @@ def main():
         "note": "BVH traversal is bound by divergent node fetches, not by FP32: ncu (profiles/r1_g_wave_trace_bvh_cfg5_8k.txt, "
                 "this frame, primary-ray launch) shows the L1 data pipe at 64 % of its wavefront peak and the issue slots at 74 %; "
                 "the FP32 fraction is reported for completeness, see roofline_brute for the FP32-bound kernel"
-        if accel_used == 2 else "",
+        if accel_used >= 2 else "",
     }
 
     # brute-force leg: the reference's O(rays x objects) search (filter + exact) on a bounded band of the same frame
@@ -499,7 +501,7 @@ def main():
             "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": dict(config, accel=["brute", "filter", "bvh"][accel_used], pipeline=["megakernel", "wavefront"][pipeline_used],
+            "config": dict(config, accel=["brute", "filter", "bvh", "perspective grids + bvh"][accel_used], pipeline=["megakernel", "wavefront"][pipeline_used],
                            sharding="row-blocks of %d rows round-robin over %d ranks, peer stores into rank 0 (CUDA IPC)" % (args.block_rows, world)
                            if world > 1 else "single GPU",
                            l2="framebuffer %d MB > L2; 256 MB memset between steps flushes L2 (scene is re-read from HBM each step)" % (W * H * 16 >> 20),

@@ -54,7 +54,11 @@ typedef enum rt_accel {
     RT_ACCEL_AUTO = -1,
     RT_ACCEL_BRUTE = 0, /* every ray x every object, the reference's arithmetic on every pair   */
     RT_ACCEL_CULL = 1,  /* every ray x every object, conservative bounding-sphere reject first  */
-    RT_ACCEL_BVH = 2    /* bounding volume hierarchy, conservative traversal, exact leaf tests  */
+    RT_ACCEL_BVH = 2,   /* bounding volume hierarchy, conservative traversal, exact leaf tests  */
+    RT_ACCEL_GRID = 3   /* wavefront pipeline: rays through a common point -- camera rays (all start at the view-space origin,
+                         * OpenCL-Raytracer.cpp:68-72) and shadow rays of point lights (their line passes through the light,
+                         * shade_and_reflect_kernel.cl:196-209) -- look up ONE cell of a perspective grid around that point and
+                         * walk its sorted object list; every other ray uses the BVH.  On the megakernel it is the BVH. */
 } rt_accel;
 
 /* Material.hpp:6-11 / cl_Material OpenCLRaytracer.hpp:32-39 (tightly packed here). */
@@ -125,6 +129,7 @@ typedef enum rt_option {
                                   device (scenes that change every frame: ~1 ms instead of ~150 ms per 10^5 objects, a looser tree) */
     RT_OPT_LANES = 7,      /* 2 (default): camera launches of the wavefront pipeline run as two halves on two streams, each filling the
                               thin generation tails of the other; 1: one launch sequence */
+    RT_OPT_GRID_RES = 8,   /* cells per side of each of the six perspective grids around a light (default 512, 32..4096) */
     RT_OPT_READBACK_BANDS = 5  /* rt_render of a large camera frame (or shard of one): bands of rows / row-blocks whose readback
                                   overlaps the next band's kernels, shrinking geometrically by the measured kernel : copy time
                                   ratio of the previous frame.  0 (default) = 2 bands, n = n bands,

@@ -14,6 +14,7 @@
 #include "../../include/rt_b200.h"
 #include "rt_kernels.cuh"
 #include "rt_lbvh.cuh"
+#include "rt_pgrid_build.cuh"
 #include "rt_scene.hpp"
 #include "rt_wavefront.cuh"
 
@@ -105,6 +106,23 @@ struct rt_ctx {
     int last_pipeline = 0;
     uint32_t last_launches = 1;
 
+    // perspective grids (rt_pgrid.cuh): one set for the camera, one for the lights, built lazily on the device
+    struct GridBufs {
+        DevBuf<rt::PGrid> grids;
+        DevBuf<uint32_t> cell_start;
+        DevBuf<rt::GridEntry> entries;
+        rt::GridSet set;
+        bool dirty = true;
+        uint64_t n_entries = 0;
+        uint32_t n_cells = 0;
+        float build_ms = 0.f;
+    } g_cam, g_lit;
+    DevBuf<uint32_t> g_cursor;
+    DevBuf<char> g_scan;
+    uint32_t g_cam_w = 0, g_cam_h = 0;
+    float g_cam_z = 0.f;
+    int opt_grid_res = 512;
+
     // options
     int opt_pipeline = -1, opt_count = 0, opt_leaf = 1, opt_skip_dead = 1, opt_bands = 0, opt_builder = 0, opt_lanes = 2;
     // banded readback: kernel time : copy time of the same rows, measured on the previous banded frame
@@ -183,6 +201,112 @@ int sync_scene(rt_ctx* c) {
     s.root_f = c->hs.f_global;
     s.filter_h = c->hs.h_min;
     c->scene_dirty = false;
+    c->g_cam.dirty = c->g_lit.dirty = true;
+    c->g_cam.set = c->g_lit.set = rt::GridSet{};
+    return RT_OK;
+}
+
+// Build one set of perspective grids on the device (rt_pgrid.cu): count, scan, fill, sort.  `grids` arrive without
+// cell_base.  A set whose lists would be out of proportion (an apex buried in large objects) is dropped -- its rays then
+// use the BVH -- by returning with set.valid_mask == 0.
+int build_grid_set(rt_ctx* c, rt_ctx::GridBufs& gb, std::vector<rt::PGrid>& grids, uint32_t valid_mask) {
+    gb.set = rt::GridSet{};
+    gb.n_entries = 0;
+    gb.n_cells = 0;
+    gb.dirty = false;
+    uint64_t cells = 0;
+    for (rt::PGrid& g : grids) {
+        g.cell_base = (uint32_t)cells;
+        cells += (uint64_t)g.nu * g.nv;
+    }
+    if (valid_mask == 0u || cells == 0 || cells >= (1ull << 28)) return RT_OK;
+    const uint32_t n_cells = (uint32_t)cells, n_grids = (uint32_t)grids.size(), n_objs = c->hs.n_objs;
+    const auto t0 = std::chrono::steady_clock::now();
+    RT_CUDA(gb.grids.ensure(n_grids));
+    RT_CUDA(cudaMemcpyAsync(gb.grids.p, grids.data(), n_grids * sizeof(rt::PGrid), cudaMemcpyHostToDevice, c->stream));
+    RT_CUDA(gb.cell_start.ensure((size_t)n_cells + 1));
+    RT_CUDA(c->g_cursor.ensure((size_t)n_cells + 1));
+    const size_t sb = rt::pgrid_scan_bytes(n_cells);
+    RT_CUDA(c->g_scan.ensure(sb));
+    RT_CUDA(rt::pgrid_count(gb.grids.p, n_grids, n_cells, c->d_cull.p, n_objs, c->hs.omax, c->g_cursor.p, gb.cell_start.p, c->g_scan.p, sb, c->stream));
+    uint32_t total = 0;
+    RT_CUDA(cudaMemcpyAsync(&total, gb.cell_start.p + n_cells, sizeof total, cudaMemcpyDeviceToHost, c->stream));
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    if ((uint64_t)total > 96ull * n_objs + 4ull * n_cells + (1ull << 20)) return RT_OK;  // not worth it: BVH instead
+    RT_CUDA(gb.entries.ensure(std::max<size_t>(total, 1)));
+    RT_CUDA(rt::pgrid_fill(gb.grids.p, n_grids, n_cells, c->d_cull.p, n_objs, c->hs.omax, c->g_cursor.p, gb.cell_start.p, gb.entries.p, c->stream));
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    gb.set.grids = gb.grids.p;
+    gb.set.cell_start = gb.cell_start.p;
+    gb.set.entries = gb.entries.p;
+    gb.set.n_grids = n_grids;
+    gb.set.valid_mask = valid_mask;
+    gb.n_entries = total;
+    gb.n_cells = n_cells;
+    gb.build_ms = (float)std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return RT_OK;
+}
+
+// The camera's grid: apex = the view-space origin every primary ray starts from (OpenCL-Raytracer.cpp:68-72), cells = tiles of
+// TW x TH pixels (8 x 4, the patch one warp of wave_gen covers, unless the frame has more than 2 M of them).
+int build_camera_grid(rt_ctx* c) {
+    std::vector<rt::PGrid> grids(1);
+    rt::PGrid& g = grids[0];
+    memset(&g, 0, sizeof g);
+    const float f = -c->zdir;
+    uint32_t tw = 8, th = 4;
+    while ((uint64_t)((c->width + tw - 1) / tw) * ((c->height + th) / th) > (2ull << 20)) (tw <= th ? tw : th) *= 2;
+    const float half_w = (float)c->width / 2.0f, half_h = (float)c->height / 2.0f;
+    uint32_t valid = 0;
+    if (c->use_camera && f > 0.f && std::isfinite(f) && half_w / f < 30.f && half_h / f < 30.f && c->hs.n_objs > 0) {
+        g.ax = g.ay = g.az = 0.f;
+        g.axis = 2u | 4u;  // looks down -z
+        g.u0 = -half_w / f;
+        g.v0 = -half_h / f;
+        g.inv_du = f / (float)tw;
+        g.inv_dv = f / (float)th;
+        g.nu = (c->width + tw - 1) / tw;
+        g.nv = c->height / th + 1;  // dir.y = (H - jj) - H/2 runs from -H/2 + 1 to H/2 inclusive
+        g.kind = 0;
+        valid = 1;
+    }
+    c->g_cam_w = c->width;
+    c->g_cam_h = c->height;
+    c->g_cam_z = c->zdir;
+    return build_grid_set(c, c->g_cam, grids, valid);
+}
+
+// Six grids (a cube map) around every point light; a light at infinity (position.w == 0, SAR:198) has parallel shadow rays
+// and keeps the BVH.
+int build_light_grids(rt_ctx* c) {
+    const uint32_t L = std::min<uint32_t>((uint32_t)c->lights.size(), RT_GRID_MAX_LIGHTS);
+    int res = c->opt_grid_res;
+    for (int attempt = 0; attempt < 3; ++attempt, res /= 2) {
+        std::vector<rt::PGrid> grids(6 * (size_t)L);
+        uint32_t valid = 0;
+        for (uint32_t li = 0; li < L; ++li) {
+            const rt_light& lt = c->lights[li];
+            const bool ok = lt.position[3] != 0.f && std::isfinite(lt.position[0]) && std::isfinite(lt.position[1]) && std::isfinite(lt.position[2]) &&
+                            c->hs.n_objs > 0;
+            for (uint32_t face = 0; face < 6; ++face) {
+                rt::PGrid& g = grids[6 * li + face];
+                memset(&g, 0, sizeof g);
+                if (!ok) continue;
+                g.ax = lt.position[0];
+                g.ay = lt.position[1];
+                g.az = lt.position[2];
+                g.axis = (face % 3u) | (face >= 3u ? 4u : 0u);
+                g.u0 = g.v0 = -1.f;
+                g.inv_du = g.inv_dv = (float)res / 2.f;
+                g.nu = g.nv = (uint32_t)res;
+                g.kind = 1;
+            }
+            if (ok) valid |= 1u << li;
+        }
+        const int rc = build_grid_set(c, c->g_lit, grids, valid);
+        if (rc != RT_OK) return rc;
+        if (c->g_lit.set.valid_mask || valid == 0u || res <= 64) break;
+    }
     return RT_OK;
 }
 
@@ -191,7 +315,7 @@ int pick_accel(const rt_ctx* c, int accel) {
         const size_t m = c->objs.size();
         if (m <= 4) return RT_ACCEL_BRUTE;
         if (m <= 48) return RT_ACCEL_CULL;
-        return RT_ACCEL_BVH;
+        return RT_ACCEL_GRID;
     }
     return accel;
 }
@@ -199,7 +323,7 @@ int pick_accel(const rt_ctx* c, int accel) {
 int check_render_args(rt_ctx* c, int mode, int accel) {
     if (!c) return fail(RT_ERR_INVALID, "null context");
     if (mode < RT_MODE_HITTEST || mode > RT_MODE_SHADE_AND_REFLECT) return fail(RT_ERR_INVALID, "bad mode");
-    if (accel < RT_ACCEL_AUTO || accel > RT_ACCEL_BVH) return fail(RT_ERR_INVALID, "bad accel");
+    if (accel < RT_ACCEL_AUTO || accel > RT_ACCEL_GRID) return fail(RT_ERR_INVALID, "bad accel");
     if (!c->use_camera && !c->have_rays) return fail(RT_ERR_INVALID, "neither rt_set_rays nor rt_set_camera was called");
     return RT_OK;
 }
@@ -311,16 +435,19 @@ int collect_stats(rt_ctx* c, int accel, uint64_t pixels, uint32_t launches) {
 
 // 0 megakernel, 1 wavefront.  The wavefront always skips dead rays, so asking for every reference ray
 // (RT_OPT_SKIP_DEAD_RAYS = 0) selects the megakernel; tiny scenes are launch-bound and stay on the megakernel too.
-int pick_pipeline(const rt_ctx* c, int accel) {
+constexpr uint32_t kMaxWaveGenerations = 4096;
+int pick_pipeline(const rt_ctx* c, int accel, uint32_t max_bounces, int mode) {
     if (!c->opt_skip_dead) return 0;
     if (c->opt_pipeline == 0 || c->opt_pipeline == 1) return c->opt_pipeline;
+    // many lights x many bounces: thousands of (mostly empty) generations -- the megakernel handles those in-thread
+    if (rt::wave_max_generations(max_bounces, (uint32_t)c->lights.size(), mode) > kMaxWaveGenerations) return 0;
     return (accel != RT_ACCEL_BRUTE && c->objs.size() > 48) ? 1 : 0;
 }
 
 // Wavefront buffers for `capacity` paths, handed out as two halves (lanes) that run on two streams; lane 0 alone may
 // use everything (wb[0].capacity == capacity).
 int ensure_wave_buffers(rt_ctx* c, uint64_t capacity, uint32_t gens, rt::WaveBuffers wb[2]) {
-    if (capacity >= (1ull << 31)) return fail(RT_ERR_INVALID, "too many rays for one wavefront context");
+    if (capacity > RT_TASK_PATH_MASK) return fail(RT_ERR_INVALID, "too many rays for one wavefront context (2^27 - 1 per GPU; shard the frame)");
     RT_CUDA(c->w_acc.ensure(capacity));
     RT_CUDA(c->w_refl.ensure(capacity));
     RT_CUDA(c->w_P.ensure(capacity));
@@ -334,7 +461,7 @@ int ensure_wave_buffers(rt_ctx* c, uint64_t capacity, uint32_t gens, rt::WaveBuf
     }
     RT_CUDA(c->w_res_t.ensure(capacity));
     RT_CUDA(c->w_res_id.ensure(capacity));
-    const size_t per_lane = 2 * (size_t)(gens + 2);
+    const size_t per_lane = 4 * (size_t)(gens + 2);
     RT_CUDA(c->w_counts.ensure(2 * per_lane));
     const uint64_t half = (capacity / 2) & ~(uint64_t)255;  // lane 1 starts here
     for (int l = 0; l < 2; ++l) {
@@ -353,8 +480,9 @@ int ensure_wave_buffers(rt_ctx* c, uint64_t capacity, uint32_t gens, rt::WaveBuf
         wb[l].res_t = c->w_res_t.p + o;
         wb[l].res_id = c->w_res_id.p + o;
         wb[l].counts = c->w_counts.p + l * per_lane;
-        wb[l].n_counts = (uint32_t)(per_lane / 2);
+        wb[l].n_counts = (uint32_t)(per_lane / 4);
         wb[l].capacity = l ? capacity - half : capacity;
+        wb[l].qcap = (uint32_t)wb[l].capacity;  // lane 0 of a two-lane launch is cut down to `half` by the caller
     }
     return RT_OK;
 }
@@ -370,8 +498,20 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
     if (rc != RT_OK) return rc;
     accel = pick_accel(c, accel);
     *accel_used = accel;
-    const int pipeline = pick_pipeline(c, accel);
+    const int pipeline = pick_pipeline(c, accel, max_bounces, mode);
     c->last_pipeline = pipeline;
+    if (accel == RT_ACCEL_GRID && pipeline == 1) {  // perspective grids, (re)built on the device when the scene / the camera changed
+        if (c->g_lit.dirty) {
+            rc = build_light_grids(c);
+            if (rc != RT_OK) return rc;
+        }
+        if (c->use_camera && (c->g_cam.dirty || c->g_cam_w != c->width || c->g_cam_h != c->height || c->g_cam_z != c->zdir)) {
+            rc = build_camera_grid(c);
+            if (rc != RT_OK) return rc;
+        }
+    } else if (accel == RT_ACCEL_GRID) {
+        *accel_used = RT_ACCEL_BVH;  // the megakernel has no grid search
+    }
     if (c->opt_count) {
         RT_CUDA(c->d_counters.ensure(1));
         if (band <= 0) RT_CUDA(cudaMemsetAsync(c->d_counters.p, 0, sizeof(rt::Counters), c->stream));
@@ -380,7 +520,7 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
 
     if (pipeline == 1) {
         const uint32_t gens = rt::wave_max_generations(max_bounces, c->scene.n_lights, mode);
-        if (gens > 4096) return fail(RT_ERR_INVALID, "max_bounces x lights too large for the wavefront pipeline; use RT_OPT_PIPELINE 0");
+        if (gens > kMaxWaveGenerations) return fail(RT_ERR_INVALID, "max_bounces x lights too large for the wavefront pipeline; use RT_OPT_PIPELINE 0");
         // unit range of this launch
         uint32_t u0 = 0, u1 = 0;
         if (c->use_camera) {
@@ -410,6 +550,10 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
             fr[0].hit_id = c->d_hit_id.p;
             fr[0].hit_t = c->d_hit_t.p;
         }
+        if (lanes) wb[0].qcap = (uint32_t)(wb[0].capacity - wb[1].capacity);
+        rt::WaveGrids wg;
+        wg.cam = c->use_camera ? c->g_cam.set : rt::GridSet{};
+        wg.lit = c->g_lit.set;
         if (fr[0].n_local > wb[0].capacity || (lanes && (fr[0].n_local > wb[0].capacity - wb[1].capacity || fr[1].n_local > wb[1].capacity)))
             return fail(RT_ERR_INVALID, "internal: wavefront buffers too small for the launch");
         if (band <= 0) RT_CUDA(cudaEventRecord(c->ev0, c->stream));
@@ -418,10 +562,10 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
             RT_CUDA(cudaEventRecord(c->lane_go, c->stream));  // lane 1 starts after everything queued before this launch
             RT_CUDA(cudaStreamWaitEvent(c->lane_stream, c->lane_go, 0));
         }
-        if (fr[0].n_local > 0) RT_CUDA(rt::wave_render(c->scene, fr[0], wb[0], accel, (uint32_t)c->opt_leaf, c->sm_count, &nl, c->stream));
+        if (fr[0].n_local > 0) RT_CUDA(rt::wave_render(c->scene, fr[0], wb[0], accel, &wg, c->sm_count, &nl, c->stream));
         if (lanes) {
             if (fr[1].n_local > 0)
-                RT_CUDA(rt::wave_render(c->scene, fr[1], wb[1], accel, (uint32_t)c->opt_leaf, c->sm_count, &nl1, c->lane_stream));
+                RT_CUDA(rt::wave_render(c->scene, fr[1], wb[1], accel, &wg, c->sm_count, &nl1, c->lane_stream));
             RT_CUDA(cudaEventRecord(c->lane_done, c->lane_stream));
             RT_CUDA(cudaStreamWaitEvent(c->stream, c->lane_done, 0));
         }
@@ -506,6 +650,9 @@ int rt_destroy(rt_ctx* c) {
     c->d_cull.release(); c->d_leaf_cull.release(); c->d_nodes.release(); c->d_lbvh_leaves.release(); c->d_lbvh_scratch.release(); c->d_leaf_obj.release();
     c->d_rays.release(); c->d_fb.release(); c->d_hit_id.release(); c->d_hit_t.release(); c->d_counters.release();
     c->d_sink.release();
+    c->g_cam.grids.release(); c->g_cam.cell_start.release(); c->g_cam.entries.release();
+    c->g_lit.grids.release(); c->g_lit.cell_start.release(); c->g_lit.entries.release();
+    c->g_cursor.release(); c->g_scan.release();
     c->w_acc.release(); c->w_refl.release(); c->w_P.release(); c->w_Nm.release(); c->w_Rc.release(); c->w_out.release();
     for (int i = 0; i < 2; ++i) { c->w_qs[i].release(); c->w_qd[i].release(); c->w_qpath[i].release(); }
     c->w_res_t.release(); c->w_res_id.release(); c->w_counts.release();
@@ -544,6 +691,11 @@ int rt_set_option(rt_ctx* c, int option, int64_t value) {
         case RT_OPT_READBACK_BANDS:
             if (value < 0 || value > rt_ctx::kMaxBands) return fail(RT_ERR_INVALID, "readback bands must be 0 (auto) or 1..16");
             c->opt_bands = (int)value;
+            return RT_OK;
+        case RT_OPT_GRID_RES:
+            if (value < 32 || value > 4096) return fail(RT_ERR_INVALID, "grid resolution must be 32..4096");
+            c->opt_grid_res = (int)value;
+            c->g_lit.dirty = true;
             return RT_OK;
         case RT_OPT_LANES:
             if (value < 1 || value > 2) return fail(RT_ERR_INVALID, "lanes must be 1 or 2");
@@ -598,6 +750,7 @@ int rt_set_camera(rt_ctx* c, uint32_t width, uint32_t height, float zdir) {
     c->height = height;
     c->zdir = zdir;
     c->use_camera = true;
+    c->g_cam.dirty = true;
     RT_CUDA(c->d_fb.ensure((uint64_t)width * height));
     return RT_OK;
 }
@@ -639,7 +792,7 @@ int rt_render(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float* host_
     // copy of a finished band (copy stream) overlaps the kernels of the next one (compute stream).
     const int nb = auto_bands(c);
     const bool banded = c->use_camera && nb > 1 && local_pixels(c) >= (1ull << 21) && band_units(c) >= (uint32_t)(4 * nb) &&
-                        c->have_scene && pick_pipeline(c, pick_accel(c, accel)) == 1;
+                        c->have_scene && pick_pipeline(c, pick_accel(c, accel), max_bounces, mode) == 1;
     if (banded) {
         uint32_t units0 = 0;  // units of the first band: its copy is timed for the next frame's split
         for (int b = 0; b < nb; ++b) {
@@ -762,7 +915,7 @@ int rt_render_aov(rt_ctx* c, int accel, int32_t* host_hit_id, float* host_hit_t)
 
 int rt_trace(rt_ctx* c, const rt_ray* host_rays, uint64_t n, int accel, int32_t* host_hit_id, float* host_hit_t) {
     if (!c) return fail(RT_ERR_INVALID, "null context");
-    if (accel < RT_ACCEL_AUTO || accel > RT_ACCEL_BVH) return fail(RT_ERR_INVALID, "bad accel");
+    if (accel < RT_ACCEL_AUTO || accel > RT_ACCEL_GRID) return fail(RT_ERR_INVALID, "bad accel");
     if (n && (!host_rays || !host_hit_id || !host_hit_t)) return fail(RT_ERR_INVALID, "null argument");
     RT_CUDA(cudaSetDevice(c->device));
     double omax2 = 0.0;
@@ -784,6 +937,7 @@ int rt_trace(rt_ctx* c, const rt_ray* host_rays, uint64_t n, int accel, int32_t*
         return rc;
     }
     accel = pick_accel(c, accel);
+    if (accel == RT_ACCEL_GRID) accel = RT_ACCEL_BVH;  // arbitrary rays have no common apex
     DevBuf<rt::Ray> rays;
     DevBuf<int32_t> ids;
     DevBuf<float> ts;

@@ -26,12 +26,19 @@ struct PathArrays {
     uint32_t* out;  // framebuffer index of the path
 };
 
+// A generation's queue is ONE array filled from both ends: tasks for the BVH / filter / brute-force kernels ("class B":
+// reflection rays, shadow rays of lights without grids, everything when the grids are off) occupy [0, nB), tasks for the
+// perspective-grid kernel ("class A": camera rays, shadow rays of point lights; rt_pgrid.cuh) occupy (cap - 1 - j),
+// j in [0, nA).  Counters: count[2 g] = nB, count[2 g + 1] = nA of generation g.
 struct TaskQueue {
     float4* s;       // ray start
     float4* d;       // ray direction
-    uint32_t* path;  // path id | RT_TASK_ANYHIT
+    uint32_t* path;  // path id | light code << 27 | RT_TASK_ANYHIT
 };
 #define RT_TASK_ANYHIT 0x80000000u
+#define RT_TASK_LIGHT_SHIFT 27
+#define RT_TASK_NO_GRID 15u         // light code of a shadow ray whose light has no grids (and of every non-shadow ray)
+#define RT_TASK_PATH_MASK 0x07ffffffu
 
 // ctrl word: phase (2 bits) | last-light-lit flag | light index of the shadow ray in flight
 #define RT_PH_PRIMARY 0u
@@ -44,11 +51,14 @@ struct TaskQueue {
 struct WaveParams {
     uint32_t max_bounces;
     int mode;
+    uint32_t grid_lights;  // bit li: shadow rays of light li go to the perspective-grid kernel (0: grids off)
+    uint32_t qcap;         // capacity of one task queue of this launch sequence (class A tasks sit at qcap - 1 - j)
 };
 
 struct StepOut {
     bool emit;    // a new ray goes into the next queue
     bool anyhit;  // ... and it is a shadow ray
+    uint32_t light;  // ... of this light
     Ray ray;
     bool write;   // the path is finished: px goes to the framebuffer
     float4 px;
@@ -64,6 +74,7 @@ __device__ __forceinline__ void emit_shadow(const Scene& sc, uint32_t li, const 
     o.ray = shadow_ray(sc.lights[li], P, lv);
     o.emit = true;
     o.anyhit = true;
+    o.light = li;
 }
 
 // SAR:281-284: the post-loop rule and the pixel store.
@@ -156,6 +167,7 @@ template <bool COUNT>
 __device__ __forceinline__ void step(const Scene& sc, const WaveParams& wp, const PathArrays& pa, uint32_t p, bool first,
                                      const Ray& ray, const Hit res, StepOut& o, LocalCounters& lc) {
     o.emit = o.write = o.anyhit = false;
+    o.light = RT_TASK_NO_GRID;
     uint32_t ctrl = RT_PH_PRIMARY;
     float4 rc = make_float4(0.f, 0.f, 0.f, 0.f);
     if (!first) {

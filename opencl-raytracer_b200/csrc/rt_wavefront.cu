@@ -14,6 +14,7 @@
 
 #include <stdlib.h>
 
+#include "rt_pgrid.cuh"
 #include "rt_wave.cuh"
 
 namespace rt {
@@ -82,8 +83,44 @@ __device__ __forceinline__ uint32_t block_append(bool emit, uint32_t* counter, u
     return sh[warp] + (uint32_t)__popc(m & lanemask_lt());
 }
 
+// The same for the two ends of a queue at once (class B: front, class A: back): both per-warp counts travel through the
+// scan packed into one word (a block emits at most 256 of each), lanes 0 and 1 of warp 0 do the two atomics.  Returns the
+// slot in the queue end the thread emits to (emit_a wins if both are set).  sh holds 2 * kBlock/32 words.
+__device__ __forceinline__ uint32_t block_append2(bool emit_b, bool emit_a, uint32_t* count_b, uint32_t* count_a, uint32_t* sh) {
+    constexpr unsigned kWarps = kBlock / 32;
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const unsigned ma = __ballot_sync(kFull, emit_a), mb = __ballot_sync(kFull, emit_b && !emit_a);
+    if (lane == 0) sh[warp] = (uint32_t)__popc(mb) | ((uint32_t)__popc(ma) << 16);
+    __syncthreads();
+    if (warp == 0) {
+        const uint32_t c = lane < kWarps ? sh[lane] : 0u;
+        uint32_t incl = c;
+#pragma unroll
+        for (unsigned o = 1; o < kWarps; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(kFull, incl, o);
+            if (lane >= o) incl += v;
+        }
+        const uint32_t total = __shfl_sync(kFull, incl, kWarps - 1);
+        uint32_t base = 0;
+        if (lane == 0 && (total & 0xffffu)) base = atomicAdd(count_b, total & 0xffffu);
+        if (lane == 1 && (total >> 16)) base = atomicAdd(count_a, total >> 16);
+        const uint32_t base_b = __shfl_sync(kFull, base, 0), base_a = __shfl_sync(kFull, base, 1);
+        const uint32_t excl = incl - c;
+        // two 32-bit bases do not fit the packed word: store B's slot base here, A's in the second half of sh
+        if (lane < kWarps) {
+            sh[lane] = base_b + (excl & 0xffffu);
+            sh[kWarps + lane] = base_a + (excl >> 16);
+        }
+    }
+    __syncthreads();
+    if (emit_a) return sh[kWarps + warp] + (uint32_t)__popc(ma & lanemask_lt());
+    return sh[warp] + (uint32_t)__popc(mb & lanemask_lt());
+}
+
 // ------------------------------------------------------------------------------------------------ generation 0
-__global__ void __launch_bounds__(kBlock) wave_gen(const Frame fr, const TaskQueue q, const PathArrays pa, uint32_t* __restrict__ count, const uint32_t strip) {
+// to_grid != 0: the camera has a perspective grid, the primary rays are class A tasks (back of the queue, counter count[1])
+__global__ void __launch_bounds__(kBlock) wave_gen(const Frame fr, const TaskQueue q, const PathArrays pa, uint32_t* __restrict__ count, const uint32_t strip,
+                                                   const uint32_t to_grid, const uint32_t qcap) {
     bool active;
     uint64_t oi = 0;
     Ray ray;
@@ -121,11 +158,12 @@ __global__ void __launch_bounds__(kBlock) wave_gen(const Frame fr, const TaskQue
         }
     }
     __shared__ uint32_t sh_append[kBlock / 32];
-    const uint32_t slot = block_append(active, count, sh_append);
+    const uint32_t slot = block_append(active, count + (to_grid ? 1 : 0), sh_append);
     if (active) {
-        q.s[slot] = ray.s;
-        q.d[slot] = ray.d;
-        q.path[slot] = slot;  // path id == slot of the primary task
+        const uint32_t at = to_grid ? qcap - 1u - slot : slot;
+        q.s[at] = ray.s;
+        q.d[at] = ray.d;
+        q.path[at] = slot | (RT_TASK_NO_GRID << RT_TASK_LIGHT_SHIFT);  // path id == slot of the primary task
         pa.out[slot] = (uint32_t)oi;
     }
 }
@@ -310,6 +348,147 @@ __global__ void __launch_bounds__(kBlock, RT_BVH_MINB) wave_trace_bvh(const Scen
         if (have && tdone && npend == 0) {
             res_t[task] = best.id >= 0 ? best.t : RT_MAX_FLOAT;
             res_id[task] = best.id;
+            have = false;
+        }
+    }
+    if (COUNT) flush_local(lc, ctr);
+}
+
+// ------------------------------------------------------------------------------------------------ trace: perspective grids
+// Class A tasks (rt_wave.cuh): camera rays and shadow rays of point lights.  Same persistent-warp scheme as the BVH
+// kernel, but a lane's "traversal" is a walk along ONE sorted list -- the cell of its direction as seen from the apex
+// (rt_pgrid.cuh): load the next entry, stop if it lies beyond the current hit (camera) or behind the ray start (shadow),
+// bounding-sphere filter, and a survivor waits for the warp's next round of exact tests.  Rays of one 8x4 pixel tile
+// share their cell, so a warp of primary rays walks its list in lockstep with broadcast loads.
+#ifndef RT_GRID_MINB
+#define RT_GRID_MINB 4
+#endif
+template <bool COUNT>
+__global__ void __launch_bounds__(kBlock, RT_GRID_MINB) wave_trace_grid(const Scene sc, const GridSet cam, const GridSet lit, const TaskQueue q,
+                                                                       const uint32_t* __restrict__ n_ptr, uint32_t* __restrict__ fetch,
+                                                                       float* __restrict__ res_t, int32_t* __restrict__ res_id, const uint32_t qcap,
+                                                                       const int min_t, const int drain_t, const int refill_t, Counters* ctr) {
+    const uint32_t n = *n_ptr;
+    if (n == 0u) return;
+    const unsigned lane = threadIdx.x & 31u;
+    LocalCounters lc;
+    const uint32_t kNone = 0xffffffffu;
+    const float4* cull4 = reinterpret_cast<const float4*>(sc.cull);
+
+    bool have = false, anyhit = false;
+    uint32_t at = 0;  // index of the lane's task in the queue arrays
+    float ox = 0.f, oy = 0.f, oz = 0.f, ux = 0.f, uy = 0.f, uz = 0.f, dlen = 0.f, cutoff = 0.f;
+    Hit best;
+    best.t = RT_MAX_FLOAT;
+    best.id = -1;
+    uint32_t btype = 0, cur = 0, end = 0, pend = kNone, ptype = 0;
+    const GridEntry* ent = cam.entries;
+    bool exhausted = false;
+
+    for (;;) {
+        // ---- refill
+        {
+            const unsigned idle = __ballot_sync(kFull, !have);
+            const unsigned walk = __ballot_sync(kFull, have && pend == kNone && cur < end);
+            if (idle && !exhausted && (__popc(idle) >= refill_t || walk == 0u)) {
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(fetch, (uint32_t)__popc(idle));
+                base = __shfl_sync(kFull, base, 0);
+                if (!have) {
+                    const uint32_t i = base + (uint32_t)__popc(idle & lanemask_lt());
+                    if (i < n) {
+                        at = qcap - 1u - i;
+                        const float4 s = q.s[at], d = q.d[at];
+                        const uint32_t pw = q.path[at];
+                        anyhit = (pw & RT_TASK_ANYHIT) != 0u;
+                        ox = s.x; oy = s.y; oz = s.z;
+                        const float l2 = fmaf(d.z, d.z, fmaf(d.y, d.y, d.x * d.x));
+                        dlen = sqrtf(l2);
+                        const float il = 1.f / dlen;
+                        ux = d.x * il; uy = d.y * il; uz = d.z * il;
+                        PGrid g;
+                        float wx = d.x, wy = d.y, wz = d.z;
+                        const uint32_t* cs;
+                        if (anyhit) {
+                            wx = -wx; wy = -wy; wz = -wz;
+                            const uint32_t li = (pw >> RT_TASK_LIGHT_SHIFT) & 15u;
+                            g = lit.grids[6u * li + pgrid_face(wx, wy, wz)];
+                            cs = lit.cell_start;
+                            ent = lit.entries;
+                            const float ax = s.x - g.ax, ay = s.y - g.ay, az = s.z - g.az;
+                            cutoff = sqrtf(fmaf(az, az, fmaf(ay, ay, ax * ax))) * 1.0001f + 1e-4f;
+                        } else {
+                            g = cam.grids[0];
+                            cs = cam.cell_start;
+                            ent = cam.entries;
+                            cutoff = RT_MAX_FLOAT;
+                        }
+                        const uint32_t cell = pgrid_cell(g, wx, wy, wz);
+                        cur = __ldg(cs + cell);
+                        end = __ldg(cs + cell + 1);
+                        best.t = RT_MAX_FLOAT;
+                        best.id = -1;
+                        btype = 0;
+                        pend = kNone;
+                        have = true;
+                    }
+                }
+                if (base + (uint32_t)__popc(idle) >= n) exhausted = true;
+            }
+            if (!__any_sync(kFull, have)) break;
+        }
+
+        // ---- list steps
+        for (;;) {
+            const bool go = have && pend == kNone && cur < end;
+            const unsigned T = __ballot_sync(kFull, go);
+            if (T == 0u) break;
+            if (__popc(T) < min_t) {
+                if (__popc(__ballot_sync(kFull, have && pend != kNone)) >= drain_t) break;
+                if (!exhausted && __popc(__ballot_sync(kFull, !have || (pend == kNone && cur >= end))) >= refill_t) break;
+            }
+            if (go) {
+                const GridEntry e = ent[cur];
+                ++cur;
+                if (e.dnear > cutoff) {
+                    cur = end;
+                } else {
+                    const float4 a = __ldg(cull4 + 2 * (size_t)e.obj), b = __ldg(cull4 + 2 * (size_t)e.obj + 1);
+                    if (COUNT) lc.pair_tests++;
+                    const float x = a.x - ox, y = a.y - oy, z = a.z - oz;
+                    const float oc2 = fmaf(z, z, fmaf(y, y, x * x));
+                    const float dt = fmaf(z, uz, fmaf(y, uy, x * ux));
+                    if (!(fmaf(-dt, dt, oc2 * b.x) > a.w)) {  // cv::sphere_may_hit
+                        pend = e.obj;
+                        ptype = __float_as_uint(b.w);
+                    }
+                }
+            }
+        }
+
+        // ---- exact tests: when enough lanes hold a survivor, or nobody can walk on
+        {
+            const bool has = have && pend != kNone;
+            const unsigned P = __ballot_sync(kFull, has);
+            const unsigned W = __ballot_sync(kFull, have && pend == kNone && cur < end);
+            if (P != 0u && (__popc(P) >= drain_t || W == 0u)) {
+                if (has) {
+                    exact_pair_call(sc, q.s[at], q.d[at], pend, ptype, best, btype);
+                    if (COUNT) lc.exact_tests++;
+                    pend = kNone;
+                    if (anyhit) {
+                        if (best.t < 1.f) cur = end;  // the shadow ray is decided (SAR:229)
+                    } else if (best.id >= 0) {
+                        cutoff = best.t * dlen * 1.0001f + 1e-4f;  // distance apex -> hit point (the ray starts at the apex)
+                    }
+                }
+            }
+        }
+
+        // ---- retire
+        if (have && pend == kNone && cur >= end) {
+            res_t[at] = best.id >= 0 ? best.t : RT_MAX_FLOAT;
+            res_id[at] = best.id;
             have = false;
         }
     }
@@ -615,15 +794,21 @@ cudaError_t launch_filter(const Scene& sc, const TaskQueue& qin, const uint32_t*
     const unsigned fgrid = (unsigned)sm_count * MINB;
     const uint32_t split = fgrid * kBlock * RPT;
     const int bytes = TILE * 2 * (int)sizeof(float4);
-    static const cudaError_t attr = [] {
-        const int by = TILE * 2 * (int)sizeof(float4);
-        cudaError_t a = cudaFuncSetAttribute(wave_trace_filter<RPT, OPI, MINB, TILE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, by);
-        if (a == cudaSuccess) a = cudaFuncSetAttribute(wave_trace_filter<RPT, OPI, MINB, TILE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, by);
-        if (a == cudaSuccess) a = cudaFuncSetAttribute(wave_trace_filter<2, 1, MINB, TILE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, by);
-        if (a == cudaSuccess) a = cudaFuncSetAttribute(wave_trace_filter<2, 1, MINB, TILE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, by);
-        return a;
-    }();
-    if (attr != cudaSuccess) return attr;
+    {  // 64 KB of dynamic shared memory need the opt-in, and function attributes are per DEVICE: one process may drive
+       // several GPUs (CudaRaytracer::UseDevices), so the opt-in is made once for every device that launches the kernel
+        static bool done[64] = {};
+        int dev = 0;
+        cudaError_t a = cudaGetDevice(&dev);
+        if (a != cudaSuccess) return a;
+        if (dev < 0 || dev >= 64 || !done[dev]) {
+            a = cudaFuncSetAttribute(wave_trace_filter<RPT, OPI, MINB, TILE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+            if (a == cudaSuccess) a = cudaFuncSetAttribute(wave_trace_filter<RPT, OPI, MINB, TILE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+            if (a == cudaSuccess) a = cudaFuncSetAttribute(wave_trace_filter<2, 1, MINB, TILE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+            if (a == cudaSuccess) a = cudaFuncSetAttribute(wave_trace_filter<2, 1, MINB, TILE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+            if (a != cudaSuccess) return a;
+            if (dev >= 0 && dev < 64) done[dev] = true;
+        }
+    }
     // two instantiations, each takes the queue sizes it is efficient for (the size lives on the device)
     if (count) {
         wave_trace_filter<RPT, OPI, MINB, TILE, true><<<fgrid, kBlock, bytes, stream>>>(sc, qin, n_ptr, split, 0xffffffffu, res_t, res_id, ctr);
@@ -645,23 +830,27 @@ __global__ void __launch_bounds__(kBlock, RT_ADV_MINB) wave_advance(const Scene 
                                                        const float* __restrict__ res_t, const int32_t* __restrict__ res_id,
                                                        const int first, float4* __restrict__ fb, int32_t* __restrict__ aov_id,
                                                        float* __restrict__ aov_t, Counters* ctr) {
-    const uint32_t n = *n_in;
+    const uint32_t nb = n_in[0], na = n_in[1];  // class B tasks at [0, nb), class A tasks at qcap - 1 - j
+    const uint32_t n = nb + na;
     if (n == 0u) return;
     LocalCounters lc;
-    __shared__ uint32_t sh_append[kBlock / 32];
+    __shared__ uint32_t sh_append[2 * kBlock / 32];
+    const uint32_t back = wp.qcap - 1u;
     const uint64_t n_round = ((uint64_t)n + kBlock - 1u) / kBlock * kBlock;  // whole blocks take part in the append
     for (uint64_t i = (uint64_t)blockIdx.x * kBlock + threadIdx.x; i < n_round; i += (uint64_t)gridDim.x * kBlock) {
         StepOut o;
         o.emit = o.write = o.anyhit = false;
+        o.light = RT_TASK_NO_GRID;
         uint32_t p = 0;
         if (i < n) {
+            const uint32_t at = i < nb ? (uint32_t)i : back - ((uint32_t)i - nb);
             Ray ray;
-            ray.s = qin.s[i];
-            ray.d = qin.d[i];
-            p = qin.path[i] & ~RT_TASK_ANYHIT;
+            ray.s = qin.s[at];
+            ray.d = qin.d[at];
+            p = qin.path[at] & RT_TASK_PATH_MASK;
             Hit res;
-            res.t = res_t[i];
-            res.id = res_id[i];
+            res.t = res_t[at];
+            res.id = res_id[at];
             if (first && aov_id) {
                 const uint32_t oi = pa.out[p];
                 aov_id[oi] = res.id;
@@ -669,13 +858,21 @@ __global__ void __launch_bounds__(kBlock, RT_ADV_MINB) wave_advance(const Scene 
             }
             wave::step<COUNT>(sc, wp, pa, p, first != 0, ray, res, o, lc);
         }
-        const uint32_t slot = block_append(o.emit, n_out, sh_append);
-        if (o.emit) {
-            qout.s[slot] = o.ray.s;
-            qout.d[slot] = o.ray.d;
-            qout.path[slot] = p | (o.anyhit ? RT_TASK_ANYHIT : 0u);
+        // a shadow ray of a light with grids is a class A task -- unless it is not finite (a hit point at infinity): the BVH
+        // kernel lets such a ray reach the exact test on every object, as the reference does
+        bool to_a = false;
+        if (o.emit && o.anyhit && o.light < RT_TASK_NO_GRID && ((wp.grid_lights >> o.light) & 1u)) {
+            const float chk = o.ray.s.x + o.ray.s.y + o.ray.s.z + o.ray.d.x + o.ray.d.y + o.ray.d.z;
+            to_a = fabsf(chk) < __int_as_float(0x7f800000);
         }
-        if (o.write) fb[pa.out[p]] = o.px;  // one 128-bit store per finished pixel
+        const uint32_t slot = block_append2(o.emit, to_a, n_out, n_out + 1, sh_append);
+        if (o.emit) {
+            const uint32_t at = to_a ? back - slot : slot;
+            qout.s[at] = o.ray.s;
+            qout.d[at] = o.ray.d;
+            qout.path[at] = p | ((to_a ? o.light : RT_TASK_NO_GRID) << RT_TASK_LIGHT_SHIFT) | (o.anyhit ? RT_TASK_ANYHIT : 0u);
+        }
+        if (o.write && fb) fb[pa.out[p]] = o.px;  // one 128-bit store per finished pixel
     }
     if (COUNT) flush_local(lc, ctr);
 }
@@ -695,18 +892,24 @@ static int env_int(const char* name, int dflt) {
     return v && *v ? atoi(v) : dflt;
 }
 
-cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb, int accel, uint32_t leaf_max, int sm_count,
+cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb, int accel, const WaveGrids* grids, int sm_count,
                         uint32_t* launches, cudaStream_t stream) {
     // warp-scheduler thresholds of wave_trace_bvh (tunable for experiments)
     static const int min_t = env_int("RT_WAVE_MIN_T", 12), drain_t = env_int("RT_WAVE_DRAIN", 4), refill_t = env_int("RT_WAVE_REFILL", 16);
-    (void)leaf_max;
+    static const int g_min_t = env_int("RT_GRID_MIN_T", 12), g_drain_t = env_int("RT_GRID_DRAIN", 4), g_refill_t = env_int("RT_GRID_REFILL", 16);
     const uint32_t gens = wave_max_generations(fr.max_bounces, sc.n_lights, fr.mode);
     if (gens + 1 > wb.n_counts) return cudaErrorInvalidValue;
-    cudaError_t e = cudaMemsetAsync(wb.counts, 0, sizeof(uint32_t) * 2 * (size_t)wb.n_counts, stream);
+    if (wb.qcap == 0u || wb.qcap > RT_TASK_PATH_MASK) return cudaErrorInvalidValue;
+    cudaError_t e = cudaMemsetAsync(wb.counts, 0, sizeof(uint32_t) * 4 * (size_t)wb.n_counts, stream);
     if (e != cudaSuccess) return e;
-    uint32_t* qcount = wb.counts;                // qcount[g]: size of the queue of generation g
-    uint32_t* fetch = wb.counts + wb.n_counts;   // fetch[g]: dynamic-fetch cursor of generation g
+    uint32_t* qcount = wb.counts;                    // qcount[2 g], qcount[2 g + 1]: class B / class A tasks of generation g
+    uint32_t* fetch = wb.counts + 2 * wb.n_counts;   // fetch[2 g + class]: dynamic-fetch cursors
     uint32_t nl = 0;
+    // perspective grids: the BVH search with the rays through a common apex taken out (accel 3)
+    const bool use_grids = accel == 3 && grids != nullptr;
+    const bool cam_grid = use_grids && !fr.rays && (grids->cam.valid_mask & 1u);
+    const uint32_t light_grids = use_grids ? grids->lit.valid_mask : 0u;
+    const int accel_b = accel == 3 ? 2 : accel;
 
     unsigned grid0;
     if (fr.rays) {
@@ -719,22 +922,15 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
         return cudaSuccess;
     }
     static const int gen_strip = env_int("RT_GEN_STRIP", 64);
-    wave_gen<<<grid0, kBlock, 0, stream>>>(fr, wb.q[0], wb.pa, qcount + 0, (uint32_t)gen_strip);
+    wave_gen<<<grid0, kBlock, 0, stream>>>(fr, wb.q[0], wb.pa, qcount + 0, (uint32_t)gen_strip, cam_grid ? 1u : 0u, wb.qcap);
     ++nl;
     WaveParams wp;
     wp.max_bounces = fr.max_bounces;
     wp.mode = fr.mode;
-    {  // shared-memory carve-out of the trace kernel (percent of the SM's 228 KB; the rest is L1 for the BVH nodes)
-        static const cudaError_t carve = [] {
-            const int pct = env_int("RT_WAVE_CARVEOUT", -1);
-            if (pct < 0) return cudaSuccess;
-            cudaError_t a = cudaFuncSetAttribute(wave_trace_bvh<true>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
-            if (a == cudaSuccess) a = cudaFuncSetAttribute(wave_trace_bvh<false>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
-            return a;
-        }();
-        if (carve != cudaSuccess) return carve;
-    }
+    wp.grid_lights = light_grids;
+    wp.qcap = wb.qcap;
     const unsigned pgrid = (unsigned)sm_count * RT_BVH_MINB;  // persistent trace: RT_BVH_MINB CTAs of 8 warps per SM
+    const unsigned ggrid = (unsigned)sm_count * RT_GRID_MINB;
     const unsigned sgrid = (unsigned)sm_count * 8u;    // grid-stride kernels
     static const int adv_mult = env_int("RT_ADV_GRID", 3);  // = resident CTAs per SM; 3..32 measured within 1 %
     const unsigned agrid = (unsigned)sm_count * (unsigned)adv_mult;  // wave_advance
@@ -742,31 +938,44 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
     for (uint32_t g = 0; g < gens; ++g) {
         const TaskQueue& qin = wb.q[g & 1u];
         const TaskQueue& qout = wb.q[(g + 1u) & 1u];
-        if (accel == 2) {
+        uint32_t* nq = qcount + 2 * g;
+        // class A: generation 0 when the camera has a grid, later generations when a light has
+        if ((g == 0 && cam_grid) || (g > 0 && light_grids)) {
             if (count)
-                wave_trace_bvh<true><<<pgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, fetch + g, wb.res_t, wb.res_id, min_t, drain_t, refill_t, fr.counters);
+                wave_trace_grid<true><<<ggrid, kBlock, 0, stream>>>(sc, grids->cam, grids->lit, qin, nq + 1, fetch + 2 * g + 1, wb.res_t, wb.res_id, wb.qcap, g_min_t, g_drain_t, g_refill_t, fr.counters);
             else
-                wave_trace_bvh<false><<<pgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, fetch + g, wb.res_t, wb.res_id, min_t, drain_t, refill_t, fr.counters);
-        } else if (accel == 1) {
+                wave_trace_grid<false><<<ggrid, kBlock, 0, stream>>>(sc, grids->cam, grids->lit, qin, nq + 1, fetch + 2 * g + 1, wb.res_t, wb.res_id, wb.qcap, g_min_t, g_drain_t, g_refill_t, fr.counters);
+            ++nl;
+        }
+        if (g == 0 && cam_grid) {
+            // every primary ray is a class A task: no class B launch in this generation
+        } else if (accel_b == 2) {
+            if (count)
+                wave_trace_bvh<true><<<pgrid, kBlock, 0, stream>>>(sc, qin, nq, fetch + 2 * g, wb.res_t, wb.res_id, min_t, drain_t, refill_t, fr.counters);
+            else
+                wave_trace_bvh<false><<<pgrid, kBlock, 0, stream>>>(sc, qin, nq, fetch + 2 * g, wb.res_t, wb.res_id, min_t, drain_t, refill_t, fr.counters);
+            ++nl;
+        } else if (accel_b == 1) {
             // 4 rays per thread x 4 objects per iteration, 2 blocks per SM, 2048-object tiles: the fastest of the
             // configurations swept on the B200 (tools/build_filter_variants.sh; history in DESIGN.md)
-            const cudaError_t fe = launch_filter<RT_FILTER_RPT, RT_FILTER_OPI, RT_FILTER_MINB, RT_FILTER_TILE>(sc, qin, qcount + g, wb.res_t, wb.res_id,
+            const cudaError_t fe = launch_filter<RT_FILTER_RPT, RT_FILTER_OPI, RT_FILTER_MINB, RT_FILTER_TILE>(sc, qin, nq, wb.res_t, wb.res_id,
                                                                                                           fr.counters, count, sm_count, stream);
             if (fe != cudaSuccess) return fe;
-            ++nl;
+            nl += 2;
         } else {
             if (count)
-                wave_trace_brute<true><<<sgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, wb.res_t, wb.res_id, fr.counters);
+                wave_trace_brute<true><<<sgrid, kBlock, 0, stream>>>(sc, qin, nq, wb.res_t, wb.res_id, fr.counters);
             else
-                wave_trace_brute<false><<<sgrid, kBlock, 0, stream>>>(sc, qin, qcount + g, wb.res_t, wb.res_id, fr.counters);
+                wave_trace_brute<false><<<sgrid, kBlock, 0, stream>>>(sc, qin, nq, wb.res_t, wb.res_id, fr.counters);
+            ++nl;
         }
         if (count)
-            wave_advance<true><<<agrid, kBlock, 0, stream>>>(sc, wp, wb.pa, qin, qout, qcount + g, qcount + g + 1, wb.res_t, wb.res_id,
+            wave_advance<true><<<agrid, kBlock, 0, stream>>>(sc, wp, wb.pa, qin, qout, nq, nq + 2, wb.res_t, wb.res_id,
                                                              g == 0 ? 1 : 0, fr.out, fr.hit_id, fr.hit_t, fr.counters);
         else
-            wave_advance<false><<<agrid, kBlock, 0, stream>>>(sc, wp, wb.pa, qin, qout, qcount + g, qcount + g + 1, wb.res_t, wb.res_id,
+            wave_advance<false><<<agrid, kBlock, 0, stream>>>(sc, wp, wb.pa, qin, qout, nq, nq + 2, wb.res_t, wb.res_id,
                                                               g == 0 ? 1 : 0, fr.out, fr.hit_id, fr.hit_t, fr.counters);
-        nl += 2;
+        ++nl;
     }
     if (launches) *launches = nl;
     return cudaGetLastError();

@@ -2,6 +2,7 @@
 #pragma once
 
 #include "rt_kernels.cuh"
+#include "rt_pgrid.cuh"
 #include "rt_wave.cuh"
 
 namespace rt {
@@ -11,17 +12,24 @@ struct WaveBuffers {
     TaskQueue q[2];     // capacity tasks each
     float* res_t;       // capacity
     int32_t* res_id;    // capacity
-    uint32_t* counts;   // 2 * n_counts words: queue sizes per generation, then fetch cursors per generation
+    uint32_t* counts;   // 4 * n_counts words: queue sizes (class B, class A) per generation, then the fetch cursors likewise
     uint32_t n_counts;
     uint64_t capacity;
+    uint32_t qcap;      // entries of one task queue of this launch sequence (class A tasks are stored from the back)
+};
+
+// The perspective grids of the camera and of the lights (rt_pgrid.cuh); valid_mask == 0: none.
+struct WaveGrids {
+    GridSet cam, lit;
 };
 
 // Upper bound on the number of trace/advance generations of one frame.
 uint32_t wave_max_generations(uint32_t max_bounces, uint32_t n_lights, int mode);
 
 // Enqueue every kernel of one frame on `stream` (no host synchronisation inside).
-// accel: 0 exact brute force, 1 filter (N-body tiles), 2 BVH.  *launches receives the number of kernels enqueued.
-cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb, int accel, uint32_t leaf_max, int sm_count,
+// accel: 0 exact brute force, 1 filter (N-body tiles), 2 BVH, 3 perspective grids for camera rays and point-light shadow rays
+// (grids != nullptr) + BVH for everything else.  *launches receives the number of kernels enqueued.
+cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb, int accel, const WaveGrids* grids, int sm_count,
                         uint32_t* launches, cudaStream_t stream);
 
 }  // namespace rt

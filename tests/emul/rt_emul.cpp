@@ -10,7 +10,10 @@
 #include <vector>
 #include <atomic>
 
+#include <algorithm>
+
 #include "../../opencl-raytracer_b200/csrc/rt_pixel.cuh"
+#include "../../opencl-raytracer_b200/csrc/rt_pgrid.cuh"
 #include "../../opencl-raytracer_b200/csrc/rt_wave.cuh"
 #include "../../opencl-raytracer_b200/csrc/rt_scene.hpp"
 
@@ -39,6 +42,86 @@ void bind(const rt::HostScene& hs, rt::Scene& s) {
     s.root = hs.root;
     s.root_f = hs.f_global;
     s.filter_h = hs.h_min;
+}
+
+// Host stand-in for the device builder of the perspective grids (rt_pgrid.cu): the same per-object functions
+// (pgrid_object_sphere, pgrid_rect), plain loops instead of count / scan / fill kernels.
+struct HostGrids {
+    std::vector<rt::PGrid> grids;
+    std::vector<uint32_t> cell_start;
+    std::vector<rt::GridEntry> entries;
+    rt::GridSet set{};
+    void build(const rt::HostScene& hs, uint32_t valid_mask) {
+        uint32_t cells = 0;
+        for (auto& g : grids) {
+            g.cell_base = cells;
+            cells += g.nu * g.nv;
+        }
+        std::vector<std::vector<rt::GridEntry>> lists(cells);
+        for (const auto& g : grids) {
+            if (!g.nu) continue;
+            for (uint32_t o = 0; o < hs.n_objs; ++o) {
+                float r, dnear;
+                if (!rt::pgrid_object_sphere(g, hs.cull[o], hs.omax, r, dnear)) continue;
+                int u0, u1, v0, v1;
+                if (!rt::pgrid_rect(g, hs.cull[o].cx, hs.cull[o].cy, hs.cull[o].cz, r, u0, u1, v0, v1)) continue;
+                for (int v = v0; v <= v1; ++v)
+                    for (int u = u0; u <= u1; ++u) lists[g.cell_base + (uint32_t)v * g.nu + (uint32_t)u].push_back(rt::GridEntry{o, dnear});
+            }
+        }
+        cell_start.assign(cells + 1, 0);
+        for (uint32_t c = 0; c < cells; ++c) {
+            std::sort(lists[c].begin(), lists[c].end(),
+                      [](const rt::GridEntry& a, const rt::GridEntry& b) { return a.dnear < b.dnear || (a.dnear == b.dnear && a.obj < b.obj); });
+            cell_start[c + 1] = cell_start[c] + (uint32_t)lists[c].size();
+            entries.insert(entries.end(), lists[c].begin(), lists[c].end());
+        }
+        set.grids = grids.data();
+        set.cell_start = cell_start.data();
+        set.entries = entries.data();
+        set.n_grids = (uint32_t)grids.size();
+        set.valid_mask = valid_mask;
+    }
+};
+
+void camera_grid(HostGrids& hg, const rt::HostScene& hs, uint32_t W, uint32_t H, float zdir, uint32_t tw, uint32_t th) {
+    rt::PGrid g;
+    memset(&g, 0, sizeof g);
+    const float f = -zdir;
+    g.axis = 2u | 4u;
+    g.u0 = -((float)W / 2.0f) / f;
+    g.v0 = -((float)H / 2.0f) / f;
+    g.inv_du = f / (float)tw;
+    g.inv_dv = f / (float)th;
+    g.nu = (W + tw - 1) / tw;
+    g.nv = H / th + 1;
+    g.kind = 0;
+    hg.grids.assign(1, g);
+    hg.build(hs, 1u);
+}
+
+void light_grids(HostGrids& hg, const rt::HostScene& hs, const rt_light* lights, uint32_t n_lights, uint32_t res) {
+    const uint32_t L = n_lights < RT_GRID_MAX_LIGHTS ? n_lights : RT_GRID_MAX_LIGHTS;
+    hg.grids.resize(6 * (size_t)L);
+    uint32_t valid = 0;
+    for (uint32_t li = 0; li < L; ++li) {
+        const bool ok = lights[li].position[3] != 0.f;
+        for (uint32_t face = 0; face < 6; ++face) {
+            rt::PGrid& g = hg.grids[6 * li + face];
+            memset(&g, 0, sizeof g);
+            if (!ok) continue;
+            g.ax = lights[li].position[0];
+            g.ay = lights[li].position[1];
+            g.az = lights[li].position[2];
+            g.axis = (face % 3u) | (face >= 3u ? 4u : 0u);
+            g.u0 = g.v0 = -1.f;
+            g.inv_du = g.inv_dv = (float)res / 2.f;
+            g.nu = g.nv = res;
+            g.kind = 1;
+        }
+        if (ok) valid |= 1u << li;
+    }
+    hg.build(hs, valid);
 }
 
 template <int ACCEL>
@@ -115,7 +198,8 @@ int emul_render(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
 // path state and compaction as in rt_wavefront.cu, the trace step done per ray with the functions above.
 int emul_render_wave(const rt_object* objs, uint32_t n_objs, const rt_light* lights, uint32_t n_lights, const rt_ray* rays,
                      uint64_t n_rays, uint32_t max_bounces, int mode, int accel, int leaf, float omax_user, float* out_rgba,
-                     uint64_t* counters_out, uint32_t* generations_out) {
+                     uint64_t* counters_out, uint32_t* generations_out, uint32_t cam_w, uint32_t cam_h, float cam_zdir, uint32_t grid_res,
+                     uint32_t tile_w, uint32_t tile_h) {
     rt::HostScene hs;
     const int rc = rt::build_scene(objs, n_objs, lights, n_lights, omax_user, leaf, hs, g_err);
     if (rc != RT_OK) return rc;
@@ -137,7 +221,14 @@ int emul_render_wave(const rt_object* objs, uint32_t n_objs, const rt_light* lig
         outi[i] = (uint32_t)i;
         reinterpret_cast<float4*>(out_rgba)[i] = make_float4(-1.f, -1.f, -1.f, -1.f);
     }
-    rt::WaveParams wp{max_bounces, mode};
+    // accel 3: perspective grids for the camera rays (the rays must then be the cam_w x cam_h pinhole frame) and for the
+    // shadow rays of point lights, the BVH for everything else -- as wave_render does (rt_wavefront.cu)
+    HostGrids cam, lit;
+    if (accel == 3) {
+        if (cam_w && n_objs) camera_grid(cam, hs, cam_w, cam_h, cam_zdir, tile_w, tile_h);
+        if (n_objs) light_grids(lit, hs, lights, n_lights, grid_res);
+    }
+    rt::WaveParams wp{max_bounces, mode, lit.set.valid_mask, (uint32_t)n};
     rt::LocalCounters lc;
     size_t cnt = n;
     uint32_t g = 0;
@@ -151,17 +242,26 @@ int emul_render_wave(const rt_object* objs, uint32_t n_objs, const rt_light* lig
             unsigned long long ne = 0, nn = 0;
             if (accel == 0) h = rt::trace_brute(sc, ray, &ne);
             else if (accel == 1) h = rt::trace_cull(sc, ray, &ne);
-            else if (pb & RT_TASK_ANYHIT) h = rt::trace_bvh<true>(sc, ray, 1.f, &ne, &nn);
+            else if (accel == 3 && g == 0 && (cam.set.valid_mask & 1u)) {
+                unsigned long long np = 0;
+                h = rt::trace_grid<false>(sc, cam.set, 0, ray, &np, &ne);
+                lc.pair_tests += np;
+            } else if (accel == 3 && (pb & RT_TASK_ANYHIT) && ((pb >> RT_TASK_LIGHT_SHIFT) & 15u) != RT_TASK_NO_GRID) {
+                unsigned long long np = 0;
+                h = rt::trace_grid<true>(sc, lit.set, 6u * ((pb >> RT_TASK_LIGHT_SHIFT) & 15u), ray, &np, &ne);
+                lc.pair_tests += np;
+            } else if (pb & RT_TASK_ANYHIT) h = rt::trace_bvh<true>(sc, ray, 1.f, &ne, &nn);
             else h = rt::trace_bvh<false>(sc, ray, RT_MAX_FLOAT, &ne, &nn);
             lc.exact_tests += ne;
             lc.node_visits += nn;
             rt::StepOut o;
-            const uint32_t p = pb & ~RT_TASK_ANYHIT;
+            const uint32_t p = pb & RT_TASK_PATH_MASK;
             rt::wave::step<true>(sc, wp, pa, p, g == 0, ray, h, o, lc);
             if (o.emit) {
                 qs[b][nout] = o.ray.s;
                 qd[b][nout] = o.ray.d;
-                qp[b][nout] = p | (o.anyhit ? RT_TASK_ANYHIT : 0u);
+                const bool to_a = o.anyhit && o.light < RT_TASK_NO_GRID && ((wp.grid_lights >> o.light) & 1u);
+                qp[b][nout] = p | ((to_a ? o.light : RT_TASK_NO_GRID) << RT_TASK_LIGHT_SHIFT) | (o.anyhit ? RT_TASK_ANYHIT : 0u);
                 ++nout;
             }
             if (o.write) reinterpret_cast<float4*>(out_rgba)[outi[p]] = o.px;

@@ -63,7 +63,7 @@ def test_wavefront_pipeline_equals_megakernel_and_oracle(rt, ctx, oracle_mod, na
         ctx.set_option(rt.OPT_PIPELINE, 0)
         mega = ctx.render(mb, mode, 2).copy()
         sm = ctx.stats().as_dict()
-        for accel in (1, 2):
+        for accel in (1, 2, 3):
             ctx.set_option(rt.OPT_PIPELINE, 1)
             out = ctx.render(mb, mode, accel)
             s = ctx.stats()
