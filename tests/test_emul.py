@@ -205,3 +205,89 @@ def test_triangle_extension_geometry(oracle_mod):
     for accel in (0, 1, 2):
         out, eid, et, _ = emul.render(objs, lights, rays, 2, 2, accel, 1, leaf=1)
         assert np.array_equal(eid, hid) and np.array_equal(et, ht) and np.array_equal(out, ref)
+
+
+# ------------------------------------------------------------------ perspective grids (rt_pgrid.cuh), host emulation
+@pytest.mark.parametrize("second_type", [T.BOX, T.SPHERE, T.TRIANGLE])
+def test_perspective_grids_bit_exact_synthetic(oracle_mod, second_type):
+    """accel 3: camera rays and point-light shadow rays look up one cell of a perspective grid around their apex
+    (host-built here with the same per-object functions the device builder uses), the rest walks the BVH."""
+    objs, lights = S.synthetic_scene(3000, 300, second_type=second_type, n_lights=3)
+    W, H = 96, 54
+    z, rays = frame_rays(W, H)
+    for mode in (1, 2):
+        ref, _, _, st = oracle_mod.port_render(mode, 4, objs, lights, rays)
+        for res, tile in ((16, (8, 4)), (64, (8, 4)), (200, (3, 5))):
+            out, c, _ = emul.render_wave(objs, lights, rays, 4, mode, 3, camera=(W, H, z), grid_res=res, tile=tile)
+            assert np.array_equal(out, ref)
+            assert (c["ref_primary"], c["ref_shadow"], c["ref_reflect"]) == (st.rays_primary, st.rays_shadow, st.rays_reflect)
+            assert c["pair_tests"] > 0
+    # arbitrary rays: no camera grid, the shadow rays still use the light grids
+    rr = random_rays(3000, 9)
+    ref, *_ = oracle_mod.port_render(2, 4, objs, lights, rr)
+    out, c, _ = emul.render_wave(objs, lights, rr, 4, 2, 3, camera=None, grid_res=64)
+    assert np.array_equal(out, ref)
+
+
+@pytest.mark.parametrize("name", list(S.REFERENCE_SCENES) + ["simpleScene3L", "kat2"])
+def test_perspective_grids_reference_scenes(oracle_mod, name):
+    """Large objects close to the apex (a light next to a unit cube, the camera inside nothing but looking at objects that
+    fill the frame): rectangles that cover whole faces, objects partly behind the apex plane."""
+    objs, lights = _scene(name)
+    W, H = 128, 72
+    z, rays = frame_rays(W, H)
+    for mode in (1, 2):
+        ref, *_ = oracle_mod.port_render(mode, 30, objs, lights, rays)
+        out, c, _ = emul.render_wave(objs, lights, rays, 30, mode, 3, camera=(W, H, z), grid_res=32)
+        assert np.array_equal(out, ref)
+
+
+def test_perspective_grids_light_inside_objects_and_directional(oracle_mod):
+    """A light buried in objects (its grids list them in every cell), a light at infinity (position.w == 0: no grids, its
+    shadow rays use the BVH), a light exactly on the camera apex."""
+    objs, lights = S.synthetic_scene(1500, 200, n_lights=4)
+    lights = lights.copy()
+    lights[0]["position"] = (0.3, -0.2, -60.0, 1.0)   # in the middle of the object cloud
+    lights[1]["position"] = (0.2, 0.9, 0.4, 0.0)      # directional
+    lights[2]["position"] = (0.0, 0.0, 0.0, 1.0)      # at the camera
+    W, H = 80, 45
+    z, rays = frame_rays(W, H)
+    for mode in (1, 2):
+        ref, *_ = oracle_mod.port_render(mode, 3, objs, lights, rays)
+        out, c, _ = emul.render_wave(objs, lights, rays, 3, mode, 3, camera=(W, H, z), grid_res=48)
+        assert np.array_equal(out, ref)
+
+
+def test_perspective_grids_never_drop_a_noisy_hit(oracle_mod):
+    """The adversarial scene of test_filters_never_drop_a_noisy_hit seen through the grids: tiny anisotropic spheres whose
+    silhouette the reference's cancelling discriminant blurs, a camera 150 units away and lights at the far side."""
+    rng = np.random.Generator(np.random.PCG64(17))
+    n = 300
+    objs, lights = S.synthetic_scene(n, 0, seed=11, second_type=T.SPHERE, n_lights=2)
+    mv = objs["mv"].reshape(n, 4, 4).copy()
+    mi = objs["mvInverse"].reshape(n, 4, 4).copy()
+    mv[:, :3, :] *= np.float32(1 / 16.0)
+    mi[:, :, :3] *= np.float32(16.0)
+    objs["mv"], objs["mvInverse"] = mv.reshape(n, 16), mi.reshape(n, 16)
+    objs["mat"]["absorption"] = 0.5
+    centre = mv[:, 3, :3]
+    # a pinhole frame whose pixels are aimed at the (jittered) projections of the objects: dense sampling of the silhouettes
+    W, H = 4096, 2304
+    z = T.camera_zdir(H)
+    px = np.clip(np.round(centre[:, 0] / -centre[:, 2] * -z + W / 2), 2, W - 3).astype(np.int64)
+    py = np.clip(np.round(H / 2 - centre[:, 1] / -centre[:, 2] * -z), 2, H - 3).astype(np.int64)
+    rows = np.unique(np.concatenate([py - 1, py, py + 1]))
+    rays = T.camera_rays(W, H, z, rows=rows).reshape(len(rows), W)
+    pick = []
+    row_of = {int(r): i for i, r in enumerate(rows)}
+    for x, y in zip(px, py):
+        for dy in (-1, 0, 1):
+            for dx in (-2, -1, 0, 1, 2):
+                pick.append((row_of[int(y + dy)], int(x + dx)))
+    pick = np.array(sorted(set(pick)))
+    sub = rays[pick[:, 0], pick[:, 1]].copy()
+    ref, hid, ht, _ = oracle_mod.port_render(2, 2, objs, lights, sub)
+    assert (hid >= 0).sum() > 200
+    # the grid lookup only needs the camera's (W, H, zdir): the rays are a subset of that frame
+    out, c, _ = emul.render_wave(objs, lights, sub, 2, 2, 3, camera=(W, H, z), grid_res=256)
+    assert np.array_equal(out, ref)

@@ -422,3 +422,158 @@ def test_errors_are_reported_not_hidden(rt, ctx):
     ctx.set_camera(16, 16, -10.0)
     with pytest.raises(rt.RtError):
         ctx.render(4, 9, 1)  # bad mode
+
+
+# ------------------------------------------------------------------ round 2: the benchmarked configuration, edge cases on the GPU
+def _lattice(W, H, n_side, seed):
+    """A seeded, frame-covering pixel subset: an n_side x n_side jittered lattice of distinct pixels."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    jj = np.minimum((np.arange(n_side) * H // n_side + rng.integers(0, max(H // n_side, 1), n_side)), H - 1)
+    ii = np.minimum((np.arange(n_side) * W // n_side + rng.integers(0, max(W // n_side, 1), n_side)), W - 1)
+    return jj.astype(np.int64), ii.astype(np.int64)
+
+
+def _headline_against_oracle(rt, oracle_mod, n_side):
+    objs, lights = S.synthetic_scene()  # cfg5-box: 100 000 boxes + 4 096 spheres, 2 lights
+    W, H, mb = 7680, 4320, 4
+    z = T.camera_zdir(H)
+    jj, ii = _lattice(W, H, n_side, 0xC0FFEE)
+    rays = T.camera_rays(W, H, z, rows=jj).reshape(len(jj), W)[:, ii].reshape(-1).copy()
+    idx = (jj[:, None] * W + ii[None, :]).reshape(-1)
+    ref, hid, ht, st = oracle_mod.port_render(2, mb, objs, lights, rays, nthreads=os.cpu_count() or 1)
+    with rt.Context(0) as c:  # exactly as bench.py drives it: camera, depth 4, everything else on auto
+        c.upload_scene(objs, lights)
+        c.set_camera(W, H, z)
+        frame = c.render(mb, 2, -1)
+        s = c.stats()
+        assert s.pipeline_used == 1 and s.accel_used == rt.ACCEL_GRID
+        gid, gt = c.render_aov(-1)
+        assert np.array_equal(gid[idx], hid) and np.array_equal(gt[idx], ht)  # hit ids and t: bit-exact
+        assert_colours_close(frame[idx], ref)                                 # colours 1e-4, PPM <= 1 LSB
+        assert np.array_equal(frame[idx][hid < 0], ref[hid < 0])              # missed pixels exactly (0,0,0,1)
+        # the same pixels as caller-supplied rays (the drop-in ctor's path): same bits, and the ray counts by class
+        c.set_option(rt.OPT_COUNT_RAYS, 1)
+        c.set_rays(rays)
+        sub = c.render(mb, 2, -1)
+        s = c.stats()
+        assert np.array_equal(sub, frame[idx])
+        assert (s.rays_primary, s.rays_shadow, s.rays_reflect, s.hit_pixels) == (st.rays_primary, st.rays_shadow, st.rays_reflect, st.hit_pixels)
+    return len(idx)
+
+
+def test_headline_config_against_oracle(rt, oracle_mod):
+    """The benchmarked configuration itself -- cfg5-box, set_camera(7680, 4320), depth 4, auto accel / pipeline / bands /
+    lanes -- against the oracle on a seeded 64 x 64 pixel subset."""
+    assert _headline_against_oracle(rt, oracle_mod, 64) == 4096
+
+
+@pytest.mark.skipif(not os.environ.get("RT_SLOW"), reason="65 536-pixel subset: minutes of CPU brute force (RT_SLOW=1)")
+def test_headline_config_against_oracle_65536(rt, oracle_mod):
+    assert _headline_against_oracle(rt, oracle_mod, 256) == 65536
+
+
+def test_headline_frame_all_searches_agree_at_full_resolution(rt, ctx):
+    """7680 x 4320, cfg5-box: perspective grids + BVH == BVH == bounding-sphere filter on the WHOLE frame (ids, t, colours),
+    and exact brute force on 64 rows."""
+    objs, lights = S.synthetic_scene()
+    W, H = 7680, 4320
+    z = T.camera_zdir(H)
+    ctx.upload_scene(objs, lights)
+    ctx.set_camera(W, H, z)
+    a = ctx.render(4, 2, 3).copy()
+    ida, ta = ctx.render_aov(3)
+    b = ctx.render(4, 2, 2)
+    assert np.array_equal(a, b)
+    del b
+    idb, tb = ctx.render_aov(2)
+    assert np.array_equal(ida, idb) and np.array_equal(ta, tb)
+    b = ctx.render(4, 2, 1)
+    assert np.array_equal(a, b)
+    del b
+    idb, tb = ctx.render_aov(1)
+    assert np.array_equal(ida, idb) and np.array_equal(ta, tb)
+    rows = np.arange(64) * (H // 64) + 11
+    rays = T.camera_rays(W, H, z, rows=rows)
+    idc, tc = ctx.trace(rays, 0)
+    sel = (rows[:, None] * W + np.arange(W)[None, :]).reshape(-1)
+    assert np.array_equal(idc, ida[sel]) and np.array_equal(tc, ta[sel])
+
+
+@pytest.mark.parametrize("pipeline", [0, 1])
+def test_tie_rules_coincident_objects_gpu(rt, ctx, oracle_mod, pipeline):
+    """Exact ties on the GPU's own merge code (filter_flush's owner merge, the BVH kernel's deferred candidates, the grid
+    kernel's list walk): duplicated spheres -- highest index wins (SAR:108) -- and duplicated boxes -- lowest index wins
+    (SAR:147) -- plus a cloud of coincident pairs large enough for full 32-wide exact batches."""
+    base, lights = S.kat2_scene()
+    small = np.concatenate([base[[0]], base[[1]], base[[0]], base[[1]], base[[2]], base[[2]]])
+    cloud, lights2 = S.synthetic_scene(600, 200, n_lights=2)
+    cloud = np.concatenate([cloud, cloud[::-1], cloud[::3]])  # every object two or three times, in shuffled index order
+    for objs, lts, (W, H) in ((small, lights, (160, 90)), (cloud, lights2, (192, 108))):
+        z, rays = frame_rays(W, H)
+        ref, hid, ht, st = oracle_mod.port_render(2, 4, objs, lts, rays)
+        ctx.set_option(rt.OPT_PIPELINE, pipeline)
+        ctx.set_option(rt.OPT_COUNT_RAYS, 1)
+        ctx.upload_scene(objs, lts)
+        ctx.set_camera(W, H, z)
+        for accel in (0, 1, 2, 3):
+            out = ctx.render(4, 2, accel)
+            assert ctx.stats().pipeline_used == pipeline
+            assert_colours_close(out, ref)
+            gid, gt = ctx.render_aov(accel)
+            assert np.array_equal(gid, hid) and np.array_equal(gt, ht)
+    assert set(np.unique(hid)) != {-1}
+
+
+@pytest.mark.parametrize("pipeline", [0, 1])
+def test_degenerate_rays_gpu(rt, ctx, oracle_mod, pipeline):
+    """Axis-parallel rays (a direction component exactly 0: the copysign branch of the slab test, SAR:36-43), origins
+    inside a box / a sphere, an object of unknown type -- through both pipelines and every search."""
+    objs, lights = S.kat2_scene()
+    r = np.zeros(7, dtype=T.RAY_DTYPE)
+    r["start"][:, 3] = 1.0
+    r["start"][:, :3] = [(0, 0, 0), (0, 0, 0), (1, 1, 0), (0, 0, -10), (3, 2, -7), (5, 0, -10), (0, 5, -10)]
+    r["direction"][:, :3] = [(0, 0, -1), (0, 0, 1), (0, 0, -3), (0, 1, 0), (1, 0, 0), (-1, 0, 0), (0, -2, 0)]
+    r = np.concatenate([r] * 40)  # more than one warp, ragged
+    weird = np.concatenate([objs, objs[[1]]])
+    weird[3]["type"] = 7
+    hid, ht = oracle_mod.port_trace(weird, r)
+    ref, *_ = oracle_mod.port_render(2, 3, weird, lights, r)
+    assert (hid >= 0).sum() >= 5 * 40 and not (hid == 3).any()
+    ctx.set_option(rt.OPT_PIPELINE, pipeline)
+    ctx.upload_scene(weird, lights)
+    ctx.set_rays(r)
+    for accel in (0, 1, 2, 3):
+        gid, gt = ctx.render_aov(accel)
+        assert np.array_equal(gid, hid) and np.array_equal(gt, ht)
+        assert_colours_close(ctx.render(3, 2, accel), ref)
+        tid, tt = ctx.trace(r, accel)
+        assert np.array_equal(tid, hid) and np.array_equal(tt, ht)
+
+
+def test_perspective_grids_lights_everywhere(rt, ctx, oracle_mod):
+    """Grids around a light buried in the object cloud, a light on the camera apex, a directional light (no grids: BVH),
+    more lights than light codes (lights 15.. keep the BVH), several grid resolutions; SHADE and SAR modes."""
+    objs, lights = S.synthetic_scene(4000, 400, n_lights=4)
+    lights = lights.copy()
+    lights[0]["position"] = (0.3, -0.2, -60.0, 1.0)
+    lights[1]["position"] = (0.2, 0.9, 0.4, 0.0)
+    lights[2]["position"] = (0.0, 0.0, 0.0, 1.0)
+    many = np.concatenate([lights] * 5)[:18]
+    W, H = 160, 90
+    z, rays = frame_rays(W, H)
+    ctx.set_option(rt.OPT_PIPELINE, 1)
+    ctx.set_option(rt.OPT_COUNT_RAYS, 1)
+    for lts, mb in ((lights, 3), (many, 1)):
+        for mode in (1, 2):
+            ref, hid, ht, st = oracle_mod.port_render(mode, mb, objs, lts, rays)
+            for res in (32, 512, 1024):
+                ctx.set_option(rt.OPT_GRID_RES, res)
+                ctx.upload_scene(objs, lts)
+                ctx.set_camera(W, H, z)
+                out = ctx.render(mb, mode, 3)
+                s = ctx.stats()
+                assert s.accel_used == rt.ACCEL_GRID and s.pair_tests > 0
+                assert_colours_close(out, ref)
+                assert (s.rays_primary, s.rays_shadow, s.rays_reflect) == (st.rays_primary, st.rays_shadow, st.rays_reflect)
+                if lts is many:
+                    break
