@@ -40,7 +40,8 @@ METRIC = "Mrays/s (primary+shadow+reflect)"
 # flops of the arithmetic each counted unit executes (DESIGN.md "Work per unit")
 FLOPS_FILTER = 14.0   # bounding-sphere filter, expanded form: 7 fma per (ray, object) pair = 3.5 FFMA2 (rt_wavefront.cu)
 FLOPS_EXACT = 78.0    # reference arithmetic of one ray x object test as written
-FLOPS_NODE = 62.0     # two inflated slab tests of one BVH node
+FLOPS_NODE = 52.0     # two inflated slab tests of one BVH node: 10 FADD + 6 FMUL + 18 FFMA in the SASS of wave_trace_bvh
+                      # (profiles/r2_sass_wave_trace_bvh_node_step.txt); the 7 min/max and 4 compares are not counted
 FLOPS_SHADE = 100.0   # Phong terms per (hit, light)
 FLOPS_ALGO_PAIR = 54.5  # minimal affine ray x object test
 
@@ -135,23 +136,28 @@ def ncu_traffic(name):
                 tot += float(f[1]) * unit[f[2]]
                 seen += 1
                 if seen == 2:
-                    return tot, "profiles/%s: first wave_trace_bvh launch of the frame (primary rays, the longest of the trace launches)" % name
+                    return tot, "profiles/%s: first wave_trace_bvh launch captured there (the longest trace launch of the frame)" % name
     except Exception:
         pass
     return None, None
 
 
-def sample_rays(width, height, zdir, n_side=64):
-    """A bounded, frame-covering pixel sample: an n_side x n_side lattice of pixels of the full frame."""
+def sample_rays(width, height, zdir, n_side=64, with_index=False):
+    """A bounded, frame-covering pixel sample: an n_side x n_side lattice of pixels of the full frame
+    (with_index: also their indices jj * width + ii in the frame)."""
     jj = np.linspace(0, height - 1, n_side).astype(np.int64)
     ii = np.linspace(0, width - 1, n_side).astype(np.int64)
     rows = types.camera_rays(width, height, zdir, rows=jj)
-    return rows.reshape(len(jj), width)[:, ii].reshape(-1).copy()
+    rays = rows.reshape(len(jj), width)[:, ii].reshape(-1).copy()
+    if with_index:
+        return rays, (jj[:, None] * width + ii[None, :]).reshape(-1)
+    return rays
 
 
-def cpu_arm(objs, lights, rays, max_bounces, mode, steps, warmup, n_ref_rays=None):
+def cpu_arm(objs, lights, rays, max_bounces, mode, steps, warmup, n_ref_rays=None, strict=False):
     """The reference's CPU implementation of the path on the host cores: oracle/_ref when it was built,
-    else the C restatement.  Returns (Mrays/s, ms_per_step, kind, cores, ray_count)."""
+    else the C restatement.  strict: the contraction-free build (-O2 -ffp-contract=off, the parity target) instead
+    of the fastest one.  Returns (Mrays/s, ms_per_step, kind, cores, ray_count, build flags, pixels of the last step)."""
     import oracle
 
     cores = os.cpu_count() or 1
@@ -160,14 +166,15 @@ def cpu_arm(objs, lights, rays, max_bounces, mode, steps, warmup, n_ref_rays=Non
         n_ref_rays = st.rays_primary + st.rays_shadow + st.rays_reflect
     # the reference kernels skip every type but sphere / box: a scene with the triangle extension is timed on the C restatement
     use_ref = oracle.have_ref() and not bool((np.asarray(objs["type"]) > 1).any())
-    fast = use_ref and oracle.cpu_has_avx2_fma() and os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libsar_ref_fast.so"))
+    fast = (not strict) and use_ref and oracle.cpu_has_avx2_fma() and os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libsar_ref_fast.so"))
     kind = "reference" if use_ref else "port"
+    last = [None]
 
     def once():
         if use_ref:
-            oracle.ref_render(mode, max_bounces, objs, lights, rays, nthreads=cores, fast=fast)
+            last[0] = oracle.ref_render(mode, max_bounces, objs, lights, rays, nthreads=cores, fast=fast)
         else:
-            oracle.port_render(mode, max_bounces, objs, lights, rays, nthreads=cores)
+            last[0] = oracle.port_render(mode, max_bounces, objs, lights, rays, nthreads=cores)[0]
 
     for _ in range(warmup):
         once()
@@ -176,7 +183,7 @@ def cpu_arm(objs, lights, rays, max_bounces, mode, steps, warmup, n_ref_rays=Non
         once()
     dt = (time.perf_counter() - t0) / max(steps, 1)
     build = "-O3 -march=x86-64-v3" if fast else "-O2 -ffp-contract=off"
-    return n_ref_rays / dt / 1e6, dt * 1e3, kind, cores, n_ref_rays, build
+    return n_ref_rays / dt / 1e6, dt * 1e3, kind, cores, n_ref_rays, build, last[0]
 
 
 def main():
@@ -194,6 +201,8 @@ def main():
     ap.add_argument("--builder", type=int, default=0, help="BVH builder: 0 host SAH, 1 device LBVH")
     ap.add_argument("--bands", type=int, default=0, help="readback bands of rt_render (0 = library default)")
     ap.add_argument("--lanes", type=int, default=0, help="1: one launch sequence per frame, 2: two half-frames on two streams (0 = library default)")
+    ap.add_argument("--zero-copy", type=int, default=-1, help="rt_render stores into the pinned host frame directly: -1 library default, 0 off, 1 on")
+    ap.add_argument("--grid-res", type=int, default=0, help="cells per side of the light grids (0 = library default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-brute-leg", action="store_true")
     args = ap.parse_args()
@@ -214,7 +223,7 @@ def main():
             return
         side = args.cpu_sample or (48 if len(objs) > 10000 else 512)
         rays = sample_rays(W, H, zdir, side)
-        v, ms, kind, cores, nrays, build = cpu_arm(objs, lights, rays, max_bounces, mode, args.steps, args.warmup)
+        v, ms, kind, cores, nrays, build, _ = cpu_arm(objs, lights, rays, max_bounces, mode, args.steps, args.warmup)
         sample = "%dx%d pixel lattice of the frame (%d rays/step), %s, %d threads" % (side, side, nrays, build, cores)
         print(json.dumps({
             "impl": "reference", "metric": METRIC, "value": v, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
@@ -257,6 +266,10 @@ def main():
         ctx.set_option(lib.OPT_LANES, args.lanes)
     if args.builder:
         ctx.set_option(lib.OPT_BVH_BUILDER, args.builder)
+    if args.zero_copy >= 0:
+        ctx.set_option(lib.OPT_ZERO_COPY, args.zero_copy)
+    if args.grid_res:
+        ctx.set_option(lib.OPT_GRID_RES, args.grid_res)
     t_up0 = time.perf_counter()
     ctx.upload_scene(objs, lights)
     ctx.set_camera(W, H, zdir)
@@ -403,14 +416,21 @@ def main():
     else:
         flops = pair_tests * FLOPS_EXACT + shades * FLOPS_SHADE
     achieved_tf = flops / world / (ms_dev * 1e-3) / 1e12
-    traffic, traffic_src = (ncu_traffic("r1_g_wave_trace_bvh_cfg5_8k.txt") if accel_used == 2 and pipeline_used == 1 and args.workload == "cfg5-box"
-                            else (None, None))
+    # dram bytes of the dominant kernel's longest launch, from the committed ncu capture of this command (N = 1 only: a
+    # shard's launches move other bytes)
+    traffic, traffic_src = (None, None)
+    if world == 1 and pipeline_used == 1 and args.workload == "cfg5-box":
+        traffic, traffic_src = ncu_traffic({2: "r1_g_wave_trace_bvh_cfg5_8k.txt", 3: "r2_wave_trace_bvh_cfg5_8k.txt"}.get(accel_used, "none"))
     roofline = {
         "kernel": kernel_names[accel_used], "bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
         "frac": achieved_tf / peak_tf if peak_tf else None, "traffic": traffic, "traffic_source": traffic_src,
         "peak_source": "rt_measure_fp32_peak (register-only loops, this GPU, this run: scalar FFMA %.1f, packed FFMA2 %.1f TFLOP/s; "
                        "the larger is the peak and implies %.0f MHz)" % (peak_scalar, peak_packed, peak_mhz),
         "flops_per_launch": flops / world,
+        # SURVEY.md 8(d)'s algorithmic unit beside the executed flops: 54.5 flop per exact ray x object test + 100 per shade --
+        # what the path HAS to compute, which cannot be inflated by traversal or filter work
+        "algorithmic": {"flops_per_launch": (exact_tests * FLOPS_ALGO_PAIR + shades * FLOPS_SHADE) / world,
+                        "frac": (exact_tests * FLOPS_ALGO_PAIR + shades * FLOPS_SHADE) / world / (ms_dev * 1e-3) / 1e12 / peak_tf if peak_tf else None},
         "hbm": {"framebuffer_bytes_per_launch": pixels * 16 / world, "achieved_gbs": pixels * 16 / world / (ms_dev * 1e-3) / 1e9,
                 "peak_gbs": peaks.get("hbm_gbs")},
         "note": "BVH traversal is bound by divergent node fetches, not by FP32: ncu (profiles/r1_g_wave_trace_bvh_cfg5_8k.txt, "
@@ -447,11 +467,18 @@ def main():
                 "mrays_per_s": s2.rays_traced / (best * 1e-3) / 1e6,
             }
 
-    # ------------------------------------------------------------------ CPU baseline (rank 0, N = 1 only)
+    # ------------------------------------------------------------------ CPU baseline (rank 0, N = 1 only) + parity of THIS run
+    # The timed CPU leg is the reference's own kernel source in its contraction-free build -- the parity target -- so its
+    # pixels are not thrown away: they are compared with the same pixels of the frame the GPU just produced through
+    # rt_render (colours 1e-4 * max(1, |ref|), PPM <= 1 LSB), and the C restatement adds hit ids and t (bit-exact).  A
+    # mismatch fails the run: a fast frame that differs from the reference's is not a result.
     cpu = None
+    parity = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        import oracle
+
         side = args.cpu_sample or (40 if len(objs) > 10000 else 384)
-        rays = sample_rays(W, H, zdir, side)
+        rays, pix = sample_rays(W, H, zdir, side, with_index=True)
         with lib.Context(local_rank) as c3:  # reference ray count of the sample (GPU count == oracle count, tests)
             c3.upload_scene(objs, lights)
             c3.set_rays(rays)
@@ -459,9 +486,21 @@ def main():
             c3.set_option(lib.OPT_SKIP_DEAD_RAYS, 0)
             c3.render_device(max_bounces, mode, -1)
             nref = c3.stats().rays_reference
-        v, ms, kind, cores, nrays, build = cpu_arm(objs, lights, rays, max_bounces, mode, 1, 0, n_ref_rays=nref)
+        v, ms, kind, cores, nrays, build, ref_px = cpu_arm(objs, lights, rays, max_bounces, mode, 1, 0, n_ref_rays=nref, strict=True)
         cpu = {"value": v, "unit": "Mrays/s", "cores": cores, "kind": kind,
                "sample": "%dx%d pixel lattice of the frame, %d reference rays, %.1f s, %s" % (side, side, nrays, ms / 1e3, build)}
+        got = host.array[pix]
+        d = np.abs(got[:, :3].astype(np.float64) - ref_px[:, :3].astype(np.float64))
+        lim = 1e-4 * np.maximum(1.0, np.abs(ref_px[:, :3].astype(np.float64)))
+        ppm = int(np.abs(types.quantize_ppm(got).astype(np.int64) - types.quantize_ppm(ref_px).astype(np.int64)).max(initial=0))
+        _, hid, ht, _ = oracle.port_render(mode, max_bounces, objs, lights, rays, nthreads=cores)
+        gid, gt = ctx.render_aov(args.accel)
+        parity = {"pixels": int(len(pix)), "against": "oracle/_ref (%s) colours, oracle port hit ids / t" % build if kind == "reference" else "oracle port",
+                  "colours_ok": bool((d <= lim).all()), "max_abs": float(d.max(initial=0.0)),
+                  "max_rel": float((d / np.maximum(1.0, np.abs(ref_px[:, :3]))).max(initial=0.0)), "ppm_max_lsb": ppm,
+                  "ids_exact": bool(np.array_equal(gid[pix], hid)), "t_exact": bool(np.array_equal(gt[pix], ht)),
+                  "hit_pixels": int((hid >= 0).sum())}
+        del gid, gt
 
     # ------------------------------------------------------------------ the reference's own .cl on this GPU (rank 0, N = 1)
     ref_ocl = None
@@ -528,10 +567,15 @@ def main():
             out["roofline_brute"] = roofline_brute
         if cpu:
             out["cpu_baseline"] = cpu
+        if parity:
+            out["parity"] = parity
         if ref_ocl:
             out["reference_opencl_gpu"] = ref_ocl
         sys.stdout.flush()
         os.write(json_fd, (json.dumps(out) + "\n").encode())
+    if parity and not (parity["colours_ok"] and parity["ids_exact"] and parity["t_exact"] and parity["ppm_max_lsb"] <= 1):
+        sys.stderr.write("PARITY FAILED: %s\n" % json.dumps(parity))
+        sys.exit(3)
     if world > 1:
         if target:
             ctx.ipc_close(target)

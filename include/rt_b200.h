@@ -129,6 +129,9 @@ typedef enum rt_option {
                                   device (scenes that change every frame: ~1 ms instead of ~150 ms per 10^5 objects, a looser tree) */
     RT_OPT_LANES = 7,      /* 2 (default): camera launches of the wavefront pipeline run as two halves on two streams, each filling the
                               thin generation tails of the other; 1: one launch sequence */
+    RT_OPT_ZERO_COPY = 9,  /* rt_render into page-locked, device-addressable host memory (rt_host_alloc / rt_host_register / cudaHostAlloc):
+                              the kernels store finished pixels straight into the caller's frame instead of a framebuffer in HBM that is
+                              copied afterwards.  -1 (default): on the wavefront pipeline, 0: never, 1: on both pipelines */
     RT_OPT_GRID_RES = 8,   /* cells per side of each of the six perspective grids around a light (default 512, 32..4096) */
     RT_OPT_READBACK_BANDS = 5  /* rt_render of a large camera frame (or shard of one): bands of rows / row-blocks whose readback
                                   overlaps the next band's kernels, shrinking geometrically by the measured kernel : copy time

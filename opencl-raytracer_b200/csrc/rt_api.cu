@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -63,11 +64,12 @@ struct DevBuf {
 
 struct rt_ctx {
     int device = 0;
-    cudaStream_t stream = nullptr, copy_stream = nullptr, lane_stream = nullptr;
-    cudaEvent_t lane_go = nullptr, lane_done = nullptr;
+    cudaStream_t stream = nullptr, copy_stream = nullptr;
+    cudaEvent_t copy_done = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
     static const int kMaxBands = 16;
     cudaEvent_t band_done[kMaxBands] = {};
+    cudaStream_t seq_stream[kMaxBands] = {};  // one per concurrent launch sequence, descending priority
 
     // host copy of the AoS scene (kept so that the bounds can be rebuilt when the ray-origin bound grows)
     std::vector<rt_object> objs;
@@ -124,10 +126,8 @@ struct rt_ctx {
     int opt_grid_res = 512;
 
     // options
-    int opt_pipeline = -1, opt_count = 0, opt_leaf = 1, opt_skip_dead = 1, opt_bands = 0, opt_builder = 0, opt_lanes = 2;
-    // banded readback: kernel time : copy time of the same rows, measured on the previous banded frame
-    double band_ratio = 7.0;
-    cudaEvent_t copy_ev[2] = {};
+    int opt_zero_copy = 0;  // 0 (default) never, 1 whenever the target is mapped pinned memory, -1 on the wavefront pipeline only -- measured slower, see rt_render
+    int opt_pipeline = -1, opt_count = 0, opt_leaf = 1, opt_skip_dead = 1, opt_bands = 0, opt_builder = 0, opt_lanes = 0;
 
     rt_stats stats;
     float fp32_peak_tf[2] = {0.f, 0.f};  // last rt_measure_fp32_peak: scalar FFMA loop, packed FFMA2 loop
@@ -359,14 +359,12 @@ void plan_band(uint32_t units, int band, int n_bands, double ratio, uint32_t* u0
     *u1 = end;
 }
 uint32_t band_units(const rt_ctx* c) { return plan_units(c->height, c->block_rows, c->shard, c->n_shards); }
-void band_range(const rt_ctx* c, int band, int n_bands, uint32_t* u0, uint32_t* u1) {
-    plan_band(band_units(c), band, n_bands, c->band_ratio, u0, u1);
-}
+
 // Number of bands when the caller leaves it open: two.  One more band costs its ramp-up and thin last generations
 // again (0.8 ms of an 8K frame on one GPU, 1.4 ms at 8 GPUs) and hides less than that in every configuration measured
 // (1, 2, 4, 8 GPUs); a cost model on the measured copy time is not robust, because that time depends on how many ranks
 // copy at the same moment, i.e. on the decision itself.
-int auto_bands(const rt_ctx* c) { return c->opt_bands > 0 ? c->opt_bands : 2; }
+
 
 // Frame descriptor.  Camera frames are described by a range [u0, u1) of the context's units (band_units(): rows of the
 // whole frame, or owned row-blocks of a shard); u1 == 0 means "everything" (and is the only form for explicit rays).
@@ -444,10 +442,9 @@ int pick_pipeline(const rt_ctx* c, int accel, uint32_t max_bounces, int mode) {
     return (accel != RT_ACCEL_BRUTE && c->objs.size() > 48) ? 1 : 0;
 }
 
-// Wavefront buffers for `capacity` paths, handed out as two halves (lanes) that run on two streams; lane 0 alone may
-// use everything (wb[0].capacity == capacity).
-int ensure_wave_buffers(rt_ctx* c, uint64_t capacity, uint32_t gens, rt::WaveBuffers wb[2]) {
-    if (capacity > RT_TASK_PATH_MASK) return fail(RT_ERR_INVALID, "too many rays for one wavefront context (2^27 - 1 per GPU; shard the frame)");
+// Wavefront buffers for `capacity` paths in total, cut into one slice per concurrent launch sequence: sequence k owns the
+// entries [offset[k], offset[k] + cap[k]).
+int ensure_wave_buffers(rt_ctx* c, uint64_t capacity, uint32_t gens, int n_seq, const uint64_t* offset, const uint64_t* cap, rt::WaveBuffers* wb) {
     RT_CUDA(c->w_acc.ensure(capacity));
     RT_CUDA(c->w_refl.ensure(capacity));
     RT_CUDA(c->w_P.ensure(capacity));
@@ -461,11 +458,11 @@ int ensure_wave_buffers(rt_ctx* c, uint64_t capacity, uint32_t gens, rt::WaveBuf
     }
     RT_CUDA(c->w_res_t.ensure(capacity));
     RT_CUDA(c->w_res_id.ensure(capacity));
-    const size_t per_lane = 4 * (size_t)(gens + 2);
-    RT_CUDA(c->w_counts.ensure(2 * per_lane));
-    const uint64_t half = (capacity / 2) & ~(uint64_t)255;  // lane 1 starts here
-    for (int l = 0; l < 2; ++l) {
-        const uint64_t o = l ? half : 0;
+    const size_t per_seq = 4 * (size_t)(gens + 2);
+    RT_CUDA(c->w_counts.ensure((size_t)n_seq * per_seq));
+    for (int l = 0; l < n_seq; ++l) {
+        if (cap[l] > RT_TASK_PATH_MASK) return fail(RT_ERR_INVALID, "too many rays for one launch sequence (2^27 - 1): more lanes / shards needed");
+        const uint64_t o = offset[l];
         wb[l].pa.acc = c->w_acc.p + o;
         wb[l].pa.refl = c->w_refl.p + o;
         wb[l].pa.P = c->w_P.p + o;
@@ -479,21 +476,38 @@ int ensure_wave_buffers(rt_ctx* c, uint64_t capacity, uint32_t gens, rt::WaveBuf
         }
         wb[l].res_t = c->w_res_t.p + o;
         wb[l].res_id = c->w_res_id.p + o;
-        wb[l].counts = c->w_counts.p + l * per_lane;
-        wb[l].n_counts = (uint32_t)(per_lane / 4);
-        wb[l].capacity = l ? capacity - half : capacity;
-        wb[l].qcap = (uint32_t)wb[l].capacity;  // lane 0 of a two-lane launch is cut down to `half` by the caller
+        wb[l].counts = c->w_counts.p + l * per_seq;
+        wb[l].n_counts = (uint32_t)(per_seq / 4);
+        wb[l].capacity = cap[l];
+        wb[l].qcap = (uint32_t)cap[l];
     }
     return RT_OK;
 }
 
-// Kernels of one render, bracketed by ev0/ev1 on c->stream.  band >= 0: band `band` of n_bands of a banded render (ev0
-// stays at the start of band 0).  On the wavefront pipeline a camera launch is split into two halves (lanes) that run
-// on two streams with their own queues: every kernel of the pipeline is followed by the same kernel of the other lane,
-// whose blocks move in as the first one's persistent blocks retire -- the thin tail of every generation (and the
-// latency of the nearly empty last generations) is filled with the other lane's work.  RT_OPT_LANES = 1 turns it off.
+// How many launch sequences a camera render is cut into (wavefront pipeline).  The frame -- or this context's shard of it --
+// is split into bands of rows / owned row-blocks, and ALL bands are enqueued at once, each on its own stream, the streams in
+// descending priority: band 0's blocks are scheduled first, the blocks of the later bands move into every slot it leaves free
+// -- the thin tail of each of its generations, the latency-bound last generations -- and the bands finish roughly in order.
+// rt_render copies a band to the host as soon as it is done, under the kernels of the bands still running.  (Round 1 ran
+// the bands one after the other, two lanes each: every band paid the ~2 ms of its thin generations again.)  Measured on the
+// 8K cfg5 frame (profiles/r2_sweep_bands.txt): kernels alone 33.0 ms with 2 sequences, 33.6 with 1, 34.3 with 6; end to end
+// 42.3 (2: both finish together, the whole 9.4 ms copy is exposed) / 37.5 (4) / 36.9 (6) / 37.9 (8).  Stream priorities do
+// not order persistent kernels -- a resident low-priority CTA runs until its queue is empty -- and starting band k only
+// after the heavy generations of band k - 1 (an event chain) ordered the bands but cost more kernel time than it hid copy
+// (38.2 ms at 4 bands).  Hence: 6 bands when the frame goes to the host, 2 otherwise.
+int auto_sequences(const rt_ctx* c, bool to_host, bool aov_only) {
+    if (!c->use_camera || aov_only) return 1;
+    int n = to_host && c->opt_bands > 0 ? c->opt_bands : (c->opt_lanes > 0 ? c->opt_lanes : (to_host ? 6 : 2));
+    n = std::min(n, rt_ctx::kMaxBands);
+    const uint64_t px = local_pixels(c);
+    while (n > 1 && (px / n < (1ull << 19) || band_units(c) < (uint32_t)(4 * n))) --n;  // at least 0.5 Mpixel and 4 units per band
+    return std::max(n, 1);
+}
+
+// Kernels of one render, bracketed by ev0/ev1 on c->stream; host_out != nullptr: plus the device->host copy of every band
+// (copy stream), ev2 after the last one.  Nothing is synchronised here.
 int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float4* out, int* accel_used, bool aov_only = false,
-                     int band = -1, int n_bands = 1) {
+                     float* host_out = nullptr) {
     int rc = sync_scene(c);
     if (rc != RT_OK) return rc;
     accel = pick_accel(c, accel);
@@ -514,63 +528,74 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
     }
     if (c->opt_count) {
         RT_CUDA(c->d_counters.ensure(1));
-        if (band <= 0) RT_CUDA(cudaMemsetAsync(c->d_counters.p, 0, sizeof(rt::Counters), c->stream));
+        RT_CUDA(cudaMemsetAsync(c->d_counters.p, 0, sizeof(rt::Counters), c->stream));
     }
-    if (band <= 0) c->last_launches = 0;
+    c->last_launches = 0;
 
     if (pipeline == 1) {
         const uint32_t gens = rt::wave_max_generations(max_bounces, c->scene.n_lights, mode);
         if (gens > kMaxWaveGenerations) return fail(RT_ERR_INVALID, "max_bounces x lights too large for the wavefront pipeline; use RT_OPT_PIPELINE 0");
-        // unit range of this launch
-        uint32_t u0 = 0, u1 = 0;
-        if (c->use_camera) {
-            if (band >= 0)
-                band_range(c, band, n_bands, &u0, &u1);
+        const int n_seq = auto_sequences(c, host_out != nullptr, aov_only);
+        const uint32_t units = c->use_camera ? band_units(c) : 0u;
+        rt::Frame fr[rt_ctx::kMaxBands];
+        uint64_t offset[rt_ctx::kMaxBands], cap[rt_ctx::kMaxBands];
+        uint32_t ub[rt_ctx::kMaxBands + 1];
+        uint64_t total = 0;
+        for (int k = 0; k < n_seq; ++k) {
+            ub[k] = (uint32_t)((uint64_t)units * k / n_seq);
+            ub[k + 1] = (uint32_t)((uint64_t)units * (k + 1) / n_seq);
+            if (c->use_camera)
+                fill_frame_desc(c, fr[k], max_bounces, mode, out, ub[k], ub[k + 1]);
             else
-                u1 = band_units(c);
-            if (u1 == u0) {
-                if (band <= 0) {
-                    RT_CUDA(cudaEventRecord(c->ev0, c->stream));
-                    RT_CUDA(cudaEventRecord(c->ev1, c->stream));
-                }
-                return RT_OK;
+                fill_frame_desc(c, fr[k], max_bounces, mode, out);
+            if (c->use_camera && ub[k + 1] == ub[k]) fr[k].n_local = 0;
+            if (aov_only) {
+                fr[k].hit_id = c->d_hit_id.p;
+                fr[k].hit_t = c->d_hit_t.p;
             }
+            offset[k] = total;
+            cap[k] = (fr[k].n_local + 255u) & ~(uint64_t)255;
+            total += cap[k];
         }
-        const uint64_t unit_px = (uint64_t)c->width * (c->n_shards <= 1 ? 1u : c->block_rows);
-        rt::WaveBuffers wb[2];
-        // sized for the whole local frame (the band split moves from frame to frame), + slack for the lane split
-        rc = ensure_wave_buffers(c, c->use_camera ? local_pixels(c) + 2 * unit_px + 512 : c->n_rays, gens, wb);
+        rt::WaveBuffers wb[rt_ctx::kMaxBands];
+        rc = ensure_wave_buffers(c, std::max<uint64_t>(total, 256), gens, n_seq, offset, cap, wb);
         if (rc != RT_OK) return rc;
-        rt::Frame fr[2];
-        const bool lanes = c->use_camera && !aov_only && c->opt_lanes > 1 && u1 - u0 >= 8 && (uint64_t)(u1 - u0) * unit_px >= (1ull << 20);
-        const uint32_t um = lanes ? u0 + (u1 - u0 + 1) / 2 : u1;
-        fill_frame_desc(c, fr[0], max_bounces, mode, out, u0, um);
-        if (lanes) fill_frame_desc(c, fr[1], max_bounces, mode, out, um, u1);
-        if (aov_only) {
-            fr[0].hit_id = c->d_hit_id.p;
-            fr[0].hit_t = c->d_hit_t.p;
-        }
-        if (lanes) wb[0].qcap = (uint32_t)(wb[0].capacity - wb[1].capacity);
         rt::WaveGrids wg;
         wg.cam = c->use_camera ? c->g_cam.set : rt::GridSet{};
         wg.lit = c->g_lit.set;
-        if (fr[0].n_local > wb[0].capacity || (lanes && (fr[0].n_local > wb[0].capacity - wb[1].capacity || fr[1].n_local > wb[1].capacity)))
-            return fail(RT_ERR_INVALID, "internal: wavefront buffers too small for the launch");
-        if (band <= 0) RT_CUDA(cudaEventRecord(c->ev0, c->stream));
-        uint32_t nl = 0, nl1 = 0;
-        if (lanes) {
-            RT_CUDA(cudaEventRecord(c->lane_go, c->stream));  // lane 1 starts after everything queued before this launch
-            RT_CUDA(cudaStreamWaitEvent(c->lane_stream, c->lane_go, 0));
+        RT_CUDA(cudaEventRecord(c->ev0, c->stream));  // every sequence starts after what was queued before this render
+        for (int k = 0; k < n_seq; ++k) {
+            cudaStream_t st = n_seq == 1 ? c->stream : c->seq_stream[k];
+            if (n_seq > 1) RT_CUDA(cudaStreamWaitEvent(st, c->ev0, 0));
+            uint32_t nl = 0;
+            if (fr[k].n_local > 0) RT_CUDA(rt::wave_render(c->scene, fr[k], wb[k], accel, &wg, c->sm_count, &nl, st));
+            c->last_launches += nl;
+            if (n_seq > 1 || host_out) RT_CUDA(cudaEventRecord(c->band_done[k], st));
+            if (host_out && fr[k].n_local > 0) {  // the band's rows go home under the kernels of the bands behind it
+                RT_CUDA(cudaStreamWaitEvent(c->copy_stream, c->band_done[k], 0));
+                if (!c->use_camera) {
+                    RT_CUDA(cudaMemcpyAsync(host_out, c->d_fb.p, c->n_rays * sizeof(float4), cudaMemcpyDeviceToHost, c->copy_stream));
+                } else if (c->n_shards <= 1) {
+                    const uint64_t first = (uint64_t)ub[k] * c->width, cnt = (uint64_t)(ub[k + 1] - ub[k]) * c->width;
+                    RT_CUDA(cudaMemcpyAsync(host_out + 4 * first, c->d_fb.p + first, cnt * sizeof(float4), cudaMemcpyDeviceToHost, c->copy_stream));
+                } else {
+                    for (uint32_t u = ub[k]; u < ub[k + 1]; ++u) {
+                        const uint32_t row = (c->shard + u * c->n_shards) * c->block_rows;
+                        if (row >= c->height) break;
+                        const uint64_t first = (uint64_t)row * c->width, cnt = (uint64_t)std::min(c->block_rows, c->height - row) * c->width;
+                        RT_CUDA(cudaMemcpyAsync(host_out + 4 * first, c->d_fb.p + first, cnt * sizeof(float4), cudaMemcpyDeviceToHost, c->copy_stream));
+                    }
+                }
+            }
         }
-        if (fr[0].n_local > 0) RT_CUDA(rt::wave_render(c->scene, fr[0], wb[0], accel, &wg, c->sm_count, &nl, c->stream));
-        if (lanes) {
-            if (fr[1].n_local > 0)
-                RT_CUDA(rt::wave_render(c->scene, fr[1], wb[1], accel, &wg, c->sm_count, &nl1, c->lane_stream));
-            RT_CUDA(cudaEventRecord(c->lane_done, c->lane_stream));
-            RT_CUDA(cudaStreamWaitEvent(c->stream, c->lane_done, 0));
-        }
-        c->last_launches += nl + nl1;
+        if (n_seq > 1)
+            for (int k = 0; k < n_seq; ++k) RT_CUDA(cudaStreamWaitEvent(c->stream, c->band_done[k], 0));
         RT_CUDA(cudaEventRecord(c->ev1, c->stream));
+        if (host_out) {
+            RT_CUDA(cudaEventRecord(c->copy_done, c->copy_stream));
+            RT_CUDA(cudaStreamWaitEvent(c->stream, c->copy_done, 0));
+            RT_CUDA(cudaEventRecord(c->ev2, c->stream));
+        }
         return RT_OK;
     }
     rt::Frame fr;
@@ -581,8 +606,21 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
     }
     c->last_launches = 1;
     RT_CUDA(cudaEventRecord(c->ev0, c->stream));
-    RT_CUDA(rt::launch_megakernel(c->scene, fr, accel, aov_only, c->stream));
+    RT_CUDA(rt::launch_megakernel(c->scene, fr, accel == RT_ACCEL_GRID ? (int)RT_ACCEL_BVH : accel, aov_only, c->stream));
     RT_CUDA(cudaEventRecord(c->ev1, c->stream));
+    if (host_out) {  // readback: the shard's row-blocks (or everything)
+        if (c->use_camera && c->n_shards > 1) {
+            const uint32_t br = c->block_rows, n_blocks = (c->height + br - 1) / br;
+            for (uint32_t b = c->shard; b < n_blocks; b += c->n_shards) {
+                const uint64_t first = (uint64_t)b * br * c->width;
+                const uint64_t cnt = (uint64_t)std::min(br, c->height - b * br) * c->width;
+                RT_CUDA(cudaMemcpyAsync(host_out + 4 * first, c->d_fb.p + first, cnt * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+            }
+        } else if (n_pixels(c)) {
+            RT_CUDA(cudaMemcpyAsync(host_out, c->d_fb.p, n_pixels(c) * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+        }
+        RT_CUDA(cudaEventRecord(c->ev2, c->stream));
+    }
     return RT_OK;
 }
 
@@ -627,12 +665,13 @@ int rt_create(rt_ctx** out, int device) {
     memset(&c->stats, 0, sizeof c->stats);
     memset(&c->scene, 0, sizeof c->scene);
     bool bands_ok = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) == cudaSuccess;
-    for (int i = 0; i < rt_ctx::kMaxBands && bands_ok; ++i)
-        bands_ok = cudaEventCreateWithFlags(&c->band_done[i], cudaEventDisableTiming) == cudaSuccess;
-    bands_ok = bands_ok && cudaEventCreate(&c->copy_ev[0]) == cudaSuccess && cudaEventCreate(&c->copy_ev[1]) == cudaSuccess;
-    bands_ok = bands_ok && cudaStreamCreateWithFlags(&c->lane_stream, cudaStreamNonBlocking) == cudaSuccess &&
-               cudaEventCreateWithFlags(&c->lane_go, cudaEventDisableTiming) == cudaSuccess &&
-               cudaEventCreateWithFlags(&c->lane_done, cudaEventDisableTiming) == cudaSuccess;
+    int prio_lo = 0, prio_hi = 0;  // numerically lower = higher priority
+    if (cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi) != cudaSuccess) prio_lo = prio_hi = 0;
+    for (int i = 0; i < rt_ctx::kMaxBands && bands_ok; ++i) {
+        bands_ok = cudaEventCreateWithFlags(&c->band_done[i], cudaEventDisableTiming) == cudaSuccess &&
+                   cudaStreamCreateWithPriority(&c->seq_stream[i], cudaStreamNonBlocking, std::min(prio_hi + i, prio_lo)) == cudaSuccess;
+    }
+    bands_ok = bands_ok && cudaEventCreateWithFlags(&c->copy_done, cudaEventDisableTiming) == cudaSuccess;
     if (!bands_ok || cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&c->ev0) != cudaSuccess ||
         cudaEventCreate(&c->ev1) != cudaSuccess || cudaEventCreate(&c->ev2) != cudaSuccess) {
         delete c;
@@ -659,13 +698,11 @@ int rt_destroy(rt_ctx* c) {
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->ev2) cudaEventDestroy(c->ev2);
-    for (int i = 0; i < 2; ++i)
-        if (c->copy_ev[i]) cudaEventDestroy(c->copy_ev[i]);
-    for (int i = 0; i < rt_ctx::kMaxBands; ++i)
+    for (int i = 0; i < rt_ctx::kMaxBands; ++i) {
         if (c->band_done[i]) cudaEventDestroy(c->band_done[i]);
-    if (c->lane_go) cudaEventDestroy(c->lane_go);
-    if (c->lane_done) cudaEventDestroy(c->lane_done);
-    if (c->lane_stream) cudaStreamDestroy(c->lane_stream);
+        if (c->seq_stream[i]) cudaStreamDestroy(c->seq_stream[i]);
+    }
+    if (c->copy_done) cudaEventDestroy(c->copy_done);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -692,13 +729,17 @@ int rt_set_option(rt_ctx* c, int option, int64_t value) {
             if (value < 0 || value > rt_ctx::kMaxBands) return fail(RT_ERR_INVALID, "readback bands must be 0 (auto) or 1..16");
             c->opt_bands = (int)value;
             return RT_OK;
+        case RT_OPT_ZERO_COPY:
+            if (value < -1 || value > 1) return fail(RT_ERR_INVALID, "zero copy must be -1 (auto), 0 or 1");
+            c->opt_zero_copy = (int)value;
+            return RT_OK;
         case RT_OPT_GRID_RES:
             if (value < 32 || value > 4096) return fail(RT_ERR_INVALID, "grid resolution must be 32..4096");
             c->opt_grid_res = (int)value;
             c->g_lit.dirty = true;
             return RT_OK;
         case RT_OPT_LANES:
-            if (value < 1 || value > 2) return fail(RT_ERR_INVALID, "lanes must be 1 or 2");
+            if (value < 0 || value > rt_ctx::kMaxBands) return fail(RT_ERR_INVALID, "lanes must be 0 (auto) or 1..16");
             c->opt_lanes = (int)value;
             return RT_OK;
         default: return fail(RT_ERR_INVALID, "unknown option");
@@ -788,82 +829,47 @@ int rt_render(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float* host_
     if (!host_out) return fail(RT_ERR_INVALID, "null output buffer");
     RT_CUDA(cudaSetDevice(c->device));
     int used = 0;
-    // Camera renders on the wavefront pipeline are cut into bands (rows, or the shard's row-blocks): the device->host
-    // copy of a finished band (copy stream) overlaps the kernels of the next one (compute stream).
-    const int nb = auto_bands(c);
-    const bool banded = c->use_camera && nb > 1 && local_pixels(c) >= (1ull << 21) && band_units(c) >= (uint32_t)(4 * nb) &&
-                        c->have_scene && pick_pipeline(c, pick_accel(c, accel), max_bounces, mode) == 1;
-    if (banded) {
-        uint32_t units0 = 0;  // units of the first band: its copy is timed for the next frame's split
-        for (int b = 0; b < nb; ++b) {
-            rc = render_on_device(c, max_bounces, mode, accel, c->d_fb.p, &used, false, b, nb);
+    // Zero-copy: when the caller's frame is page-locked memory the device can address (rt_host_alloc, rt_host_register,
+    // cudaHostAlloc), the kernels store every finished pixel straight into it -- one 128-bit store per pixel over PCIe,
+    // spread over the whole frame time instead of a copy at its end, no bands.  Render() semantics are kept: the call
+    // returns when the stream is idle, i.e. when the frame is in host memory (OpenCLRaytracer.cpp:91-94).
+    // MEASURED AND NOT THE DEFAULT (8K cfg5 frame, B200, PCIe 5): the 33 M scattered 16-byte stores stall wave_advance --
+    // kernels 33.0 -> 45.0 ms, end to end 45.1 ms against 37.2 ms for framebuffer in HBM + banded copies.
+    if (c->opt_zero_copy != 0 && c->have_scene) {
+        const bool wave = pick_pipeline(c, pick_accel(c, accel), max_bounces, mode) == 1;
+        void* dp = nullptr;
+        if ((wave || c->opt_zero_copy == 1) && n_pixels(c) > 0) {
+            if (cudaHostGetDevicePointer(&dp, host_out, 0) != cudaSuccess) {
+                (void)cudaGetLastError();  // pageable memory: the copy path below
+                dp = nullptr;
+            }
+        }
+        if (dp) {
+            rc = render_on_device(c, max_bounces, mode, accel, reinterpret_cast<float4*>(dp), &used);
             if (rc != RT_OK) return rc;
-            uint32_t u0, u1;
-            band_range(c, b, nb, &u0, &u1);
-            if (u1 == u0) continue;
-            RT_CUDA(cudaEventRecord(c->band_done[b], c->stream));
-            RT_CUDA(cudaStreamWaitEvent(c->copy_stream, c->band_done[b], 0));
-            if (b == 0) RT_CUDA(cudaEventRecord(c->copy_ev[0], c->copy_stream));
-            if (c->n_shards <= 1) {
-                const uint64_t first = (uint64_t)u0 * c->width, cnt = (uint64_t)(u1 - u0) * c->width;
-                RT_CUDA(cudaMemcpyAsync(host_out + 4 * first, c->d_fb.p + first, cnt * sizeof(float4), cudaMemcpyDeviceToHost, c->copy_stream));
-            } else {
-                for (uint32_t u = u0; u < u1; ++u) {
-                    const uint32_t row = (c->shard + u * c->n_shards) * c->block_rows;
-                    if (row >= c->height) break;
-                    const uint64_t first = (uint64_t)row * c->width, cnt = (uint64_t)std::min(c->block_rows, c->height - row) * c->width;
-                    RT_CUDA(cudaMemcpyAsync(host_out + 4 * first, c->d_fb.p + first, cnt * sizeof(float4), cudaMemcpyDeviceToHost, c->copy_stream));
-                }
-            }
-            if (b == 0) {
-                RT_CUDA(cudaEventRecord(c->copy_ev[1], c->copy_stream));
-                units0 = u1 - u0;
-            }
+            RT_CUDA(cudaEventRecord(c->ev2, c->stream));
+            RT_CUDA(cudaStreamSynchronize(c->stream));
+            rc = collect_stats(c, used, local_pixels(c), 1);
+            if (rc != RT_OK) return rc;
+            float ms = 0.f, ms2 = 0.f;
+            RT_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+            RT_CUDA(cudaEventElapsedTime(&ms2, c->ev0, c->ev2));
+            c->stats.kernel_ms = ms;
+            c->stats.total_ms = ms2;
+            return RT_OK;
         }
-        RT_CUDA(cudaEventRecord(c->band_done[0], c->copy_stream));
-        RT_CUDA(cudaStreamWaitEvent(c->stream, c->band_done[0], 0));  // ev2 on the compute stream, after the last copy
-        RT_CUDA(cudaEventRecord(c->ev2, c->stream));
-        RT_CUDA(cudaStreamSynchronize(c->stream));
-        rc = collect_stats(c, used, local_pixels(c), 1);
-        if (rc != RT_OK) return rc;
-        float ms = 0.f, ms2 = 0.f, cp = 0.f;
-        RT_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
-        RT_CUDA(cudaEventElapsedTime(&ms2, c->ev0, c->ev2));
-        c->stats.kernel_ms = ms;  // kernels of all bands (copies of earlier bands run underneath)
-        c->stats.total_ms = ms2;
-        // next frame's split: kernel time per unit : copy time per unit (the first band's copy, as fast as the link and
-        // the other ranks' copies let it be)
-        if (units0 && cudaEventElapsedTime(&cp, c->copy_ev[0], c->copy_ev[1]) == cudaSuccess && cp > 0.f && ms > 0.f) {
-            const double r = ((double)ms / band_units(c)) / ((double)cp / units0);
-            c->band_ratio = std::min(16.0, std::max(1.25, 0.5 * c->band_ratio + 0.5 * r));
-        }
-        return RT_OK;
     }
-    rc = render_on_device(c, max_bounces, mode, accel, c->d_fb.p, &used);
+    // kernels + copy: on the wavefront pipeline the frame is cut into concurrent bands whose copies overlap the kernels of
+    // the bands behind them (render_on_device)
+    rc = render_on_device(c, max_bounces, mode, accel, c->d_fb.p, &used, false, host_out);
     if (rc != RT_OK) return rc;
-    // readback: the shard's row-blocks (or everything)
-    uint64_t pixels;
-    if (c->use_camera && c->n_shards > 1) {
-        const uint32_t br = c->block_rows, n_blocks = (c->height + br - 1) / br;
-        pixels = 0;
-        for (uint32_t b = c->shard; b < n_blocks; b += c->n_shards) {
-            const uint64_t first = (uint64_t)b * br * c->width;
-            const uint64_t cnt = (uint64_t)std::min(br, c->height - b * br) * c->width;
-            RT_CUDA(cudaMemcpyAsync(host_out + 4 * first, c->d_fb.p + first, cnt * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
-            pixels += cnt;
-        }
-    } else {
-        pixels = n_pixels(c);
-        if (pixels) RT_CUDA(cudaMemcpyAsync(host_out, c->d_fb.p, pixels * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
-    }
-    RT_CUDA(cudaEventRecord(c->ev2, c->stream));
     RT_CUDA(cudaStreamSynchronize(c->stream));
-    rc = collect_stats(c, used, pixels, 1);
+    rc = collect_stats(c, used, local_pixels(c), 1);
     if (rc != RT_OK) return rc;
     float ms = 0.f, ms2 = 0.f;
     RT_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
     RT_CUDA(cudaEventElapsedTime(&ms2, c->ev0, c->ev2));
-    c->stats.kernel_ms = ms;
+    c->stats.kernel_ms = ms;  // all bands' kernels (copies of finished bands run underneath)
     c->stats.total_ms = ms2;
     return RT_OK;
 }
@@ -898,7 +904,7 @@ int rt_render_aov(rt_ctx* c, int accel, int32_t* host_hit_id, float* host_hit_t)
         RT_CUDA(cudaMemsetAsync(c->d_hit_id.p, 0xff, n * sizeof(int32_t), c->stream));
         RT_CUDA(cudaMemsetAsync(c->d_hit_t.p, 0, n * sizeof(float), c->stream));
     }
-    rc = render_on_device(c, 0, RT_MODE_HITTEST, accel, c->d_fb.p, &accel, true);
+    rc = render_on_device(c, 0, RT_MODE_HITTEST, accel, nullptr, &accel, true);  // AOVs only: the framebuffer is not touched
     if (rc != RT_OK) return rc;
     if (n) {
         RT_CUDA(cudaMemcpyAsync(host_hit_id, c->d_hit_id.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
@@ -1102,13 +1108,13 @@ int rt_ipc_close(rt_ctx* c, void* dev_ptr) {
 
 int rt_host_alloc(void** out, uint64_t bytes) {
     if (!out) return fail(RT_ERR_INVALID, "null argument");
-    RT_CUDA(cudaHostAlloc(out, std::max<uint64_t>(bytes, 1), cudaHostAllocPortable));
+    RT_CUDA(cudaHostAlloc(out, std::max<uint64_t>(bytes, 1), cudaHostAllocPortable | cudaHostAllocMapped));
     return RT_OK;
 }
 
 int rt_host_register(void* p, uint64_t bytes) {
     if (!p || !bytes) return fail(RT_ERR_INVALID, "null argument");
-    RT_CUDA(cudaHostRegister(p, bytes, cudaHostRegisterPortable));
+    RT_CUDA(cudaHostRegister(p, bytes, cudaHostRegisterPortable | cudaHostRegisterMapped));
     return RT_OK;
 }
 

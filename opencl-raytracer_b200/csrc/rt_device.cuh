@@ -185,7 +185,13 @@ __device__ __forceinline__ bool candidate(uint32_t type, const float4 s, const f
 // the sequential rules "sphere skipped only if hit.time < t" (SAR:108) and "box skipped
 // if hit.time <= t" (SAR:147; the triangle extension follows the box rule): among objects tied at the minimum t the winner is the
 // highest-index sphere if any sphere is tied, else the lowest-index box.
+// A candidate with t >= MAX_FLOAT (an overflowed t, +inf) never becomes a hit in the reference either: the sphere rule
+// skips it (MAX < t), the box rule skips it (MAX <= t), and t == MAX_FLOAT reads as "miss" at SAR:173.  A NaN t (a ray whose
+// object-space direction is zero or not finite) is OUTSIDE the bit-exact domain: the reference's sequential loop then
+// depends on the object order in a way no order-independent rule reproduces (every later candidate overwrites a NaN);
+// here such a candidate is dropped.
 __device__ __forceinline__ bool replaces(float tc, int32_t c, uint32_t type_c, float tk, int32_t k, uint32_t type_k) {
+    if (!(tc < RT_MAX_FLOAT)) return false;
     if (k < 0) return true;
     if (tc < tk) return true;
     if (tc > tk) return false;

@@ -8,6 +8,8 @@
 // (__f*_ru / __f*_rd), so the boxes contain what the host builder's double-precision boxes would contain.
 #include "rt_lbvh.cuh"
 
+#include "rt_device.cuh"
+
 #include <cub/cub.cuh>
 
 namespace rt {
@@ -32,6 +34,9 @@ __global__ void lbvh_keys(const LbvhLeaf* __restrict__ leaves, uint32_t n, float
     const float y = fminf(fmaxf((l.c[1] - lo.y) * inv.y, 0.f), 1023.f);
     const float z = fminf(fmaxf((l.c[2] - lo.z) * inv.z, 0.f), 1023.f);
     const uint32_t m = (expand10((uint32_t)x) << 2) | (expand10((uint32_t)y) << 1) | expand10((uint32_t)z);
+    // a radix tree is at most as deep as its keys have significant bits: 30 (Morton) + 27 (index; build_scene rejects
+    // 2^27 objects and more) = 57 levels, below the traversal stack of RT_BVH_STACK entries
+    static_assert(30 + 27 < RT_BVH_STACK, "LBVH depth bound exceeds the traversal stack");
     keys[i] = ((uint64_t)m << 32) | i;
 }
 

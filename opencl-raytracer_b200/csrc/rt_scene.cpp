@@ -16,7 +16,8 @@
 //      => box inflation                      + sqrt(g) * |oc|,                |oc| <= distance origin -> farthest box point
 //
 // plus static pads for the rounding of the transform itself.  K = 32 is twice the first-order worst case.
-// tests/test_bounds.py checks on adversarial scenes that no exact hit is ever filtered.
+// tests/test_emul.py (test_filters_never_drop_a_noisy_hit, test_perspective_grids_never_drop_a_noisy_hit) checks on
+// adversarial scenes that no exact hit is ever filtered.
 #include "rt_scene.hpp"
 
 #include <math.h>
@@ -719,6 +720,12 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
         }
     }
     out.bvh_depth = bld.max_depth;
+    // the traversal kernels keep RT_BVH_STACK (64) pending siblings per ray and push without a bound: SAH to depth 32, then
+    // median splits of at most 2^27 objects, stays below 60 -- enforced here rather than assumed
+    if (out.bvh_depth >= 62u) {
+        err = "BVH deeper than the traversal stack";
+        return RT_ERR_UNSUPPORTED;
+    }
 
     out.leaf_obj.resize(live.size());
     out.leaf_cull.resize(live.size());

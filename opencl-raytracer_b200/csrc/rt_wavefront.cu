@@ -14,6 +14,8 @@
 
 #include <stdlib.h>
 
+#include <algorithm>
+
 #include "rt_pgrid.cuh"
 #include "rt_wave.cuh"
 
@@ -568,7 +570,7 @@ __device__ __noinline__ void filter_flush(const Scene& sc, const TaskQueue& q, F
         const float4 d = ex::xform(c0, c1, c2, c3, q.d[i]);
         float t = 0.f;
         const bool hit = ex::candidate(type, s, d, t);
-        fs.res_t[warp][lane] = hit ? t : -1.f;  // candidates have t >= 0 (or NaN: ex::replaces treats it like the kernels do)
+        fs.res_t[warp][lane] = hit ? t : -1.f;  // candidates have t >= 0 (a NaN t is dropped by ex::replaces, see there)
         fs.res_type[warp][lane] = type;
     }
     __syncwarp();

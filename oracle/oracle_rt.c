@@ -347,11 +347,12 @@ typedef struct {
     atomic_ullong* next;
     oracle_stats st;
     int trace_only;
+    uint64_t chunk;
 } job_t;
 
 static void* worker(void* arg) {
     job_t* j = (job_t*)arg;
-    const uint64_t chunk = 256;
+    const uint64_t chunk = j->chunk ? j->chunk : 256;
     for (;;) {
         const uint64_t b = atomic_fetch_add(j->next, chunk);
         if (b >= j->N) break;
@@ -388,8 +389,12 @@ static int run_jobs(job_t* proto, int nthreads, oracle_stats* total) {
     job_t* jobs = (job_t*)calloc((size_t)nthreads, sizeof(job_t));
     pthread_t* th = (pthread_t*)calloc((size_t)nthreads, sizeof(pthread_t));
     if (!jobs || !th) return -1;
+    /* every thread gets work even on a few thousand expensive rays */
+    uint64_t chunk = proto->N / ((uint64_t)nthreads * 8u);
+    chunk = chunk < 1 ? 1 : (chunk > 256 ? 256 : chunk);
     for (int t = 0; t < nthreads; ++t) {
         jobs[t] = *proto;
+        jobs[t].chunk = chunk;
         jobs[t].next = &next;
         memset(&jobs[t].st, 0, sizeof(oracle_stats));
     }

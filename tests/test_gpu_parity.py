@@ -577,3 +577,36 @@ def test_perspective_grids_lights_everywhere(rt, ctx, oracle_mod):
                 assert (s.rays_primary, s.rays_shadow, s.rays_reflect) == (st.rays_primary, st.rays_shadow, st.rays_reflect)
                 if lts is many:
                     break
+
+
+def test_zero_copy_frame_equals_copied_frame(rt, ctx):
+    """rt_render into page-locked, device-addressable memory: the kernels store the pixels straight into the caller's frame
+    (RT_OPT_ZERO_COPY).  Same bits as the copy path -- whole frame, ragged shard, explicit rays, both pipelines."""
+    objs, lights = S.synthetic_scene(3000, 300)
+    W, H = 1024, 515
+    z = T.camera_zdir(H)
+    ctx.upload_scene(objs, lights)
+    ctx.set_camera(W, H, z)
+    pinned = rt.PinnedBuffer((W * H, 4))
+    try:
+        for pipeline in (1, 0):
+            ctx.set_option(rt.OPT_PIPELINE, pipeline)
+            ctx.set_option(rt.OPT_ZERO_COPY, 0)
+            ref = ctx.render(4, 2, -1).copy()
+            ctx.set_option(rt.OPT_ZERO_COPY, 1)
+            pinned.array[:] = -9.0
+            ctx.render(4, 2, -1, out=pinned.array)
+            assert np.array_equal(pinned.array, ref)
+            pinned.array[:] = -9.0
+            for s in range(3):
+                ctx.set_shard(16, s, 3)
+                ctx.render(4, 2, -1, out=pinned.array)
+            ctx.set_shard(1, 0, 1)
+            assert np.array_equal(pinned.array, ref)
+        ctx.set_option(rt.OPT_PIPELINE, -1)
+        ctx.set_option(rt.OPT_ZERO_COPY, -1)
+        pageable = np.full((W * H, 4), -9.0, dtype=np.float32)  # not device-addressable: the copy path, silently
+        ctx.render(4, 2, -1, out=pageable)
+        assert np.array_equal(pageable, ref)
+    finally:
+        pinned.close()
