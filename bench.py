@@ -203,6 +203,7 @@ def main():
     ap.add_argument("--lanes", type=int, default=0, help="1: one launch sequence per frame, 2: two half-frames on two streams (0 = library default)")
     ap.add_argument("--zero-copy", type=int, default=-1, help="rt_render stores into the pinned host frame directly: -1 library default, 0 off, 1 on")
     ap.add_argument("--grid-res", type=int, default=0, help="cells per side of the light grids (0 = library default)")
+    ap.add_argument("--grid3", type=int, default=-1, help="uniform 3-D grid for rays without an apex: cells per 100 objects (0 = BVH, -1 = library default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-brute-leg", action="store_true")
     args = ap.parse_args()
@@ -270,6 +271,8 @@ def main():
         ctx.set_option(lib.OPT_ZERO_COPY, args.zero_copy)
     if args.grid_res:
         ctx.set_option(lib.OPT_GRID_RES, args.grid_res)
+    if args.grid3 >= 0:
+        ctx.set_option(lib.OPT_GRID3_DENSITY, args.grid3)
     t_up0 = time.perf_counter()
     ctx.upload_scene(objs, lights)
     ctx.set_camera(W, H, zdir)

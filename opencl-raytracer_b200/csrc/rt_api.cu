@@ -121,6 +121,13 @@ struct rt_ctx {
     } g_cam, g_lit;
     DevBuf<uint32_t> g_cursor;
     DevBuf<char> g_scan;
+    // uniform 3-D grid (rt_grid3.cuh) for the rays without a common apex
+    DevBuf<uint32_t> g3_cell_start;
+    DevBuf<rt::Grid3Entry> g3_entries;
+    rt::Grid3 g3 = {};
+    bool g3_dirty = true;
+    uint64_t g3_n_entries = 0;
+    int opt_grid3 = 0;  // cells per 100 objects; 0 (default): off, the BVH serves these rays -- measured: no faster (build_grid3)
     uint32_t g_cam_w = 0, g_cam_h = 0;
     float g_cam_z = 0.f;
     int opt_grid_res = 512;
@@ -201,8 +208,9 @@ int sync_scene(rt_ctx* c) {
     s.root_f = c->hs.f_global;
     s.filter_h = c->hs.h_min;
     c->scene_dirty = false;
-    c->g_cam.dirty = c->g_lit.dirty = true;
+    c->g_cam.dirty = c->g_lit.dirty = c->g3_dirty = true;
     c->g_cam.set = c->g_lit.set = rt::GridSet{};
+    c->g3 = rt::Grid3{};
     return RT_OK;
 }
 
@@ -244,6 +252,72 @@ int build_grid_set(rt_ctx* c, rt_ctx::GridBufs& gb, std::vector<rt::PGrid>& grid
     gb.n_entries = total;
     gb.n_cells = n_cells;
     gb.build_ms = (float)std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return RT_OK;
+}
+
+// The uniform grid over the whole scene (rt_grid3.cuh): cubic cells, about opt_grid3 / 100 of them per object.  Not built --
+// the BVH stays in charge of the rays without a common apex -- when the lists come out long: objects that are large against
+// the cell (few big objects among many small ones, a clustered scene) would be entered into thousands of cells.
+// OFF BY DEFAULT.  Measured on the 8K cfg5 frame (profiles/r2_sweep_grid3.txt, r2_wave_trace_dda_cfg5_8k.txt): the walk needs
+// 15 cells and 38 filter tests per reflection ray where the BVH needs 52 node steps, but its two short code paths (cell step,
+// list entry) diverge inside the warp (10 and 17 of 32 lanes active), 5 800 thread instructions per ray against the BVH's
+// ~6 400: 33.2 ms per frame at the best density (4 cells per object) against 33.0 ms with the BVH.
+int build_grid3(rt_ctx* c) {
+    c->g3 = rt::Grid3{};
+    c->g3_dirty = false;
+    c->g3_n_entries = 0;
+    const uint32_t n_objs = c->hs.n_objs;
+    if (c->opt_grid3 <= 0 || n_objs < 64) return RT_OK;
+    const float ext0 = 2.f * c->hs.scene_radius + 1.f;
+    const float eps = 2e-5f * ext0 + 1e-4f;
+    double lo[3] = {1e30, 1e30, 1e30}, hi[3] = {-1e30, -1e30, -1e30}, rsum = 0;
+    uint32_t live = 0;
+    for (uint32_t o = 0; o < n_objs; ++o) {
+        float r;
+        if (!rt::grid3_object_sphere(c->hs.cull[o], c->hs.omax, eps, r)) continue;
+        ++live;
+        rsum += r;
+        const float ctr[3] = {c->hs.cull[o].cx, c->hs.cull[o].cy, c->hs.cull[o].cz};
+        for (int k = 0; k < 3; ++k) {
+            lo[k] = std::min(lo[k], (double)ctr[k] - r);
+            hi[k] = std::max(hi[k], (double)ctr[k] + r);
+        }
+    }
+    if (live < 64) return RT_OK;
+    double vol = 1;
+    for (int k = 0; k < 3; ++k) vol *= std::max(hi[k] - lo[k], 1e-3);
+    float h = (float)cbrt(vol / (c->opt_grid3 * 0.01 * live));
+    for (int k = 0; k < 3; ++k) h = std::max(h, (float)((hi[k] - lo[k]) / 1024.0));
+    rt::Grid3 g = {};
+    g.h = h;
+    g.inv_h = 1.f / h;
+    g.lox = (float)lo[0] - 2 * eps;
+    g.loy = (float)lo[1] - 2 * eps;
+    g.loz = (float)lo[2] - 2 * eps;
+    g.nx = (uint32_t)((hi[0] + 2 * eps - g.lox) / h) + 1;
+    g.ny = (uint32_t)((hi[1] + 2 * eps - g.loy) / h) + 1;
+    g.nz = (uint32_t)((hi[2] + 2 * eps - g.loz) / h) + 1;
+    g.eps = eps;
+    const uint64_t cells = (uint64_t)g.nx * g.ny * g.nz;
+    if (cells >= (1ull << 28)) return RT_OK;
+    const uint32_t n_cells = (uint32_t)cells;
+    RT_CUDA(c->g3_cell_start.ensure((size_t)n_cells + 1));
+    RT_CUDA(c->g_cursor.ensure((size_t)n_cells + 1));
+    const size_t sb = rt::pgrid_scan_bytes(n_cells);
+    RT_CUDA(c->g_scan.ensure(sb));
+    RT_CUDA(rt::grid3_count(g, c->d_cull.p, n_objs, c->hs.omax, c->g_cursor.p, c->g3_cell_start.p, c->g_scan.p, sb, c->stream));
+    uint32_t total = 0;
+    RT_CUDA(cudaMemcpyAsync(&total, c->g3_cell_start.p + n_cells, sizeof total, cudaMemcpyDeviceToHost, c->stream));
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    if ((uint64_t)total > 64ull * live) return RT_OK;  // long lists: the BVH serves this scene better
+    RT_CUDA(c->g3_entries.ensure(std::max<size_t>(total, 1)));
+    RT_CUDA(rt::grid3_fill(g, c->d_cull.p, n_objs, c->hs.omax, c->g_cursor.p, c->g3_cell_start.p, c->g3_entries.p, c->stream));
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    g.cell_start = c->g3_cell_start.p;
+    g.entries = c->g3_entries.p;
+    g.valid = 1;
+    c->g3 = g;
+    c->g3_n_entries = total;
     return RT_OK;
 }
 
@@ -519,6 +593,10 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
             rc = build_light_grids(c);
             if (rc != RT_OK) return rc;
         }
+        if (c->g3_dirty) {
+            rc = build_grid3(c);
+            if (rc != RT_OK) return rc;
+        }
         if (c->use_camera && (c->g_cam.dirty || c->g_cam_w != c->width || c->g_cam_h != c->height || c->g_cam_z != c->zdir)) {
             rc = build_camera_grid(c);
             if (rc != RT_OK) return rc;
@@ -563,6 +641,7 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
         rt::WaveGrids wg;
         wg.cam = c->use_camera ? c->g_cam.set : rt::GridSet{};
         wg.lit = c->g_lit.set;
+        wg.g3 = c->g3;
         RT_CUDA(cudaEventRecord(c->ev0, c->stream));  // every sequence starts after what was queued before this render
         for (int k = 0; k < n_seq; ++k) {
             cudaStream_t st = n_seq == 1 ? c->stream : c->seq_stream[k];
@@ -691,7 +770,7 @@ int rt_destroy(rt_ctx* c) {
     c->d_sink.release();
     c->g_cam.grids.release(); c->g_cam.cell_start.release(); c->g_cam.entries.release();
     c->g_lit.grids.release(); c->g_lit.cell_start.release(); c->g_lit.entries.release();
-    c->g_cursor.release(); c->g_scan.release();
+    c->g_cursor.release(); c->g_scan.release(); c->g3_cell_start.release(); c->g3_entries.release();
     c->w_acc.release(); c->w_refl.release(); c->w_P.release(); c->w_Nm.release(); c->w_Rc.release(); c->w_out.release();
     for (int i = 0; i < 2; ++i) { c->w_qs[i].release(); c->w_qd[i].release(); c->w_qpath[i].release(); }
     c->w_res_t.release(); c->w_res_id.release(); c->w_counts.release();
@@ -732,6 +811,11 @@ int rt_set_option(rt_ctx* c, int option, int64_t value) {
         case RT_OPT_ZERO_COPY:
             if (value < -1 || value > 1) return fail(RT_ERR_INVALID, "zero copy must be -1 (auto), 0 or 1");
             c->opt_zero_copy = (int)value;
+            return RT_OK;
+        case RT_OPT_GRID3_DENSITY:
+            if (value < 0 || value > 100000) return fail(RT_ERR_INVALID, "grid density must be 0 (off) .. 100000 cells per 100 objects");
+            c->opt_grid3 = (int)value;
+            c->g3_dirty = true;
             return RT_OK;
         case RT_OPT_GRID_RES:
             if (value < 32 || value > 4096) return fail(RT_ERR_INVALID, "grid resolution must be 32..4096");

@@ -16,6 +16,7 @@
 
 #include <algorithm>
 
+#include "rt_grid3.cuh"
 #include "rt_pgrid.cuh"
 #include "rt_wave.cuh"
 
@@ -497,6 +498,167 @@ __global__ void __launch_bounds__(kBlock, RT_GRID_MINB) wave_trace_grid(const Sc
     if (COUNT) flush_local(lc, ctr);
 }
 
+// ------------------------------------------------------------------------------------------------ trace: uniform grid, DDA
+// Class B tasks (everything without a common apex) on the uniform 3-D grid of rt_grid3.cuh instead of the BVH: per lane a
+// DDA walk, per cell a short object list through the bounding-sphere filter, survivors wait for the warp's next round of
+// exact tests.  An iteration of the walk loop moves a lane whose list is used up into the next cell AND tests one entry, so
+// the two short code paths do not alternate between warp votes.
+#ifndef RT_DDA_MINB
+#define RT_DDA_MINB 3
+#endif
+template <bool COUNT>
+__global__ void __launch_bounds__(kBlock, RT_DDA_MINB) wave_trace_dda(const Scene sc, const Grid3 g, const TaskQueue q, const uint32_t* __restrict__ n_ptr,
+                                                                     uint32_t* __restrict__ fetch, float* __restrict__ res_t, int32_t* __restrict__ res_id,
+                                                                     const int min_t, const int drain_t, const int refill_t, Counters* ctr) {
+    const uint32_t n = *n_ptr;
+    if (n == 0u) return;
+    const unsigned lane = threadIdx.x & 31u;
+    LocalCounters lc;
+    const uint32_t kNone = 0xffffffffu;
+
+    bool have = false, anyhit = false, done = false;
+    uint32_t at = 0;
+    float ox = 0.f, oy = 0.f, oz = 0.f, ux = 0.f, uy = 0.f, uz = 0.f;
+    Dda w;
+    w.ix = w.iy = w.iz = w.bx = w.by = w.bz = w.hx = w.hy = w.hz = w.t_end = 0.f;
+    w.cx = w.cy = w.cz = w.sx = w.sy = w.sz = 0;
+    Hit best;
+    best.t = RT_MAX_FLOAT;
+    best.id = -1;
+    uint32_t btype = 0, cur = 0, end = 0, pend = kNone, ptype = 0;
+    uint32_t mb0 = kNone, mb1 = kNone, mb2 = kNone, mb3 = kNone;  // the last objects this ray ran the exact test on
+    float4 ea = make_float4(0.f, 0.f, 0.f, 0.f), eb = ea;         // the list entry at `cur`, fetched one step ahead
+    const float4* ent4 = reinterpret_cast<const float4*>(g.entries);
+    bool exhausted = false;
+
+    for (;;) {
+        // ---- refill
+        {
+            const unsigned idle = __ballot_sync(kFull, !have);
+            const unsigned walk = __ballot_sync(kFull, have && pend == kNone && !done);
+            if (idle && !exhausted && (__popc(idle) >= refill_t || walk == 0u)) {
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(fetch, (uint32_t)__popc(idle));
+                base = __shfl_sync(kFull, base, 0);
+                if (!have) {
+                    const uint32_t i = base + (uint32_t)__popc(idle & lanemask_lt());
+                    if (i < n) {
+                        at = i;
+                        Ray ray;
+                        ray.s = q.s[i];
+                        ray.d = q.d[i];
+                        anyhit = (q.path[i] & RT_TASK_ANYHIT) != 0u;
+                        best.t = RT_MAX_FLOAT;
+                        best.id = -1;
+                        btype = 0;
+                        pend = kNone;
+                        mb0 = mb1 = mb2 = mb3 = kNone;
+                        have = true;
+                        done = false;
+                        cur = end = 0;
+                        const float chk = ray.s.x + ray.s.y + ray.s.z + ray.d.x + ray.d.y + ray.d.z;
+                        if (!(fabsf(chk) < __int_as_float(0x7f800000))) {
+                            // not finite (a hit point at infinity): the exact test on every object, as the reference does
+                            for (uint32_t k = 0; k < sc.n_objs; ++k) {
+                                exact_pair_call(sc, ray.s, ray.d, k, __ldg(&sc.cull[k].type), best, btype);
+                                if (COUNT) lc.exact_tests++;
+                            }
+                            done = true;
+                        } else if (!dda_start(g, ray, anyhit ? 1.f : RT_MAX_FLOAT, w)) {
+                            done = true;  // misses the grid
+                        } else {
+                            ox = ray.s.x; oy = ray.s.y; oz = ray.s.z;
+                            const float l = sqrtf(fmaf(ray.d.z, ray.d.z, fmaf(ray.d.y, ray.d.y, ray.d.x * ray.d.x)));
+                            const float il = 1.f / l;
+                            ux = ray.d.x * il; uy = ray.d.y * il; uz = ray.d.z * il;
+                            const uint32_t cell = dda_cell(g, w);
+                            cur = __ldg(g.cell_start + cell);
+                            end = __ldg(g.cell_start + cell + 1);
+                            if (COUNT) lc.node_visits++;
+                            if (cur < end) {
+                                ea = __ldg(ent4 + 2 * (size_t)cur);
+                                eb = __ldg(ent4 + 2 * (size_t)cur + 1);
+                            }
+                        }
+                    }
+                }
+                if (base + (uint32_t)__popc(idle) >= n) exhausted = true;
+            }
+            if (!__any_sync(kFull, have)) break;
+        }
+
+        // ---- walk
+        for (;;) {
+            const bool go = have && pend == kNone && !done;
+            const unsigned T = __ballot_sync(kFull, go);
+            if (T == 0u) break;
+            if (__popc(T) < min_t) {
+                if (__popc(__ballot_sync(kFull, have && pend != kNone)) >= drain_t) break;
+                if (!exhausted && __popc(__ballot_sync(kFull, !have || (pend == kNone && done))) >= refill_t) break;
+            }
+            if (go) {
+                if (cur >= end) {  // next cell
+                    int axis;
+                    const float t_exit = dda_exit(w, axis);
+                    // every object whose hit point lies before the exit of the cell just finished has been seen
+                    if ((best.id >= 0 && best.t < t_exit * (1.f - 1e-5f)) || t_exit > w.t_end || !dda_step(g, w, axis)) {
+                        done = true;
+                    } else {
+                        const uint32_t cell = dda_cell(g, w);
+                        cur = __ldg(g.cell_start + cell);
+                        end = __ldg(g.cell_start + cell + 1);
+                        if (COUNT) lc.node_visits++;
+                        if (cur < end) {
+                            ea = __ldg(ent4 + 2 * (size_t)cur);
+                            eb = __ldg(ent4 + 2 * (size_t)cur + 1);
+                        }
+                    }
+                } else {  // one entry: the record fetched last time round, the next one is requested before it is looked at
+                    const float4 a = ea, b = eb;
+                    ++cur;
+                    if (cur < end) {
+                        ea = __ldg(ent4 + 2 * (size_t)cur);
+                        eb = __ldg(ent4 + 2 * (size_t)cur + 1);
+                    }
+                    if (COUNT) lc.pair_tests++;
+                    const float x = a.x - ox, y = a.y - oy, z = a.z - oz;
+                    const float oc2 = fmaf(z, z, fmaf(y, y, x * x));
+                    const float dt = fmaf(z, uz, fmaf(y, uy, x * ux));
+                    const uint32_t obj = __float_as_uint(b.y);
+                    if (!(fmaf(-dt, dt, oc2 * b.x) > a.w) && obj != mb0 && obj != mb1 && obj != mb2 && obj != mb3) {  // cv::sphere_may_hit
+                        pend = obj;
+                        ptype = __float_as_uint(b.z);
+                    }
+                }
+            }
+        }
+
+        // ---- exact tests: when enough lanes hold a survivor, or nobody can walk on
+        {
+            const bool has = have && pend != kNone;
+            const unsigned P = __ballot_sync(kFull, has);
+            const unsigned W = __ballot_sync(kFull, have && pend == kNone && !done);
+            if (P != 0u && (__popc(P) >= drain_t || W == 0u)) {
+                if (has) {
+                    exact_pair_call(sc, q.s[at], q.d[at], pend, ptype, best, btype);
+                    if (COUNT) lc.exact_tests++;
+                    mb3 = mb2; mb2 = mb1; mb1 = mb0; mb0 = pend;
+                    pend = kNone;
+                    if (anyhit && best.t < 1.f) done = true;  // the shadow ray is decided (SAR:229)
+                }
+            }
+        }
+
+        // ---- retire
+        if (have && pend == kNone && done) {
+            res_t[at] = best.id >= 0 ? best.t : RT_MAX_FLOAT;
+            res_id[at] = best.id;
+            have = false;
+        }
+    }
+    if (COUNT) flush_local(lc, ctr);
+}
+
 // --------------------------------------------------------------------------- trace: brute force, two flavours
 // Exact arithmetic on every pair (reference order).
 template <bool COUNT>
@@ -933,6 +1095,8 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
     wp.qcap = wb.qcap;
     const unsigned pgrid = (unsigned)sm_count * RT_BVH_MINB;  // persistent trace: RT_BVH_MINB CTAs of 8 warps per SM
     const unsigned ggrid = (unsigned)sm_count * RT_GRID_MINB;
+    const unsigned dgrid = (unsigned)sm_count * RT_DDA_MINB;
+    static const int d_min_t = env_int("RT_DDA_MIN_T", 12), d_drain_t = env_int("RT_DDA_DRAIN", 4), d_refill_t = env_int("RT_DDA_REFILL", 16);
     const unsigned sgrid = (unsigned)sm_count * 8u;    // grid-stride kernels
     static const int adv_mult = env_int("RT_ADV_GRID", 3);  // = resident CTAs per SM; 3..32 measured within 1 %
     const unsigned agrid = (unsigned)sm_count * (unsigned)adv_mult;  // wave_advance
@@ -951,6 +1115,12 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
         }
         if (g == 0 && cam_grid) {
             // every primary ray is a class A task: no class B launch in this generation
+        } else if (accel_b == 2 && use_grids && grids->g3.valid) {
+            if (count)
+                wave_trace_dda<true><<<dgrid, kBlock, 0, stream>>>(sc, grids->g3, qin, nq, fetch + 2 * g, wb.res_t, wb.res_id, d_min_t, d_drain_t, d_refill_t, fr.counters);
+            else
+                wave_trace_dda<false><<<dgrid, kBlock, 0, stream>>>(sc, grids->g3, qin, nq, fetch + 2 * g, wb.res_t, wb.res_id, d_min_t, d_drain_t, d_refill_t, fr.counters);
+            ++nl;
         } else if (accel_b == 2) {
             if (count)
                 wave_trace_bvh<true><<<pgrid, kBlock, 0, stream>>>(sc, qin, nq, fetch + 2 * g, wb.res_t, wb.res_id, min_t, drain_t, refill_t, fr.counters);

@@ -2,6 +2,7 @@
 #pragma once
 
 #include "rt_kernels.cuh"
+#include "rt_grid3.cuh"
 #include "rt_pgrid.cuh"
 #include "rt_wave.cuh"
 
@@ -21,6 +22,7 @@ struct WaveBuffers {
 // The perspective grids of the camera and of the lights (rt_pgrid.cuh); valid_mask == 0: none.
 struct WaveGrids {
     GridSet cam, lit;
+    Grid3 g3;  // uniform grid for the rays without a common apex (valid == 0: they walk the BVH)
 };
 
 // Upper bound on the number of trace/advance generations of one frame.

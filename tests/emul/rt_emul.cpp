@@ -14,6 +14,7 @@
 
 #include "../../opencl-raytracer_b200/csrc/rt_pixel.cuh"
 #include "../../opencl-raytracer_b200/csrc/rt_pgrid.cuh"
+#include "../../opencl-raytracer_b200/csrc/rt_grid3.cuh"
 #include "../../opencl-raytracer_b200/csrc/rt_wave.cuh"
 #include "../../opencl-raytracer_b200/csrc/rt_scene.hpp"
 
@@ -81,6 +82,65 @@ struct HostGrids {
         set.entries = entries.data();
         set.n_grids = (uint32_t)grids.size();
         set.valid_mask = valid_mask;
+    }
+};
+
+// Host stand-in for the device builder of the uniform 3-D grid (rt_pgrid.cu), same per-object functions.
+struct HostGrid3 {
+    std::vector<uint32_t> cell_start;
+    std::vector<rt::Grid3Entry> entries;
+    rt::Grid3 g{};
+    void build(const rt::HostScene& hs, float cells_per_object) {
+        double lo[3] = {1e30, 1e30, 1e30}, hi[3] = {-1e30, -1e30, -1e30};
+        uint32_t live = 0;
+        std::vector<float> rad(hs.n_objs, -1.f);
+        const float ext0 = 2.f * hs.scene_radius + 1.f;
+        const float eps = 2e-5f * ext0 + 1e-4f;
+        for (uint32_t o = 0; o < hs.n_objs; ++o) {
+            float r;
+            if (!rt::grid3_object_sphere(hs.cull[o], hs.omax, eps, r)) continue;
+            rad[o] = r;
+            ++live;
+            const float c[3] = {hs.cull[o].cx, hs.cull[o].cy, hs.cull[o].cz};
+            for (int k = 0; k < 3; ++k) {
+                lo[k] = std::min(lo[k], (double)c[k] - r);
+                hi[k] = std::max(hi[k], (double)c[k] + r);
+            }
+        }
+        if (!live) return;
+        double vol = 1;
+        for (int k = 0; k < 3; ++k) vol *= std::max(hi[k] - lo[k], 1e-3);
+        float h = (float)cbrt(vol / (cells_per_object * live));
+        for (int k = 0; k < 3; ++k) h = std::max(h, (float)((hi[k] - lo[k]) / 1024.0));
+        g.h = h;
+        g.inv_h = 1.f / h;
+        g.lox = (float)lo[0] - 2 * eps; g.loy = (float)lo[1] - 2 * eps; g.loz = (float)lo[2] - 2 * eps;
+        g.nx = (uint32_t)((hi[0] + 2 * eps - g.lox) / h) + 1;
+        g.ny = (uint32_t)((hi[1] + 2 * eps - g.loy) / h) + 1;
+        g.nz = (uint32_t)((hi[2] + 2 * eps - g.loz) / h) + 1;
+        g.eps = eps;
+        const uint32_t cells = g.nx * g.ny * g.nz;
+        std::vector<std::vector<uint32_t>> lists(cells);
+        for (uint32_t o = 0; o < hs.n_objs; ++o) {
+            if (rad[o] < 0.f) continue;
+            int l[3], u[3];
+            rt::grid3_object_cells(g, hs.cull[o], rad[o], l, u);
+            for (int z = l[2]; z <= u[2]; ++z)
+                for (int y = l[1]; y <= u[1]; ++y)
+                    for (int x = l[0]; x <= u[0]; ++x) lists[((uint32_t)z * g.ny + y) * g.nx + x].push_back(o);
+        }
+        cell_start.assign(cells + 1, 0);
+        for (uint32_t c = 0; c < cells; ++c) {
+            cell_start[c + 1] = cell_start[c] + (uint32_t)lists[c].size();
+            for (uint32_t o : lists[c]) {
+                const rt::CullRec& cr = hs.cull[o];
+                entries.push_back(rt::Grid3Entry{cr.cx, cr.cy, cr.cz, cr.r2, cr.h, o, cr.type, 0u});
+            }
+        }
+        if (entries.empty()) entries.push_back(rt::Grid3Entry{});
+        g.cell_start = cell_start.data();
+        g.entries = entries.data();
+        g.valid = 1;
     }
 };
 
@@ -199,7 +259,7 @@ int emul_render(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
 int emul_render_wave(const rt_object* objs, uint32_t n_objs, const rt_light* lights, uint32_t n_lights, const rt_ray* rays,
                      uint64_t n_rays, uint32_t max_bounces, int mode, int accel, int leaf, float omax_user, float* out_rgba,
                      uint64_t* counters_out, uint32_t* generations_out, uint32_t cam_w, uint32_t cam_h, float cam_zdir, uint32_t grid_res,
-                     uint32_t tile_w, uint32_t tile_h) {
+                     uint32_t tile_w, uint32_t tile_h, float grid3_density, uint64_t* cells_out) {
     rt::HostScene hs;
     const int rc = rt::build_scene(objs, n_objs, lights, n_lights, omax_user, leaf, hs, g_err);
     if (rc != RT_OK) return rc;
@@ -224,6 +284,9 @@ int emul_render_wave(const rt_object* objs, uint32_t n_objs, const rt_light* lig
     // accel 3: perspective grids for the camera rays (the rays must then be the cam_w x cam_h pinhole frame) and for the
     // shadow rays of point lights, the BVH for everything else -- as wave_render does (rt_wavefront.cu)
     HostGrids cam, lit;
+    HostGrid3 g3;
+    unsigned long long n_cells = 0;
+    if (accel == 3 && grid3_density > 0.f && n_objs) g3.build(hs, grid3_density);
     if (accel == 3) {
         if (cam_w && n_objs) camera_grid(cam, hs, cam_w, cam_h, cam_zdir, tile_w, tile_h);
         if (n_objs) light_grids(lit, hs, lights, n_lights, grid_res);
@@ -250,6 +313,11 @@ int emul_render_wave(const rt_object* objs, uint32_t n_objs, const rt_light* lig
                 unsigned long long np = 0;
                 h = rt::trace_grid<true>(sc, lit.set, 6u * ((pb >> RT_TASK_LIGHT_SHIFT) & 15u), ray, &np, &ne);
                 lc.pair_tests += np;
+            } else if (accel == 3 && g3.g.valid) {
+                unsigned long long np = 0;
+                if (pb & RT_TASK_ANYHIT) h = rt::trace_grid3<true>(sc, g3.g, ray, 1.f, &np, &ne, &n_cells);
+                else h = rt::trace_grid3<false>(sc, g3.g, ray, RT_MAX_FLOAT, &np, &ne, &n_cells);
+                lc.pair_tests += np;
             } else if (pb & RT_TASK_ANYHIT) h = rt::trace_bvh<true>(sc, ray, 1.f, &ne, &nn);
             else h = rt::trace_bvh<false>(sc, ray, RT_MAX_FLOAT, &ne, &nn);
             lc.exact_tests += ne;
@@ -270,6 +338,7 @@ int emul_render_wave(const rt_object* objs, uint32_t n_objs, const rt_light* lig
         ++g;
     }
     if (generations_out) *generations_out = g;
+    if (cells_out) *cells_out = n_cells;
     if (g > rt_wave_max_generations_host(max_bounces, n_lights, mode)) {
         g_err = "more generations than wave_max_generations allows";
         return RT_ERR_INVALID;

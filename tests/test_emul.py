@@ -291,3 +291,22 @@ def test_perspective_grids_never_drop_a_noisy_hit(oracle_mod):
     # the grid lookup only needs the camera's (W, H, zdir): the rays are a subset of that frame
     out, c, _ = emul.render_wave(objs, lights, sub, 2, 2, 3, camera=(W, H, z), grid_res=256)
     assert np.array_equal(out, ref)
+
+
+def test_uniform_grid_walk_bit_exact(oracle_mod):
+    """rt_grid3.cuh: the DDA walk over a uniform grid for the rays without a common apex, several cell sizes, rays that start
+    outside the grid, axis-parallel rays."""
+    objs, lights = S.synthetic_scene(3000, 300, n_lights=3)
+    W, H = 96, 54
+    z, rays = frame_rays(W, H)
+    ref, *_ = oracle_mod.port_render(2, 4, objs, lights, rays)
+    for dens in (0.25, 1.0, 8.0):
+        out, c, _ = emul.render_wave(objs, lights, rays, 4, 2, 3, camera=(W, H, z), grid_res=64, grid3=dens)
+        assert np.array_equal(out, ref) and c["cells"] > 0
+    rr = random_rays(3000, 9)
+    rr["direction"][::7, 0] = 0.0   # walks that never leave their x slab
+    rr["direction"][::11, 1:3] = 0.0
+    rr["direction"][::11, 0] = 3.0
+    ref, *_ = oracle_mod.port_render(2, 4, objs, lights, rr)
+    out, c, _ = emul.render_wave(objs, lights, rr, 4, 2, 3, camera=None, grid_res=64, grid3=2.0)
+    assert np.array_equal(out, ref)

@@ -610,3 +610,33 @@ def test_zero_copy_frame_equals_copied_frame(rt, ctx):
         assert np.array_equal(pageable, ref)
     finally:
         pinned.close()
+
+
+def test_uniform_grid_walk_equals_bvh(rt, ctx, oracle_mod):
+    """RT_OPT_GRID3_DENSITY: the rays without a common apex walk a uniform 3-D grid (DDA, rt_grid3.cuh) instead of the BVH
+    (off by default).  Same hits, same frame -- camera rays, caller rays, a shard."""
+    objs, lights = S.synthetic_scene(6000, 500, n_lights=3)
+    lights = lights.copy()
+    lights[1]["position"] = (0.3, 0.8, 0.5, 0.0)  # directional: its shadow rays are class B too
+    W, H = 200, 112
+    z, rays = frame_rays(W, H)
+    ref, hid, ht, st = oracle_mod.port_render(2, 4, objs, lights, rays)
+    ctx.set_option(rt.OPT_PIPELINE, 1)
+    ctx.set_option(rt.OPT_COUNT_RAYS, 1)
+    for density in (50, 200, 1600):
+        ctx.set_option(rt.OPT_GRID3_DENSITY, density)
+        ctx.upload_scene(objs, lights)
+        ctx.set_camera(W, H, z)
+        out = ctx.render(4, 2, 3)
+        s = ctx.stats()
+        assert_colours_close(out, ref)
+        assert (s.rays_primary, s.rays_shadow, s.rays_reflect) == (st.rays_primary, st.rays_shadow, st.rays_reflect)
+        ctx.set_rays(rays)
+        assert np.array_equal(ctx.render(4, 2, 3), out)
+        gid, gt = ctx.render_aov(3)
+        assert np.array_equal(gid, hid) and np.array_equal(gt, ht)
+    rr = random_rays(20000, 5)
+    rid, rtt = oracle_mod.port_trace(objs, rr)
+    ctx.set_rays(rr)
+    gid, gt = ctx.render_aov(3)
+    assert np.array_equal(gid, rid) and np.array_equal(gt, rtt)

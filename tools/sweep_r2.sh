@@ -1,5 +1,5 @@
-# round-2 sweeps of the frame-level knobs (gpurun -- bash tools/sweep_r2.sh)
-for h in -1 2 4 6; do for b in 2 4 6 8; do
-RT_HEAD_GEN=$h python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-brute-leg --bands $b --lanes $b 2>/dev/null | python -c "
-import json,sys; d=json.loads(sys.stdin.read()); print('head $h bands $b kernel %.2f e2e %.2f dev %s launches %d'%(d['ms_per_step'],d['e2e']['ms_per_step'],d['e2e']['device_ms'],d['gpu_launches']))"
-done; done
+# round-2 sweeps (gpurun -- bash tools/sweep_r2.sh)
+for d in 0 50 100 200 400 800; do
+python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-brute-leg --grid3 $d 2>/dev/null | python -c "
+import json,sys; d=json.loads(sys.stdin.read()); print('grid3 $d kernel %.2f e2e %.2f pair %d exact %d cells/nodes %d upload %.0f'%(d['ms_per_step'],d['e2e']['ms_per_step'],d['rays']['pair_tests'],d['rays']['exact_tests'],d['rays']['node_visits'],d['config']['scene_upload_ms']))"
+done
