@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RT_B200_ABI_VERSION 1
+#define RT_B200_ABI_VERSION 2
 
 typedef struct rt_ctx rt_ctx;
 
@@ -129,6 +129,8 @@ typedef enum rt_option {
                                   device (scenes that change every frame: ~1 ms instead of ~150 ms per 10^5 objects, a looser tree) */
     RT_OPT_LANES = 7,      /* 2 (default): camera launches of the wavefront pipeline run as two halves on two streams, each filling the
                               thin generation tails of the other; 1: one launch sequence */
+    RT_OPT_DETECT_PINHOLE = 11, /* 1 (default): rt_set_rays recognises the pinhole grid main() builds (OpenCL-Raytracer.cpp:68-72) and
+                                   switches to rt_set_camera (device ray generation, no 32 B/ray upload); 0: upload whatever arrives */
     RT_OPT_ZERO_COPY = 9,  /* rt_render into page-locked, device-addressable host memory (rt_host_alloc / rt_host_register / cudaHostAlloc):
                               the kernels store finished pixels straight into the caller's frame instead of a framebuffer in HBM that is
                               copied afterwards.  -1 (default): on the wavefront pipeline, 0: never, 1: on both pipelines */
@@ -155,12 +157,14 @@ int rt_set_option(rt_ctx* ctx, int option, int64_t value);
 /* Repack the AoS scene into the device SoA (and build the BVH lazily). */
 int rt_upload_scene(rt_ctx* ctx, const rt_object* objs, uint32_t n_objs, const rt_light* lights, uint32_t n_lights);
 
-/* Rays: either an explicit host array (any rays, index = output index) ... */
+/* Rays: either an explicit host array (any rays, index = output index; the pinhole grid is recognised, RT_OPT_DETECT_PINHOLE) ... */
 int rt_set_rays(rt_ctx* ctx, const rt_ray* host_rays, uint64_t n_rays);
 /* ... or the reference's pinhole grid generated on the device, bit-identical to
  * OpenCL-Raytracer.cpp:18-26,68-72: start (0,0,0,1), dir (ii - W/2, (H - jj) - H/2, zdir, 0),
  * zdir = -(H/2)/tan(fov/2) computed by the caller in float. */
 int rt_set_camera(rt_ctx* ctx, uint32_t width, uint32_t height, float zdir);
+/* The camera in use (set by rt_set_camera, or recognised by rt_set_rays); RT_ERR_INVALID when the context renders caller rays. */
+int rt_get_camera(rt_ctx* ctx, uint32_t* width, uint32_t* height, float* zdir);
 /* Restrict this context to a shard of the camera frame: row-blocks of
  * `block_rows` rows dealt round-robin, this context owning blocks b with
  * b % n_shards == shard.  (1 block, shard 0 of 1) = whole frame. */
@@ -188,9 +192,12 @@ int rt_trace(rt_ctx* ctx, const rt_ray* host_rays, uint64_t n_rays, int accel, i
 
 int rt_get_stats(rt_ctx* ctx, rt_stats* out);
 
-/* Byte-identical device version of PPMExporter.cpp:19-21 quantisation:
- * min(255, (int)floorf(c * 255.f)) per channel, rgb8 packed, from a host float4 frame. */
-int rt_quantize_rgb8(rt_ctx* ctx, const float* host_rgba, uint64_t n_pixels, int32_t* host_rgb_out);
+/* Device version of PPMExporter.cpp:19-21 quantisation, min(255, (int)floorf(c * 255.f)) per channel, packed rgb8
+ * (3 bytes per pixel).  host_rgba == NULL: the frame the last render left in the context's DEVICE framebuffer (nothing is
+ * uploaded, n_pixels is ignored); otherwise a host float4 frame of n_pixels.  The exporter prints a negative channel as a
+ * negative number; bytes cannot, so negative channels are clamped to 0 and counted in *n_negative (may be NULL): a caller
+ * that needs the exporter's exact text falls back to it when the count is not zero. */
+int rt_quantize_rgb8(rt_ctx* ctx, const float* host_rgba, uint64_t n_pixels, uint8_t* host_rgb_out, uint64_t* n_negative);
 
 /* Multi-GPU, one process per GPU: the gather root exports its device framebuffer as a
  * 64-byte CUDA IPC handle; every other rank opens it and passes the mapped pointer to rt_render_device,

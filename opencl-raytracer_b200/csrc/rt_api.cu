@@ -10,6 +10,7 @@
 #include <algorithm>
 #include <chrono>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/rt_b200.h"
@@ -133,6 +134,7 @@ struct rt_ctx {
     int opt_grid_res = 512;
 
     // options
+    int opt_detect_pinhole = 1;
     int opt_zero_copy = 0;  // 0 (default) never, 1 whenever the target is mapped pinned memory, -1 on the wavefront pipeline only -- measured slower, see rt_render
     int opt_pipeline = -1, opt_count = 0, opt_leaf = 1, opt_skip_dead = 1, opt_bands = 0, opt_builder = 0, opt_lanes = 0;
 
@@ -382,6 +384,52 @@ int build_light_grids(rt_ctx* c) {
         if (c->g_lit.set.valid_mask || valid == 0u || res <= 64) break;
     }
     return RT_OK;
+}
+
+// Is `rays` the W x H pinhole grid main() builds (OpenCL-Raytracer.cpp:18-26,68-72): start (0,0,0,1), direction
+// (ii - W/2, (H - jj) - H/2, zdir, 0), row-major, zdir < 0 the same for all?  W is where direction.y first changes.
+bool detect_pinhole(const rt_ray* rays, uint64_t n, uint32_t* w_out, uint32_t* h_out, float* z_out) {
+    const float z = rays[0].direction[2], y0 = rays[0].direction[1];
+    if (!(z < 0.f) || !std::isfinite(z)) return false;
+    uint64_t w = n;
+    for (uint64_t i = 1; i < n; ++i)
+        if (rays[i].direction[1] != y0) {
+            w = i;
+            break;
+        }
+    if (w == 0 || n % w != 0 || w >= (1ull << 31) || n / w >= (1ull << 31)) return false;
+    const uint64_t h = n / w;
+    const float half_w = (float)w / 2.0f, half_h = (float)h / 2.0f;
+    const int nt = (int)std::min<uint64_t>(std::max<uint64_t>(n >> 20, 1), std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u));
+    std::vector<char> ok(nt, 1);
+    auto check = [&](int t) {
+        const uint64_t r0 = h * t / nt, r1 = h * (t + 1) / nt;
+        for (uint64_t jj = r0; jj < r1; ++jj) {
+            const float dy = (float)((int)h - (int)jj) - half_h;
+            const rt_ray* row = rays + jj * w;
+            for (uint64_t ii = 0; ii < w; ++ii) {
+                const rt_ray& r = row[ii];
+                if (r.start[0] != 0.f || r.start[1] != 0.f || r.start[2] != 0.f || r.start[3] != 1.f || r.direction[3] != 0.f ||
+                    r.direction[0] != (float)ii - half_w || r.direction[1] != dy || r.direction[2] != z) {
+                    ok[t] = 0;
+                    return;
+                }
+            }
+        }
+    };
+    if (nt == 1) {
+        check(0);
+    } else {
+        std::vector<std::thread> pool;
+        for (int t = 0; t < nt; ++t) pool.emplace_back(check, t);
+        for (auto& th : pool) th.join();
+    }
+    for (char k : ok)
+        if (!k) return false;
+    *w_out = (uint32_t)w;
+    *h_out = (uint32_t)h;
+    *z_out = z;
+    return true;
 }
 
 int pick_accel(const rt_ctx* c, int accel) {
@@ -808,6 +856,9 @@ int rt_set_option(rt_ctx* c, int option, int64_t value) {
             if (value < 0 || value > rt_ctx::kMaxBands) return fail(RT_ERR_INVALID, "readback bands must be 0 (auto) or 1..16");
             c->opt_bands = (int)value;
             return RT_OK;
+        case RT_OPT_DETECT_PINHOLE:
+            c->opt_detect_pinhole = value ? 1 : 0;
+            return RT_OK;
         case RT_OPT_ZERO_COPY:
             if (value < -1 || value > 1) return fail(RT_ERR_INVALID, "zero copy must be -1 (auto), 0 or 1");
             c->opt_zero_copy = (int)value;
@@ -845,6 +896,22 @@ int rt_set_rays(rt_ctx* c, const rt_ray* host_rays, uint64_t n) {
     if (!c) return fail(RT_ERR_INVALID, "null context");
     if (n && !host_rays) return fail(RT_ERR_INVALID, "null rays");
     RT_CUDA(cudaSetDevice(c->device));
+    if (c->opt_detect_pinhole && n >= 2) {
+        // The reference's main() hands its tracer exactly one kind of ray vector: the pinhole grid of OpenCL-Raytracer.cpp:68-72.
+        // If that is what arrived, nothing is uploaded (1.06 GB at 8K): the rays are generated on the device, bit for bit the
+        // same, and the frame gets the camera's perspective grid, bands and lanes -- the unmodified drop-in is the fast path.
+        uint32_t w = 0, h = 0;
+        float z = 0.f;
+        if (detect_pinhole(host_rays, n, &w, &h, &z)) {
+            const int rc = rt_set_camera(c, w, h, z);
+            if (rc == RT_OK) {
+                c->n_rays = n;
+                c->have_rays = false;
+                c->d_rays.release();
+            }
+            return rc;
+        }
+    }
     double omax2 = 0.0;
     for (uint64_t i = 0; i < n; ++i) {
         const float* s = host_rays[i].start;
@@ -877,6 +944,15 @@ int rt_set_camera(rt_ctx* c, uint32_t width, uint32_t height, float zdir) {
     c->use_camera = true;
     c->g_cam.dirty = true;
     RT_CUDA(c->d_fb.ensure((uint64_t)width * height));
+    return RT_OK;
+}
+
+int rt_get_camera(rt_ctx* c, uint32_t* width, uint32_t* height, float* zdir) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    if (!c->use_camera) return fail(RT_ERR_INVALID, "the context renders caller-supplied rays, not the pinhole camera");
+    if (width) *width = c->width;
+    if (height) *height = c->height;
+    if (zdir) *zdir = c->zdir;
     return RT_OK;
 }
 
@@ -1065,22 +1141,39 @@ int rt_get_stats(rt_ctx* c, rt_stats* out) {
     return RT_OK;
 }
 
-int rt_quantize_rgb8(rt_ctx* c, const float* host_rgba, uint64_t n, int32_t* host_rgb_out) {
+int rt_quantize_rgb8(rt_ctx* c, const float* host_rgba, uint64_t n, uint8_t* host_rgb_out, uint64_t* n_negative) {
     if (!c) return fail(RT_ERR_INVALID, "null context");
-    if (n && (!host_rgba || !host_rgb_out)) return fail(RT_ERR_INVALID, "null argument");
-    if (n == 0) return RT_OK;
-    RT_CUDA(cudaSetDevice(c->device));
+    if (n_negative) *n_negative = 0;
+    const float4* src = nullptr;
     DevBuf<float4> in;
-    DevBuf<int32_t> outb;
-    cudaError_t e = in.ensure(n);
-    if (e == cudaSuccess) e = outb.ensure(3 * n);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(in.p, host_rgba, n * sizeof(float4), cudaMemcpyHostToDevice, c->stream);
-    if (e == cudaSuccess) e = rt::launch_quantize(in.p, n, outb.p, c->stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(host_rgb_out, outb.p, 3 * n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream);
+    RT_CUDA(cudaSetDevice(c->device));
+    if (!host_rgba) {  // the frame the last render left in this context's device framebuffer: nothing is uploaded
+        if (!c->use_camera && !c->have_rays) return fail(RT_ERR_INVALID, "no frame: neither rays nor a camera are set");
+        n = n_pixels(c);
+        src = c->d_fb.p;
+    }
+    if (n == 0) return RT_OK;
+    if (!host_rgb_out) return fail(RT_ERR_INVALID, "null argument");
+    DevBuf<uint8_t> outb;
+    DevBuf<unsigned long long> neg;
+    cudaError_t e = outb.ensure(3 * n);
+    if (e == cudaSuccess) e = neg.ensure(1);
+    if (e == cudaSuccess) e = cudaMemsetAsync(neg.p, 0, sizeof(unsigned long long), c->stream);
+    if (e == cudaSuccess && host_rgba) {
+        e = in.ensure(n);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(in.p, host_rgba, n * sizeof(float4), cudaMemcpyHostToDevice, c->stream);
+        src = in.p;
+    }
+    unsigned long long h_neg = 0;
+    if (e == cudaSuccess) e = rt::launch_quantize(src, n, outb.p, neg.p, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(host_rgb_out, outb.p, 3 * n, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&h_neg, neg.p, sizeof h_neg, cudaMemcpyDeviceToHost, c->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
     in.release();
     outb.release();
+    neg.release();
     if (e != cudaSuccess) return fail(RT_ERR_CUDA, std::string("rt_quantize_rgb8: ") + cudaGetErrorString(e));
+    if (n_negative) *n_negative = h_neg;
     return RT_OK;
 }
 

@@ -99,14 +99,40 @@ __global__ void __launch_bounds__(kBlock) trace_rays(const Scene sc, const Ray* 
     if (COUNT) flush_counters(lc, counters);
 }
 
-// PPMExporter.cpp:19-21: min(255, (int)floorf(c * 255.f)) per channel, no lower clamp.
-__global__ void quantize_rgb8(const float4* __restrict__ rgba, const uint64_t n, int32_t* __restrict__ rgb) {
-    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const float4 p = __ldg(rgba + i);
-    rgb[3 * i + 0] = min(255, (int)floorf(__fmul_rn(p.x, 255.f)));
-    rgb[3 * i + 1] = min(255, (int)floorf(__fmul_rn(p.y, 255.f)));
-    rgb[3 * i + 2] = min(255, (int)floorf(__fmul_rn(p.z, 255.f)));
+// PPMExporter.cpp:19-21: min(255, (int)floorf(c * 255.f)) per channel.  The exporter has no lower clamp (a negative channel
+// is printed as a negative number); bytes cannot hold that, so negative channels are clamped to 0 AND counted -- the caller
+// falls back to the integer path when the count is not zero.  Four pixels per thread: 64 bytes in, three 32-bit words out.
+__device__ __forceinline__ uint32_t quant1(float c, unsigned long long& neg) {
+    const int q = (int)floorf(__fmul_rn(c, 255.f));
+    if (q < 0) ++neg;
+    return (uint32_t)min(255, max(q, 0));
+}
+__global__ void __launch_bounds__(256) quantize_rgb8(const float4* __restrict__ rgba, const uint64_t n, uint8_t* __restrict__ rgb,
+                                                     unsigned long long* __restrict__ n_negative) {
+    const uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;  // group of four pixels
+    unsigned long long neg = 0;
+    if (4 * g + 3 < n) {
+        uint32_t b[12];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float4 p = __ldg(rgba + 4 * g + k);
+            b[3 * k] = quant1(p.x, neg);
+            b[3 * k + 1] = quant1(p.y, neg);
+            b[3 * k + 2] = quant1(p.z, neg);
+        }
+        uint32_t* o = reinterpret_cast<uint32_t*>(rgb + 12 * g);  // 12 g is a multiple of 4: aligned
+        o[0] = b[0] | (b[1] << 8) | (b[2] << 16) | (b[3] << 24);
+        o[1] = b[4] | (b[5] << 8) | (b[6] << 16) | (b[7] << 24);
+        o[2] = b[8] | (b[9] << 8) | (b[10] << 16) | (b[11] << 24);
+    } else {
+        for (uint64_t i = 4 * g; i < n; ++i) {
+            const float4 p = __ldg(rgba + i);
+            rgb[3 * i] = (uint8_t)quant1(p.x, neg);
+            rgb[3 * i + 1] = (uint8_t)quant1(p.y, neg);
+            rgb[3 * i + 2] = (uint8_t)quant1(p.z, neg);
+        }
+    }
+    if (neg) atomicAdd(n_negative, neg);
 }
 
 __global__ void fill_frame(float4* __restrict__ out, const uint64_t n) {
@@ -194,9 +220,10 @@ cudaError_t launch_trace(const Scene& sc, const Ray* rays, uint64_t n, int accel
     }
 }
 
-cudaError_t launch_quantize(const float4* rgba, uint64_t n, int32_t* rgb, cudaStream_t stream) {
+cudaError_t launch_quantize(const float4* rgba, uint64_t n, uint8_t* rgb, unsigned long long* n_negative, cudaStream_t stream) {
     if (n == 0) return cudaSuccess;
-    quantize_rgb8<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(rgba, n, rgb);
+    const uint64_t groups = (n + 3) / 4;
+    quantize_rgb8<<<(unsigned)((groups + 255) / 256), 256, 0, stream>>>(rgba, n, rgb, n_negative);
     return cudaGetLastError();
 }
 

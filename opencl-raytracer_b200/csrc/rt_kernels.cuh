@@ -43,7 +43,7 @@ struct Frame {
 cudaError_t launch_megakernel(const Scene& sc, const Frame& fr, int accel, bool aov_only, cudaStream_t stream);
 cudaError_t launch_trace(const Scene& sc, const Ray* rays, uint64_t n, int accel, int32_t* hit_id, float* hit_t,
                          Counters* counters, cudaStream_t stream);
-cudaError_t launch_quantize(const float4* rgba, uint64_t n, int32_t* rgb, cudaStream_t stream);
+cudaError_t launch_quantize(const float4* rgba, uint64_t n, uint8_t* rgb, unsigned long long* n_negative, cudaStream_t stream);
 cudaError_t launch_fill(float4* out, uint64_t n, cudaStream_t stream);
 // register-only FFMA loop; returns flops executed through *flops, kernel on `stream`
 cudaError_t launch_fp32_peak(float* sink, int iters, int blocks, int threads, bool packed, cudaStream_t stream);

@@ -60,6 +60,7 @@ CudaRaytracer::CudaRaytracer(const std::vector<ObjectData>& objects, const std::
         check(rt_upload_scene(ctx_, objArr.data(), (uint32_t)objArr.size(), lightArr.data(), (uint32_t)lightArr.size()),
               "rt_upload_scene");
         check(rt_set_rays(ctx_, reinterpret_cast<const rt_ray*>(rays.data()), rays.size()), "rt_set_rays");
+        if (rt_get_camera(ctx_, &camW_, &camH_, &camZ_) != RT_OK) camW_ = camH_ = 0;  // not the pinhole grid: the rays were uploaded
         void* p = nullptr;
         check(rt_host_alloc(&p, rays.size() * sizeof(cl_float4)), "rt_host_alloc");
         pixelDataArr = static_cast<cl_float4*>(p);
@@ -128,6 +129,12 @@ unsigned CudaRaytracer::UseDevices(unsigned n) {
     return n;
 }
 
+void CudaRaytracer::ReuploadRays() {
+    if (!extra_.empty()) UseDevices(1);
+    check(rt_set_rays(ctx_, reinterpret_cast<const rt_ray*>(rays.data()), rays.size()), "rt_set_rays");
+    if (rt_get_camera(ctx_, &camW_, &camH_, &camZ_) != RT_OK) camW_ = camH_ = 0;
+}
+
 bool CudaRaytracer::UseCameraIfPinhole(unsigned width, unsigned height) {
     if ((size_t)width * height != rays.size() || rays.empty()) return false;
     const float zdir = rays[0].direction.z;
@@ -145,6 +152,15 @@ bool CudaRaytracer::UseCameraIfPinhole(unsigned width, unsigned height) {
     camH_ = height;
     camZ_ = zdir;
     return true;
+}
+
+unsigned long long CudaRaytracer::QuantizeRgb8(std::vector<unsigned char>& rgb) const {
+    rgb.resize(3 * rays.size());
+    uint64_t neg = 0;
+    // one device: its framebuffer holds the frame; several: the pieces are on different devices, the host frame is quantised
+    const float* host = extra_.empty() ? nullptr : reinterpret_cast<const float*>(pixelDataArr);
+    check(rt_quantize_rgb8(ctx_, host, rays.size(), rgb.data(), &neg), "rt_quantize_rgb8");
+    return neg;
 }
 
 rt_stats CudaRaytracer::Stats() const {

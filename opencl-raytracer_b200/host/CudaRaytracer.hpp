@@ -36,12 +36,20 @@ public:
     void SetMode(rt_mode mode) { mode_ = mode; }        // default RT_MODE_SHADE_AND_REFLECT (the live kernel)
     void SetAccel(rt_accel accel) { accel_ = accel; }   // default RT_ACCEL_AUTO
     void SetOption(rt_option option, long long value);
-    // If `rays` is exactly the pinhole grid main() builds (OpenCL-Raytracer.cpp:68-72) for width x height, the rays
-    // are generated on the device instead of being uploaded (bit-identical, saves 32 B/ray of HBM and PCIe).
+    // The constructor hands `rays` to rt_set_rays, which recognises the pinhole grid main() builds (OpenCL-Raytracer.cpp:68-72)
+    // and then generates the rays on the device (bit-identical; nothing uploaded; camera grid, bands and lanes apply): the
+    // one-line integration is the fast path.  IsPinhole() tells whether that happened; UseCameraIfPinhole() is the explicit
+    // form (e.g. after SetOption(RT_OPT_DETECT_PINHOLE, 0) was used to force the upload).
+    bool IsPinhole() const { return camW_ != 0; }
     bool UseCameraIfPinhole(unsigned width, unsigned height);
+    void ReuploadRays();  // hand `rays` to rt_set_rays again (after changing RT_OPT_DETECT_PINHOLE)
+    // PPMExporter's quantisation (PPMExporter.cpp:19-21) of the frame of the last Render(), on the device where that frame
+    // still is (one device) -- 3 bytes per pixel come back instead of 16.  Returns the number of negative channels (clamped to
+    // 0; the exporter would print them as negative numbers).
+    unsigned long long QuantizeRgb8(std::vector<unsigned char>& rgb) const;
     // Shard the camera frame over the first n CUDA devices of this process (row-blocks of 16 rows dealt round-robin,
     // SURVEY.md 8(e)): one context and one host thread per device, every device renders its rows and copies them into
-    // the one pinned frame Render() returns.  Needs UseCameraIfPinhole() first; n = 1 undoes it.  Returns the number of
+    // the one pinned frame Render() returns.  Needs the pinhole camera (IsPinhole()); n = 1 undoes it.  Returns the number of
     // devices actually used (at most rt_device_count()).  The reference has no multi-device path.
     unsigned UseDevices(unsigned n);
     rt_stats Stats() const;  // ray counts summed over the devices, times of the slowest device
@@ -52,7 +60,7 @@ private:
     std::vector<rt_ctx*> extra_;  // contexts of devices 1 .. n-1 (UseDevices)
     std::vector<rt_object> objArr_;  // marshalled scene, kept for UseDevices
     std::vector<rt_light> lightArr_;
-    unsigned camW_ = 0, camH_ = 0;
+    uint32_t camW_ = 0, camH_ = 0;
     float camZ_ = 0.f;
     cl_float4* pixelDataArr = nullptr;  // pinned, rays.size() entries
     const unsigned int MAX_BOUNCES;

@@ -12,7 +12,9 @@
 #include <cstdlib>
 #include <cstring>
 #include <iostream>
+#include <algorithm>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "CudaRaytracer.hpp"
@@ -31,7 +33,7 @@ static Ray3D screenSpaceToViewSpace(float width, float height, glm::vec2 pos, fl
 
 static void usage() {
     std::puts("usage: rt_cli --scene file.txt [--width 2560] [--height 1440] [--fov 60] [--bounces 30]\n"
-              "              [--mode hittest|shade|sar] [--accel auto|brute|filter|bvh] [--frames 1]\n"
+              "              [--mode hittest|shade|sar] [--accel auto|brute|filter|bvh|grid] [--frames 1]\n"
               "              [--gpus 1] [--out render.ppm] [--fast-ppm] [--upload-rays]");
 }
 
@@ -68,7 +70,7 @@ int main(int argc, char** argv) {
             mode = m == "hittest" ? RT_MODE_HITTEST : m == "shade" ? RT_MODE_SHADE : RT_MODE_SHADE_AND_REFLECT;
         } else if (a == "--accel") {
             const std::string m = next();
-            accel = m == "brute" ? RT_ACCEL_BRUTE : m == "filter" ? RT_ACCEL_CULL : m == "bvh" ? RT_ACCEL_BVH : RT_ACCEL_AUTO;
+            accel = m == "brute" ? RT_ACCEL_BRUTE : m == "filter" ? RT_ACCEL_CULL : m == "bvh" ? RT_ACCEL_BVH : m == "grid" ? RT_ACCEL_GRID : RT_ACCEL_AUTO;
         } else if (scene.empty() && a[0] != '-') {
             scene = a;  // the reference takes the scene as argv[1] (OpenCL-Raytracer.cpp:47)
         } else {
@@ -101,10 +103,14 @@ int main(int argc, char** argv) {
             rays.emplace_back(screenSpaceToViewSpace((float)width, (float)height, glm::vec2(ii, height - jj), fov));
 
     try {
-        CudaRaytracer tracer(objects, lights, rays, bounces);
+        CudaRaytracer tracer(objects, lights, rays, bounces);  // <- the one line that differs from the reference's main()
         tracer.SetMode(mode);
         tracer.SetAccel(accel);
-        if (!uploadRays && tracer.UseCameraIfPinhole((unsigned)width, (unsigned)height)) {
+        if (uploadRays) {  // force the generic path: the ray vector is uploaded and traced as arbitrary rays
+            tracer.SetOption(RT_OPT_DETECT_PINHOLE, 0);
+            tracer.ReuploadRays();
+        }
+        if (tracer.IsPinhole()) {
             std::cout << "Primary rays are the pinhole grid: generated on the device.\n";
             if (gpus > 1) std::cout << "Frame sharded over " << tracer.UseDevices((unsigned)gpus) << " GPU(s).\n";
         }
@@ -124,23 +130,41 @@ int main(int argc, char** argv) {
         }
         if (!out.empty() && out != "none") {
             const size_t n = (size_t)width * height;
+            std::vector<unsigned char> rgb8;
+            if (fastPpm && tracer.QuantizeRgb8(rgb8) != 0) {
+                std::cout << "Negative colour channels: falling back to PPMExporter::ExportP3.\n";
+                fastPpm = false;
+            }
             if (fastPpm) {
-                // PPMExporter.cpp:19-21 quantisation on the device, one bulk write instead of a flush per pixel
-                std::vector<int32_t> rgb(3 * n);
-                rt_ctx* q = nullptr;
-                if (rt_create(&q, -1) != RT_OK || rt_quantize_rgb8(q, reinterpret_cast<const float*>(pixelData), n, rgb.data()) != RT_OK)
-                    throw std::runtime_error(rt_last_error());
-                rt_destroy(q);
-                std::string text = "P3\n" + std::to_string(width) + " " + std::to_string(height) + "\n255\n";
-                text.reserve(text.size() + n * 12);
-                char buf[48];
-                for (size_t i = 0; i < n; ++i) {
-                    const int len = std::snprintf(buf, sizeof buf, "%d %d %d\n", rgb[3 * i], rgb[3 * i + 1], rgb[3 * i + 2]);
-                    text.append(buf, (size_t)len);
-                }
+                // PPMExporter.cpp:19-21 quantisation ran on the device (3 bytes per pixel came back); the text is formatted by all
+                // host threads, a row range each, and written in one piece instead of a flush per pixel (PPMExporter.cpp:21)
+                static char lut[256][4];
+                static int lutLen[256];
+                for (int v = 0; v < 256; ++v) lutLen[v] = std::snprintf(lut[v], 4, "%d", v);
+                const unsigned nt = std::max(1u, std::min(std::thread::hardware_concurrency(), 32u));
+                std::vector<std::string> part(nt);
+                std::vector<std::thread> pool;
+                for (unsigned t = 0; t < nt; ++t)
+                    pool.emplace_back([&, t] {
+                        const size_t b = n * t / nt, e = n * (t + 1) / nt;
+                        std::string& txt = part[t];
+                        txt.reserve((e - b) * 12);
+                        for (size_t i = b; i < e; ++i) {
+                            const unsigned char* px = &rgb8[3 * i];
+                            txt.append(lut[px[0]], (size_t)lutLen[px[0]]);
+                            txt.push_back(' ');
+                            txt.append(lut[px[1]], (size_t)lutLen[px[1]]);
+                            txt.push_back(' ');
+                            txt.append(lut[px[2]], (size_t)lutLen[px[2]]);
+                            txt.push_back('\n');
+                        }
+                    });
+                for (std::thread& th : pool) th.join();
                 FILE* fp = std::fopen(out.c_str(), "wb");
                 if (!fp) throw std::runtime_error("cannot open " + out);
-                std::fwrite(text.data(), 1, text.size(), fp);
+                const std::string head = "P3\n" + std::to_string(width) + " " + std::to_string(height) + "\n255\n";
+                std::fwrite(head.data(), 1, head.size(), fp);
+                for (const std::string& txt : part) std::fwrite(txt.data(), 1, txt.size(), fp);
                 std::fclose(fp);
             } else {
                 // float4 -> 3 floats per pixel adapter (PPMExporter.cpp:19-21 reads 3, Render() returns 4)

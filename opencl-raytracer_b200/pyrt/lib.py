@@ -15,13 +15,13 @@ _PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 # RT_B200_LIB: an alternative build of the same library (kernel experiments); never a fallback
 LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_PKG, "librt_b200.so")
 
-OPT_PIPELINE, OPT_COUNT_RAYS, OPT_BVH_LEAF, OPT_SKIP_DEAD_RAYS, OPT_READBACK_BANDS, OPT_BVH_BUILDER, OPT_LANES, OPT_GRID_RES, OPT_ZERO_COPY, OPT_GRID3_DENSITY = 1, 2, 3, 4, 5, 6, 7, 8, 9, 10
+OPT_PIPELINE, OPT_COUNT_RAYS, OPT_BVH_LEAF, OPT_SKIP_DEAD_RAYS, OPT_READBACK_BANDS, OPT_BVH_BUILDER, OPT_LANES, OPT_GRID_RES, OPT_ZERO_COPY, OPT_GRID3_DENSITY, OPT_DETECT_PINHOLE = 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11
 ACCEL_AUTO, ACCEL_BRUTE, ACCEL_CULL, ACCEL_BVH, ACCEL_GRID = -1, 0, 1, 2, 3
 
 # every symbol include/rt_b200.h declares (tests check the library exports all of them)
 ABI_SYMBOLS = (
     "rt_last_error", "rt_abi_version", "rt_device_count", "rt_create", "rt_destroy", "rt_set_option", "rt_upload_scene", "rt_set_rays",
-    "rt_set_camera", "rt_set_shard", "rt_render", "rt_render_device", "rt_framebuffer", "rt_render_aov", "rt_trace",
+    "rt_set_camera", "rt_get_camera", "rt_set_shard", "rt_render", "rt_render_device", "rt_framebuffer", "rt_render_aov", "rt_trace",
     "rt_get_stats", "rt_quantize_rgb8", "rt_host_alloc", "rt_host_free", "rt_host_register", "rt_host_unregister", "rt_measure_fp32_peak", "rt_fp32_peak_detail",
     "rt_ipc_export_framebuffer", "rt_ipc_open", "rt_ipc_close", "rt_readback", "rt_host_build_bvh", "rt_plan_bands",
 )
@@ -80,6 +80,7 @@ def load():
             "rt_upload_scene": [vp, vp, u32, vp, u32],
             "rt_set_rays": [vp, vp, u64],
             "rt_set_camera": [vp, u32, u32, C.c_float],
+            "rt_get_camera": [vp, C.POINTER(u32), C.POINTER(u32), C.POINTER(C.c_float)],
             "rt_set_shard": [vp, u32, u32, u32],
             "rt_render": [vp, u32, i32, i32, vp],
             "rt_render_device": [vp, u32, i32, i32, vp],
@@ -88,7 +89,7 @@ def load():
             "rt_render_aov": [vp, i32, vp, vp],
             "rt_trace": [vp, vp, u64, i32, vp, vp],
             "rt_get_stats": [vp, C.POINTER(Stats)],
-            "rt_quantize_rgb8": [vp, vp, u64, vp],
+            "rt_quantize_rgb8": [vp, vp, u64, vp, C.POINTER(u64)],
             "rt_host_alloc": [C.POINTER(vp), u64],
             "rt_host_free": [vp],
             "rt_host_register": [vp, u64],
@@ -293,11 +294,18 @@ class Context:
         _check(load().rt_get_stats(self._h, C.byref(st)))
         return st
 
-    def quantize_rgb8(self, rgba: np.ndarray) -> np.ndarray:
+    def quantize_rgb8(self, rgba: np.ndarray | None = None):
+        """PPMExporter's quantisation on the device -> (uint8 [n, 3], number of negative channels clamped to 0).
+        rgba None: the frame of the last render, straight from the device framebuffer."""
+        neg = C.c_uint64(0)
+        if rgba is None:
+            out = np.empty((self._n, 3), dtype=np.uint8)
+            _check(load().rt_quantize_rgb8(self._h, None, 0, _ptr(out), C.byref(neg)))
+            return out, neg.value
         rgba = np.ascontiguousarray(rgba, dtype=np.float32).reshape(-1, 4)
-        out = np.empty((len(rgba), 3), dtype=np.int32)
-        _check(load().rt_quantize_rgb8(self._h, _ptr(rgba), len(rgba), _ptr(out)))
-        return out
+        out = np.empty((len(rgba), 3), dtype=np.uint8)
+        _check(load().rt_quantize_rgb8(self._h, _ptr(rgba), len(rgba), _ptr(out), C.byref(neg)))
+        return out, neg.value
 
     def measure_fp32_peak(self):
         t, mhz = C.c_float(), C.c_float()

@@ -76,3 +76,24 @@ def test_cli_multi_gpu_equals_single_gpu(rt, tmp_path):
             assert "Frame sharded over %d GPU(s)." % gpus in r.stdout
         outs.append(open(out, "rb").read())
     assert outs[0] == outs[1]
+
+
+@pytest.mark.parametrize("name", ["roundedCube", "simpleScene"])
+def test_fast_ppm_is_byte_identical_to_the_reference_exporter(tmp_path, name):
+    """--fast-ppm (quantisation on the device from the device framebuffer, 3 bytes per pixel back, text
+    formatted by all host threads) writes the very bytes PPMExporter::ExportP3 (PPMExporter.cpp:7-30, compiled unchanged)
+    writes for the same frame -- odd sizes, the unmodified drop-in constructor (pinhole grid recognised) and the uploaded
+    ray vector alike."""
+    scene = os.path.join(ROOT, "baseline", "_ref", name + ".txt")
+    if not (os.path.exists(CLI) and os.path.exists(scene)):
+        pytest.skip("build/rt_cli or the staged scene files are missing")
+    files = []
+    for flags in ([], ["--fast-ppm"], ["--fast-ppm", "--upload-rays"]):
+        out = str(tmp_path / ("r%d.ppm" % len(files)))
+        r = subprocess.run([CLI, "--scene", scene, "--width", "333", "--height", "187", "--bounces", "30", "--out", out] + flags,
+                           capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stdout + r.stderr
+        assert ("generated on the device" in r.stdout) == ("--upload-rays" not in flags)
+        files.append(open(out, "rb").read())
+    assert files[0] == files[1] == files[2]
+    assert files[0].startswith(b"P3\n333 187\n255\n")

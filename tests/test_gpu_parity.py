@@ -109,9 +109,40 @@ def test_camera_rays_equal_host_rays(rt, ctx, oracle_mod):
     ctx.upload_scene(objs, lights)
     ctx.set_camera(W, H, z)
     a = ctx.render(30, 2, 1).copy()
+    ctx.set_option(rt.OPT_DETECT_PINHOLE, 0)  # really upload the host rays
     ctx.set_rays(rays)
     b = ctx.render(30, 2, 1)
     assert np.array_equal(a, b)
+
+
+def test_pinhole_ray_vector_is_recognised(rt, ctx):
+    """rt_set_rays with exactly the ray vector main() builds (OpenCL-Raytracer.cpp:68-72) -- what the unmodified drop-in
+    constructor receives -- switches to device ray generation: camera grid, bands and lanes apply, nothing is uploaded.
+    Any other vector (one ray nudged, a transposed grid, a sub-rectangle) is uploaded as it is."""
+    objs, lights = S.synthetic_scene(3000, 300)
+    W, H = 320, 181
+    z, rays = frame_rays(W, H)
+    ctx.set_option(rt.OPT_COUNT_RAYS, 1)
+    ctx.upload_scene(objs, lights)
+    ctx.set_camera(W, H, z)
+    ref = ctx.render(4, 2, -1).copy()
+    ctx.set_rays(rays)
+    out = ctx.render(4, 2, -1)
+    s = ctx.stats()
+    assert np.array_equal(out, ref) and s.pixels == W * H
+    assert s.pair_tests > 0 and s.node_visits > 0   # camera grid for the primary rays, BVH for the reflection rays
+    nodes_cam = s.node_visits
+    for bad in ("nudge", "sub"):
+        r2 = rays.copy()
+        if bad == "nudge":
+            r2["direction"][W * 7 + 5, 0] += 0.25
+        else:
+            r2 = r2.reshape(H, W)[:, :W - 1].reshape(-1).copy()
+        ctx.set_rays(r2)
+        out2 = ctx.render(4, 2, -1)
+        assert ctx.stats().node_visits > 2 * nodes_cam  # primary rays walked the BVH: the vector was uploaded
+        if bad == "sub":
+            assert np.array_equal(out2.reshape(H, W - 1, 4), ref.reshape(H, W, 4)[:, :W - 1])
 
 
 def test_golden_vectors(rt, ctx):
@@ -375,7 +406,20 @@ def test_quantize_is_byte_identical_to_ppm_rule(rt, ctx):
     rgba = rng.uniform(-0.2, 1.3, size=(50000, 4)).astype(np.float32)
     rgba[:8, :3] = [[0, 1, 0.5], [1 / 255, 2 / 255, 254 / 255], [0.999999, 1.000001, 0.00392156], [76 / 255] * 3,
                     [0.3, 0.375826597, 0.536895216], [255.5 / 255, 3, -1], [1e-9, 0.99607843, 0.99607844], [0.5, 0.25, 0.75]]
-    assert np.array_equal(ctx.quantize_rgb8(rgba), T.quantize_ppm(rgba))
+    q, neg = ctx.quantize_rgb8(rgba)
+    ref = T.quantize_ppm(rgba)
+    assert neg == int((ref < 0).sum()) and neg > 0          # the exporter would print these as negative numbers
+    assert np.array_equal(q, np.maximum(ref, 0).astype(np.uint8))
+    for n in (1, 2, 3, 5, 4099):                            # ragged tails of the four-pixels-per-thread kernel
+        q, _ = ctx.quantize_rgb8(rgba[:n])
+        assert np.array_equal(q, np.maximum(ref[:n], 0).astype(np.uint8))
+    # straight from the device framebuffer of the last render: nothing is uploaded
+    objs, lights = S.load_reference_scene("roundedCube")
+    ctx.upload_scene(objs, lights)
+    ctx.set_camera(333, 77, T.camera_zdir(77))
+    frame = ctx.render(30, 2, -1)
+    q, neg = ctx.quantize_rgb8()
+    assert neg == 0 and np.array_equal(q, T.quantize_ppm(frame).astype(np.uint8))
 
 
 def test_edge_cases(rt, ctx, oracle_mod):
@@ -631,6 +675,7 @@ def test_uniform_grid_walk_equals_bvh(rt, ctx, oracle_mod):
         s = ctx.stats()
         assert_colours_close(out, ref)
         assert (s.rays_primary, s.rays_shadow, s.rays_reflect) == (st.rays_primary, st.rays_shadow, st.rays_reflect)
+        ctx.set_option(rt.OPT_DETECT_PINHOLE, 0)  # caller rays: the primary rays are class B too
         ctx.set_rays(rays)
         assert np.array_equal(ctx.render(4, 2, 3), out)
         gid, gt = ctx.render_aov(3)
