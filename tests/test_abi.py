@@ -24,7 +24,7 @@ def test_library_exports_every_declared_symbol():
     for name in _declared_symbols():
         assert hasattr(dll, name), name
     dll.rt_abi_version.restype = ctypes.c_int
-    assert dll.rt_abi_version() == 1
+    assert dll.rt_abi_version() == 2
 
 
 def test_struct_layouts_match_header():
