@@ -399,6 +399,27 @@ def main():
             c4.render(max_bounces, mode, args.accel, out=host.array)
         cold_ms = (time.perf_counter() - t0) * 1e3
 
+    # dynamic scene: what a re-upload of the whole scene costs when everything per object runs on the device
+    # (RT_OPT_BVH_BUILDER = 1: repack + bounds + Morton tree + grids), and the frame rendered from that tree
+    dynamic = None
+    if rank == 0 and world == 1 and len(objs) >= 2:
+        with lib.Context(local_rank) as c6:
+            c6.set_option(lib.OPT_BVH_BUILDER, 1)
+            c6.set_camera(W, H, zdir)
+            ups, firsts = [], []
+            for _ in range(4):
+                t0 = time.perf_counter()
+                c6.upload_scene(objs, lights)
+                t1 = time.perf_counter()
+                c6.render_device(max_bounces, mode, args.accel)  # rebuilds the grids, then the frame
+                t2 = time.perf_counter()
+                ups.append((t1 - t0) * 1e3)
+                firsts.append((t2 - t1) * 1e3)
+            c6.render_device(max_bounces, mode, args.accel)
+            dynamic = {"upload_ms": float(np.median(ups[1:])), "first_frame_incl_grid_build_ms": float(np.median(firsts[1:])),
+                       "steady_frame_ms": c6.stats().kernel_ms, "builder": "device: rt_bounds.cu + rt_lbvh.cu + rt_pgrid.cu",
+                       "host_builder_upload_ms": upload_ms}
+
     # ------------------------------------------------------------------ roofline of the timed kernel
     peak_tf, peak_mhz = ctx.measure_fp32_peak()
     peak_scalar, peak_packed = ctx.fp32_peak_detail()
@@ -572,6 +593,8 @@ def main():
             out["cpu_baseline"] = cpu
         if parity:
             out["parity"] = parity
+        if dynamic:
+            out["dynamic_scene"] = dynamic
         if ref_ocl:
             out["reference_opencl_gpu"] = ref_ocl
         sys.stdout.flush()

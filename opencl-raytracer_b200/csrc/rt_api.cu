@@ -15,6 +15,7 @@
 
 #include "../../include/rt_b200.h"
 #include "rt_kernels.cuh"
+#include "rt_bounds.cuh"
 #include "rt_lbvh.cuh"
 #include "rt_pgrid_build.cuh"
 #include "rt_scene.hpp"
@@ -83,6 +84,10 @@ struct rt_ctx {
     DevBuf<uint32_t> d_leaf_obj;
     DevBuf<rt::LbvhLeaf> d_lbvh_leaves;  // device tree builder (RT_OPT_BVH_BUILDER = 1): input records and scratch
     DevBuf<char> d_lbvh_scratch;
+    DevBuf<rt_object> d_objs;  // raw AoS scene for the device-side preparation (rt_bounds.cu, RT_OPT_BVH_BUILDER = 1)
+    DevBuf<char> d_bounds_scratch;
+    DevBuf<rt::BoundsGlobals> d_bounds_globals;
+    float last_upload_ms = 0.f;
     rt::Scene scene;
 
     // rays / camera
@@ -162,10 +167,101 @@ uint32_t shard_local_rows(const rt_ctx* c) {  // rows of the local image incl. t
     return owned * br;
 }
 
+void bind_scene(rt_ctx* c, uint32_t n_nodes) {
+    rt::Scene& s = c->scene;
+    s.minv = reinterpret_cast<const float4*>(c->d_minv.p);
+    s.mv = reinterpret_cast<const float4*>(c->d_mv.p);
+    s.mat = reinterpret_cast<const float4*>(c->d_mat.p);
+    s.cull = c->d_cull.p;
+    s.nodes = c->d_nodes.p;
+    s.leaf_obj = c->d_leaf_obj.p;
+    s.leaf_cull = c->d_leaf_cull.p;
+    s.lights = reinterpret_cast<const rt::Light*>(c->d_lights.p);
+    s.n_objs = c->hs.n_objs;
+    s.n_lights = c->hs.n_lights;
+    s.n_nodes = n_nodes;
+    s.root = c->hs.root;
+    s.root_f = c->hs.f_global;
+    s.filter_h = c->hs.h_min;
+    c->scene_dirty = false;
+    c->g_cam.dirty = c->g_lit.dirty = c->g3_dirty = true;
+    c->g_cam.set = c->g_lit.set = rt::GridSet{};
+    c->g3 = rt::Grid3{};
+}
+
+// RT_OPT_BVH_BUILDER = 1: everything per object happens on the device -- repack, bounds (rt_bounds.cu), tree (rt_lbvh.cu).
+// The host uploads the raw AoS array and reads back two small records (the scene radius that fixes the ray-origin bound,
+// then the leaf-centre box and the scene-wide coefficients).
+int sync_scene_device(rt_ctx* c) {
+    const uint32_t n = (uint32_t)c->objs.size(), L = (uint32_t)c->lights.size();
+    RT_CUDA(c->d_objs.upload(c->objs, c->stream));
+    RT_CUDA(c->d_minv.ensure(4 * (size_t)n));
+    RT_CUDA(c->d_mv.ensure(4 * (size_t)n));
+    RT_CUDA(c->d_mat.ensure(3 * (size_t)n));
+    RT_CUDA(c->d_cull.ensure(n));
+    RT_CUDA(c->d_lbvh_leaves.ensure(n));
+    RT_CUDA(c->d_bounds_scratch.ensure(rt::bounds_scratch_bytes(n)));
+    RT_CUDA(c->d_bounds_globals.ensure(1));
+    rt::BoundsGlobals g;
+    rt::bounds_globals_init(&g);
+    RT_CUDA(cudaMemcpyAsync(c->d_bounds_globals.p, &g, sizeof g, cudaMemcpyHostToDevice, c->stream));
+    RT_CUDA(rt::bounds_pass1_launch(c->d_objs.p, n, reinterpret_cast<float4*>(c->d_minv.p), reinterpret_cast<float4*>(c->d_mv.p),
+                                    reinterpret_cast<float4*>(c->d_mat.p), c->d_bounds_scratch.p, c->d_bounds_globals.p, c->stream));
+    auto bad = [&](const rt::BoundsGlobals& gg) -> int {
+        if (gg.first_bad == ~0ull) return RT_OK;
+        static const char* what[] = {"", "non-finite matrix", "projective (non-affine) matrices are outside the supported domain", "singular mvInverse",
+                                     "degenerate transform", "anisotropy too extreme for conservative bounds"};
+        const unsigned code = (unsigned)(gg.first_bad & 0xffu);
+        return fail(RT_ERR_UNSUPPORTED, "object " + std::to_string(gg.first_bad >> 8) + ": " + what[code < 6 ? code : 0]);
+    };
+    RT_CUDA(cudaMemcpyAsync(&g, c->d_bounds_globals.p, sizeof g, cudaMemcpyDeviceToHost, c->stream));
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    int rc = bad(g);
+    if (rc != RT_OK) return rc;
+    const double omax = std::max(1.05 * g.r0 + 1.0, (double)c->omax_user * 1.0001 + 1e-3);  // rt_scene.cpp
+    RT_CUDA(rt::bounds_pass2_launch(c->d_objs.p, n, c->d_bounds_scratch.p, omax, c->d_cull.p, c->d_lbvh_leaves.p, c->d_bounds_globals.p, c->stream));
+    RT_CUDA(cudaMemcpyAsync(&g, c->d_bounds_globals.p, sizeof g, cudaMemcpyDeviceToHost, c->stream));
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    rc = bad(g);
+    if (rc != RT_OK) return rc;
+    c->hs = rt::HostScene();
+    c->hs.n_objs = n;
+    c->hs.n_lights = L;
+    c->hs.omax = (float)omax;
+    c->hs.scene_radius = (float)g.r0;
+    c->hs.h_min = g.h_min;
+    c->hs.f_global = g.f_max;
+    c->hs.root = 0;
+    c->hs.lights.resize(4 * (size_t)L);
+    for (uint32_t i = 0; i < L; ++i) {
+        const rt_light& l = c->lights[i];
+        c->hs.lights[4 * i + 0] = rt::F4{l.ambient[0], l.ambient[1], l.ambient[2], 0.f};
+        c->hs.lights[4 * i + 1] = rt::F4{l.diffuse[0], l.diffuse[1], l.diffuse[2], 0.f};
+        c->hs.lights[4 * i + 2] = rt::F4{l.specular[0], l.specular[1], l.specular[2], 0.f};
+        c->hs.lights[4 * i + 3] = rt::F4{l.position[0], l.position[1], l.position[2], l.position[3]};
+    }
+    RT_CUDA(c->d_lights.upload(c->hs.lights, c->stream));
+    for (int k = 0; k < 3; ++k) {
+        c->hs.lbvh_lo[k] = rt::bounds_decode_ordered(g.lo[k]);
+        c->hs.lbvh_hi[k] = rt::bounds_decode_ordered(g.hi[k]);
+    }
+    const size_t sb = rt::lbvh_scratch_bytes(n);
+    RT_CUDA(c->d_lbvh_scratch.ensure(sb));
+    RT_CUDA(c->d_nodes.ensure(n - 1));
+    RT_CUDA(c->d_leaf_obj.ensure(n));
+    RT_CUDA(c->d_leaf_cull.ensure(n));
+    RT_CUDA(rt::build_lbvh_device(c->d_lbvh_leaves.p, n, c->d_cull.p, c->hs.lbvh_lo, c->hs.lbvh_hi, c->hs.omax, c->d_lbvh_scratch.p, sb, c->d_nodes.p,
+                                  c->d_leaf_obj.p, c->d_leaf_cull.p, c->stream));
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    bind_scene(c, n - 1);
+    return RT_OK;
+}
+
 int sync_scene(rt_ctx* c) {
     if (!c->have_scene) return fail(RT_ERR_INVALID, "rt_upload_scene has not been called");
     const float need_omax = c->use_camera ? 0.f : c->omax_user;
     if (!c->scene_dirty && need_omax <= c->hs.omax) return RT_OK;
+    if (c->opt_builder == 1 && c->objs.size() >= 2 && c->objs.size() < (1u << 27)) return sync_scene_device(c);
     std::string err;
     const int rc = rt::build_scene(c->objs.data(), (uint32_t)c->objs.size(), c->lights.data(), (uint32_t)c->lights.size(),
                                    c->omax_user, c->opt_builder == 1 ? 0 : c->opt_leaf, c->hs, err);
@@ -194,25 +290,7 @@ int sync_scene(rt_ctx* c) {
         RT_CUDA(c->d_leaf_obj.upload(c->hs.leaf_obj, c->stream));
     }
     RT_CUDA(cudaStreamSynchronize(c->stream));
-    rt::Scene& s = c->scene;
-    s.minv = reinterpret_cast<const float4*>(c->d_minv.p);
-    s.mv = reinterpret_cast<const float4*>(c->d_mv.p);
-    s.mat = reinterpret_cast<const float4*>(c->d_mat.p);
-    s.cull = c->d_cull.p;
-    s.nodes = c->d_nodes.p;
-    s.leaf_obj = c->d_leaf_obj.p;
-    s.leaf_cull = c->d_leaf_cull.p;
-    s.lights = reinterpret_cast<const rt::Light*>(c->d_lights.p);
-    s.n_objs = c->hs.n_objs;
-    s.n_lights = c->hs.n_lights;
-    s.n_nodes = n_nodes;
-    s.root = c->hs.root;
-    s.root_f = c->hs.f_global;
-    s.filter_h = c->hs.h_min;
-    c->scene_dirty = false;
-    c->g_cam.dirty = c->g_lit.dirty = c->g3_dirty = true;
-    c->g_cam.set = c->g_lit.set = rt::GridSet{};
-    c->g3 = rt::Grid3{};
+    bind_scene(c, n_nodes);
     return RT_OK;
 }
 
@@ -269,7 +347,7 @@ int build_grid3(rt_ctx* c) {
     c->g3_dirty = false;
     c->g3_n_entries = 0;
     const uint32_t n_objs = c->hs.n_objs;
-    if (c->opt_grid3 <= 0 || n_objs < 64) return RT_OK;
+    if (c->opt_grid3 <= 0 || n_objs < 64 || c->hs.cull.size() < n_objs) return RT_OK;  // (a device-prepared scene has no host records)
     const float ext0 = 2.f * c->hs.scene_radius + 1.f;
     const float eps = 2e-5f * ext0 + 1e-4f;
     double lo[3] = {1e30, 1e30, 1e30}, hi[3] = {-1e30, -1e30, -1e30}, rsum = 0;
@@ -814,6 +892,7 @@ int rt_destroy(rt_ctx* c) {
     cudaStreamSynchronize(c->stream);
     c->d_minv.release(); c->d_mv.release(); c->d_mat.release(); c->d_lights.release();
     c->d_cull.release(); c->d_leaf_cull.release(); c->d_nodes.release(); c->d_lbvh_leaves.release(); c->d_lbvh_scratch.release(); c->d_leaf_obj.release();
+    c->d_objs.release(); c->d_bounds_scratch.release(); c->d_bounds_globals.release();
     c->d_rays.release(); c->d_fb.release(); c->d_hit_id.release(); c->d_hit_t.release(); c->d_counters.release();
     c->d_sink.release();
     c->g_cam.grids.release(); c->g_cam.cell_start.release(); c->g_cam.entries.release();
@@ -889,7 +968,10 @@ int rt_upload_scene(rt_ctx* c, const rt_object* objs, uint32_t n_objs, const rt_
     c->lights.assign(lights, lights + n_lights);
     c->have_scene = true;
     c->scene_dirty = true;
-    return sync_scene(c);
+    const auto t0 = std::chrono::steady_clock::now();
+    const int rc = sync_scene(c);
+    c->last_upload_ms = (float)std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return rc;
 }
 
 int rt_set_rays(rt_ctx* c, const rt_ray* host_rays, uint64_t n) {

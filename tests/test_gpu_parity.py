@@ -685,3 +685,59 @@ def test_uniform_grid_walk_equals_bvh(rt, ctx, oracle_mod):
     ctx.set_rays(rr)
     gid, gt = ctx.render_aov(3)
     assert np.array_equal(gid, rid) and np.array_equal(gt, rtt)
+
+
+def test_scene_that_changes_every_frame(rt, oracle_mod):
+    """RT_OPT_BVH_BUILDER = 1 prepares the scene on the device -- repack, per-object bounds (rt_bounds.cu), tree
+    (rt_lbvh.cu), grids (rt_pgrid.cu).  Objects move between frames; every frame must equal, bit for bit, the frame of a fresh
+    context that prepared the same scene on the host (binned SAH), and the first one the oracle."""
+    objs, lights = S.synthetic_scene(6000, 500, n_lights=2)
+    W, H = 192, 108
+    z, rays = frame_rays(W, H)
+    rng = np.random.Generator(np.random.PCG64(3))
+    with rt.Context(0) as dyn:
+        dyn.set_option(rt.OPT_BVH_BUILDER, 1)
+        dyn.set_camera(W, H, z)
+        for frame in range(4):
+            if frame:
+                # rigid motion of a third of the objects: mv' = T(d) mv, mvInverse' = mvInverse T(-d)
+                mv = objs["mv"].reshape(-1, 4, 4).copy()
+                mi = objs["mvInverse"].reshape(-1, 4, 4).copy()
+                sel = rng.random(len(objs)) < 0.33
+                d = (rng.normal(size=(len(objs), 3)) * 0.7).astype(np.float32)
+                d[~sel] = 0
+                mv[:, 3, :3] += d
+                mi[:, 3, :3] -= np.einsum("nkj,nk->nj", mi[:, :3, :3], d)
+                objs = objs.copy()
+                objs["mv"], objs["mvInverse"] = mv.reshape(-1, 16), mi.reshape(-1, 16)
+            dyn.upload_scene(objs, lights)
+            for pipeline in (1, 0):
+                dyn.set_option(rt.OPT_PIPELINE, pipeline)
+                got = dyn.render(4, 2, -1).copy()
+                with rt.Context(0) as fresh:
+                    fresh.set_option(rt.OPT_PIPELINE, pipeline)
+                    fresh.upload_scene(objs, lights)
+                    fresh.set_camera(W, H, z)
+                    assert np.array_equal(got, fresh.render(4, 2, -1))
+            if frame == 0:
+                ref, *_ = oracle_mod.port_render(2, 4, objs, lights, rays)
+                assert_colours_close(got, ref)
+        # the device path rejects what the host path rejects, naming the object
+        bad = objs.copy()
+        bad[77]["mvInverse"][7] = 0.5
+        with pytest.raises(rt.RtError) as e:
+            dyn.upload_scene(bad, lights)
+        assert e.value.code == -4 and "object 77" in str(e.value)
+        bad = objs.copy()
+        bad[5]["mvInverse"][:] = 0
+        bad[5]["mvInverse"][15] = 1
+        with pytest.raises(rt.RtError) as e:
+            dyn.upload_scene(bad, lights)
+        assert e.value.code == -4 and "object 5" in str(e.value)
+        unknown = objs.copy()
+        unknown["type"][::3] = 9  # types the kernels' switch skips: leaves that are never hit
+        dyn.upload_scene(unknown, lights)
+        with rt.Context(0) as fresh:
+            fresh.upload_scene(unknown, lights)
+            fresh.set_camera(W, H, z)
+            assert np.array_equal(dyn.render(4, 2, -1), fresh.render(4, 2, -1))
