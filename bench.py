@@ -206,6 +206,7 @@ def main():
     ap.add_argument("--grid3", type=int, default=-1, help="uniform 3-D grid for rays without an apex: cells per 100 objects (0 = BVH, -1 = library default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-brute-leg", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the per-frame numbers of BASELINE.json's configs 1-4")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -398,6 +399,59 @@ def main():
             c4.set_camera(W, H, zdir)
             c4.render(max_bounces, mode, args.accel, out=host.array)
         cold_ms = (time.perf_counter() - t0) * 1e3
+
+    # ------------------------------------------------------------------ BASELINE.json's configs 1-4 (the reference's own scenes)
+    # Parity-test cases, not the headline -- but their numbers belong in front of the driver too: kernel and end-to-end time
+    # per frame, the framebuffer store rate against the HBM peak (these frames are store / PCIe bound), and the unchanged
+    # reference .cl on this same GPU where the box has an OpenCL platform.
+    small = None
+    if rank == 0 and world == 1 and args.workload == "cfg5-box" and not args.no_configs:
+        small = []
+        try:
+            import oracle
+            ocl_ok, _ = oracle.ocl_probe()
+        except Exception:
+            ocl_ok = False
+        for name in ("cfg1", "cfg2", "cfg3", "cfg3-shade", "cfg4", "cfg4-3l"):
+            o2, l2, w2, h2, mb2, mode2, label2 = workload(name, args)
+            z2 = types.camera_zdir(h2)
+            buf = lib.PinnedBuffer((w2 * h2, 4))
+            with lib.Context(local_rank) as c7:
+                c7.upload_scene(o2, l2)
+                c7.set_camera(w2, h2, z2)
+                c7.set_option(lib.OPT_COUNT_RAYS, 1)
+                c7.render_device(mb2, mode2, -1)
+                s7 = c7.stats()
+                c7.set_option(lib.OPT_COUNT_RAYS, 0)
+                ks, es = [], []
+                for i in range(8):
+                    flush.zero_()
+                    torch.cuda.synchronize()
+                    c7.render_device(mb2, mode2, -1)
+                    ks.append(c7.stats().kernel_ms)
+                for i in range(8):
+                    flush.zero_()
+                    torch.cuda.synchronize()
+                    t0 = time.perf_counter()
+                    c7.render(mb2, mode2, -1, out=buf.array)
+                    es.append((time.perf_counter() - t0) * 1e3)
+                k_ms, e_ms = float(np.median(ks[3:])), float(np.median(es[3:]))
+                entry = {"config": name, "workload": label2, "rays_traced": s7.rays_traced, "rays_reference": s7.rays_reference,
+                         "kernel_ms": k_ms, "e2e_ms": e_ms, "mrays_per_s_kernel": s7.rays_traced / (k_ms * 1e-3) / 1e6,
+                         "mrays_per_s_e2e": s7.rays_traced / (e_ms * 1e-3) / 1e6,
+                         "framebuffer_store_gbs": w2 * h2 * 16 / (k_ms * 1e-3) / 1e9,
+                         "accel": ["brute", "filter", "bvh", "grids"][s7.accel_used], "pipeline": ["megakernel", "wavefront"][s7.pipeline_used]}
+            if ocl_ok:
+                try:
+                    rays2 = types.camera_rays(w2, h2, z2)
+                    _, tm = oracle.ocl_render(mode2 if mode2 in (1, 2) else 2, mb2, o2, l2, rays2, frames=3)
+                    entry["reference_opencl_gpu"] = {"kernel_ms": tm["kernel_ms"], "render_ms": tm["render_ms"],
+                                                     "kernel_speedup": tm["kernel_ms"] / k_ms, "render_speedup": tm["render_ms"] / e_ms}
+                    del rays2
+                except Exception as e:
+                    entry["reference_opencl_gpu"] = {"unavailable": "error: %s" % e}
+            buf.close()
+            small.append(entry)
 
     # dynamic scene: what a re-upload of the whole scene costs when everything per object runs on the device
     # (RT_OPT_BVH_BUILDER = 1: repack + bounds + Morton tree + grids), and the frame rendered from that tree
@@ -595,6 +649,8 @@ def main():
             out["parity"] = parity
         if dynamic:
             out["dynamic_scene"] = dynamic
+        if small:
+            out["configs"] = small
         if ref_ocl:
             out["reference_opencl_gpu"] = ref_ocl
         sys.stdout.flush()

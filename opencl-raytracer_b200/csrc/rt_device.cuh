@@ -282,6 +282,19 @@ __device__ __forceinline__ bool sphere_may_hit(const RayK& k, float cx, float cy
     return !(lhs > r2);
 }
 
+// The same test without normalising the direction (no square root, no division per ray): with dd = |d|^2 both sides are
+// scaled by dd,  h |oc|^2 dd - (oc.d)^2 > r2 dd.  Used where a ray meets only a handful of objects (the reference's own
+// scenes: 1-9 objects), so that per-ray set-up does not outweigh the tests.  The extra roundings (two products per object)
+// are inside the 24 u of slack g carries for the filter's own arithmetic (rt_scene.cpp).
+__device__ __forceinline__ bool sphere_may_hit_raw(float ox, float oy, float oz, float dx, float dy, float dz, float dd, float cx, float cy, float cz,
+                                                   float r2, float h) {
+    const float x = cx - ox, y = cy - oy, z = cz - oz;
+    const float oc2 = fmaf(z, z, fmaf(y, y, x * x));
+    const float dt = fmaf(z, dz, fmaf(y, dy, x * dx));
+    const float lhs = fmaf(-dt, dt, oc2 * (h * dd));
+    return !(lhs > r2 * dd);
+}
+
 // Slab test of one child box against [0, tlimit].  The box (centre c, half extent e) has to be inflated by
 // f * d_far, d_far = distance from the ray origin to the farthest point of the box: every object centre of the subtree
 // lies in the box, so |oc| <= d_far and f * d_far bounds the noise term of each object (rt_scene.cpp).  d_far is
@@ -352,13 +365,13 @@ __device__ __forceinline__ Hit trace_cull(const Scene& sc, const Ray& ray, unsig
     h.t = RT_MAX_FLOAT;
     h.id = -1;
     uint32_t ktype = 0;
-    const cv::RayK rk = cv::prepare(ray);
+    const float dd = fmaf(ray.d.z, ray.d.z, fmaf(ray.d.y, ray.d.y, ray.d.x * ray.d.x));
     const float4* cr = reinterpret_cast<const float4*>(sc.cull);
     unsigned long long ne = 0;
     for (uint32_t k = 0; k < sc.n_objs; ++k) {
         const float4 a = __ldg(cr + 2 * (size_t)k);
         const float4 b = __ldg(cr + 2 * (size_t)k + 1);
-        if (cv::sphere_may_hit(rk, a.x, a.y, a.z, a.w, b.x)) {
+        if (cv::sphere_may_hit_raw(ray.s.x, ray.s.y, ray.s.z, ray.d.x, ray.d.y, ray.d.z, dd, a.x, a.y, a.z, a.w, b.x)) {
             exact_pair(sc, ray, k, __float_as_uint(b.w), h, ktype);
             ++ne;
         }

@@ -40,16 +40,17 @@ __device__ void flush_counters(const LocalCounters& lc, Counters* c) {
 }
 
 __device__ __forceinline__ bool locate_pixel(const Frame& fr, uint32_t& ii, uint32_t& jj, uint64_t& out_index) {
-    const uint32_t tiles_x = (fr.width + kTileW - 1) / kTileW;
-    const uint32_t tile = blockIdx.x;
-    const uint32_t tx = tile % tiles_x, ty = tile / tiles_x;
+    const uint32_t tx = blockIdx.x, ty = blockIdx.y;  // 2-D launch grid of 32 x 8 pixel tiles: no division per thread
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
     // each warp covers an 8 x 4 patch: neighbouring rays share BVH nodes and filter survivors
     const uint32_t lx = tx * kTileW + (warp & 3u) * 8u + (lane & 7u);
     const uint32_t ly = ty * kTileH + (warp >> 2) * 4u + (lane >> 3);
     if (lx >= fr.width || ly >= fr.local_rows) return false;
-    const uint32_t blk = ly / fr.block_rows, rib = ly % fr.block_rows;
-    const uint32_t row = fr.row0 + (blk * fr.n_shards + fr.shard) * fr.block_rows + rib;
+    uint32_t row = fr.row0 + ly;
+    if (fr.n_shards > 1u) {
+        const uint32_t blk = ly / fr.block_rows, rib = ly % fr.block_rows;
+        row = fr.row0 + (blk * fr.n_shards + fr.shard) * fr.block_rows + rib;
+    }
     if (row >= fr.height) return false;
     ii = lx;
     jj = row;
@@ -174,14 +175,15 @@ __global__ void __launch_bounds__(256) fp32_peak_packed(float* sink, const int i
 
 template <int ACCEL>
 cudaError_t launch_mega_t(const Scene& sc, const Frame& fr, bool aov_only, cudaStream_t stream) {
-    unsigned grid;
+    dim3 grid;
     if (fr.rays) {
-        grid = (unsigned)((fr.n_local + kBlock - 1) / kBlock);
+        grid = dim3((unsigned)((fr.n_local + kBlock - 1) / kBlock), 1, 1);
     } else {
         const uint32_t tiles_x = (fr.width + kTileW - 1) / kTileW, tiles_y = (fr.local_rows + kTileH - 1) / kTileH;
-        grid = tiles_x * tiles_y;
+        if (tiles_y > 65535u) return cudaErrorInvalidConfiguration;
+        grid = dim3(tiles_x, tiles_y, 1);
     }
-    if (grid == 0) return cudaSuccess;
+    if (grid.x == 0 || grid.y == 0) return cudaSuccess;
     if (fr.counters)
         render_mega<ACCEL, true><<<grid, kBlock, 0, stream>>>(sc, fr, aov_only ? 1 : 0);
     else

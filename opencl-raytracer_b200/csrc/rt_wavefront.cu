@@ -705,6 +705,58 @@ __global__ void __launch_bounds__(kBlock) wave_trace_brute(const Scene sc, const
 // results of its own rays (ex::replaces is order independent, so the merge order does not matter).
 constexpr float kExpandPad = 4.7684e-06f;  // 80 u
 
+// ---- TMA (bulk async copy) + mbarrier plumbing of the tile pipeline.  The filter records are packed ONCE per scene, in the
+// layout the hot loop reads ({cx,cx,cy,cy} {cz,cz,e',e'}: every value twice, so that the packed FFMA2 gets its broadcast operand
+// as an aligned register pair), padded to whole tiles; a tile is then one contiguous 32 KB chunk that a single thread moves
+// with cp.async.bulk (UBLKCP in SASS) into one of two shared-memory buffers while the block still computes on the other.
+// full[b] completes when the bytes of buffer b have landed (complete_tx), empty[b] when every warp has finished reading it.
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "LAB_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra DONE;\n"
+        "bra LAB_WAIT;\n"
+        "DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_copy_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)), "l"(src_gmem),
+                 "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+// Packs the filter records of the scene into the tile layout (2 float4 per object, n_pad objects, n_pad a multiple of the
+// tile): e' = h_min |c|^2 - r2 - pad folds the scene-wide smallest h; r2 < 0 ("never hit") and the padding get e' = +inf.
+__global__ void filter_pack_tiles(const CullRec* __restrict__ cull, const uint32_t n_objs, const uint32_t n_pad, const float hmin,
+                                  float4* __restrict__ out) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_pad) return;
+    const float inf = __int_as_float(0x7f800000);
+    float4 a = make_float4(0.f, 0.f, 0.f, -1.f), b = make_float4(1.f, 0.f, 0.f, 0.f);
+    if (j < n_objs) {
+        const float4* c4 = reinterpret_cast<const float4*>(cull);
+        a = __ldg(c4 + 2 * (size_t)j);      // cx cy cz r2
+        b = __ldg(c4 + 2 * (size_t)j + 1);  // h cc e0 type
+    }
+    const float e = a.w < 0.f ? inf : -fmaf(-hmin, b.y, fmaf(kExpandPad, b.y, a.w));
+    out[2 * (size_t)j] = make_float4(a.x, a.x, a.y, a.y);
+    out[2 * (size_t)j + 1] = make_float4(a.z, a.z, e, e);
+}
+
 template <int CAP>     // CAP: per warp, 31 left over + (rays per thread x 32 lanes) of one object
 struct FilterShared {  // static part; the tile is dynamic shared memory
     uint32_t cand_obj[kBlock / 32][CAP];
@@ -806,32 +858,52 @@ __device__ __noinline__ uint32_t filter_collect(const Scene& sc, const TaskQueue
 #define RT_FILTER_RPT 4
 #define RT_FILTER_OPI 4
 #define RT_FILTER_MINB 2
-#define RT_FILTER_TILE 2048
+#define RT_FILTER_TILE 1024  // two buffers of 32 KB per block
 #endif
 // RPT rays per thread (even), OPI objects per loop iteration (independent FMA chains for latency hiding), MINB resident
 // blocks per SM, TILE objects per shared-memory tile.
 template <int RPT, int OPI, int MINB, int TILE, bool COUNT>
 __global__ void __launch_bounds__(kBlock, MINB) wave_trace_filter(const Scene sc, const TaskQueue q, const uint32_t* __restrict__ n_ptr,
                                                                   const uint32_t n_min, const uint32_t n_max, float* __restrict__ res_t,
-                                                                  int32_t* __restrict__ res_id, Counters* ctr) {
+                                                                  int32_t* __restrict__ res_id, const float4* __restrict__ packed, Counters* ctr) {
     static_assert(RPT % 2 == 0 && RPT <= 8, "rays come in pairs; the ray slot is packed into 3 bits");
     static_assert(TILE % OPI == 0, "tile is a whole number of iterations");
     constexpr int P = RPT / 2;
     constexpr int CAP = 32 + RPT * 32;  // 31 left over + every ray of the warp on one object
     const uint32_t n = *n_ptr;
     if (n == 0u || n < n_min || n >= n_max) return;  // the other instantiation handles this queue size
-    extern __shared__ float4 tile[];                 // 2 per object: {cx, cx, cy, cy} {cz, cz, e', e'}
+    extern __shared__ __align__(128) float4 tiles[];  // 2 buffers x TILE objects x 2 float4: {cx, cx, cy, cy} {cz, cz, e', e'}
+    __shared__ __align__(8) uint64_t bar_full[2], bar_empty[2];
     __shared__ float best_t[RPT][kBlock];
     __shared__ int32_t best_i[RPT][kBlock];
     __shared__ FilterShared<CAP> fs;
     LocalCounters lc;
     const uint32_t M = sc.n_objs;
     const float hmin = sc.filter_h;
-    const float4* cull4 = reinterpret_cast<const float4*>(sc.cull);
     const uint32_t per_block = kBlock * RPT;
     const uint32_t n_groups = (n + per_block - 1) / per_block;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const float inf = __int_as_float(0x7f800000);
+    const uint32_t n_tiles = (M + TILE - 1) / TILE;
+    constexpr uint32_t kTileBytes = TILE * 2 * sizeof(float4);
+    // tile pipeline: `it` counts the tiles this block has consumed (over all its ray groups -- every group walks the same
+    // tile sequence, so the copy of the next tile is always known); tile `it` lives in buffer it & 1, fill number it >> 1
+    const uint32_t my_groups = blockIdx.x < n_groups ? (n_groups - blockIdx.x + gridDim.x - 1) / gridDim.x : 0u;
+    const uint64_t total_tiles = (uint64_t)my_groups * n_tiles;
+    uint64_t it = 0;
+    if (tid == 0) {
+        mbar_init(&bar_full[0], 1);
+        mbar_init(&bar_full[1], 1);
+        mbar_init(&bar_empty[0], kBlock / 32);
+        mbar_init(&bar_empty[1], kBlock / 32);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+    if (tid == 0 && total_tiles > 0) {  // prologue: tile 0 into buffer 0
+        mbar_expect_tx(&bar_full[0], kTileBytes);
+        bulk_copy_g2s(tiles, packed, kTileBytes, &bar_full[0]);
+    }
 
     for (uint32_t g = blockIdx.x; g < n_groups; g += gridDim.x) {
         float2 UX[P], UY[P], UZ[P], NQ[P], PX[P], PY[P], PZ[P], OO[P];
@@ -870,22 +942,21 @@ __global__ void __launch_bounds__(kBlock, MINB) wave_trace_filter(const Scene sc
                 PX[r / 2].x = px; PY[r / 2].x = py; PZ[r / 2].x = pz; OO[r / 2].x = oo;
             }
         }
-        for (uint32_t t0 = 0; t0 < M; t0 += TILE) {
+        for (uint32_t t0 = 0; t0 < M; t0 += TILE, ++it) {
             const uint32_t cnt = min((uint32_t)TILE, M - t0);
             const uint32_t cnt_pad = (cnt + OPI - 1) / OPI * OPI;
-            __syncthreads();
-            for (uint32_t j = tid; j < cnt_pad; j += kBlock) {
-                float4 a = make_float4(0.f, 0.f, 0.f, -1.f), b = make_float4(1.f, 0.f, 0.f, 0.f);
-                if (j < cnt) {
-                    a = __ldg(cull4 + 2 * (size_t)(t0 + j));      // cx cy cz r2
-                    b = __ldg(cull4 + 2 * (size_t)(t0 + j) + 1);  // h cc e0 type
-                }
-                // r2 < 0 marks "never hit" (and the padding of the last iteration): e' = +inf rejects every finite l
-                const float e = a.w < 0.f ? inf : -fmaf(-hmin, b.y, fmaf(kExpandPad, b.y, a.w));
-                tile[2 * j] = make_float4(a.x, a.x, a.y, a.y);
-                tile[2 * j + 1] = make_float4(a.z, a.z, e, e);
+            const uint32_t buf = (uint32_t)(it & 1u);
+            if (tid == 0 && it + 1 < total_tiles) {
+                // next tile into the other buffer, once every warp has left that buffer's previous contents (fill (it+1)>>1 needs
+                // the consumption of fill ((it+1)>>1) - 1 to be complete)
+                const uint64_t nx = it + 1;
+                const uint32_t nb = (uint32_t)(nx & 1u);
+                if (nx >= 2) mbar_wait(&bar_empty[nb], (uint32_t)(((nx >> 1) - 1) & 1u));
+                mbar_expect_tx(&bar_full[nb], kTileBytes);
+                bulk_copy_g2s(tiles + (size_t)nb * TILE * 2, packed + 2 * (size_t)((uint32_t)(nx % n_tiles) * TILE), kTileBytes, &bar_full[nb]);
             }
-            __syncthreads();
+            mbar_wait(&bar_full[buf], (uint32_t)((it >> 1) & 1u));  // the bytes of this tile have landed
+            const float4* tile = tiles + (size_t)buf * TILE * 2;
             for (uint32_t j = 0; j < cnt_pad;) {
                 float2 l[OPI][P];
                 float thr[OPI];
@@ -929,6 +1000,8 @@ __global__ void __launch_bounds__(kBlock, MINB) wave_trace_filter(const Scene sc
                     if (COUNT) lc.exact_tests += batches;
                 }
             }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bar_empty[buf]);  // this warp is done with the buffer
         }
         {  // the remainder of the list
             __syncwarp();
@@ -953,11 +1026,12 @@ __global__ void __launch_bounds__(kBlock, MINB) wave_trace_filter(const Scene sc
 
 // One configuration of the filter kernel: launches the big-queue and the small-queue instantiation.
 template <int RPT, int OPI, int MINB, int TILE>
-cudaError_t launch_filter(const Scene& sc, const TaskQueue& qin, const uint32_t* n_ptr, float* res_t, int32_t* res_id, Counters* ctr,
-                          bool count, int sm_count, cudaStream_t stream) {
+cudaError_t launch_filter(const Scene& sc, const TaskQueue& qin, const uint32_t* n_ptr, float* res_t, int32_t* res_id, const float4* packed,
+                          Counters* ctr, bool count, int sm_count, cudaStream_t stream) {
     const unsigned fgrid = (unsigned)sm_count * MINB;
     const uint32_t split = fgrid * kBlock * RPT;
-    const int bytes = TILE * 2 * (int)sizeof(float4);
+    const int bytes = 2 * TILE * 2 * (int)sizeof(float4);  // two buffers
+    if (!packed) return cudaErrorInvalidValue;
     {  // 64 KB of dynamic shared memory need the opt-in, and function attributes are per DEVICE: one process may drive
        // several GPUs (CudaRaytracer::UseDevices), so the opt-in is made once for every device that launches the kernel
         static bool done[64] = {};
@@ -975,11 +1049,11 @@ cudaError_t launch_filter(const Scene& sc, const TaskQueue& qin, const uint32_t*
     }
     // two instantiations, each takes the queue sizes it is efficient for (the size lives on the device)
     if (count) {
-        wave_trace_filter<RPT, OPI, MINB, TILE, true><<<fgrid, kBlock, bytes, stream>>>(sc, qin, n_ptr, split, 0xffffffffu, res_t, res_id, ctr);
-        wave_trace_filter<2, 1, MINB, TILE, true><<<fgrid, kBlock, bytes, stream>>>(sc, qin, n_ptr, 0u, split, res_t, res_id, ctr);
+        wave_trace_filter<RPT, OPI, MINB, TILE, true><<<fgrid, kBlock, bytes, stream>>>(sc, qin, n_ptr, split, 0xffffffffu, res_t, res_id, packed, ctr);
+        wave_trace_filter<2, 1, MINB, TILE, true><<<fgrid, kBlock, bytes, stream>>>(sc, qin, n_ptr, 0u, split, res_t, res_id, packed, ctr);
     } else {
-        wave_trace_filter<RPT, OPI, MINB, TILE, false><<<fgrid, kBlock, bytes, stream>>>(sc, qin, n_ptr, split, 0xffffffffu, res_t, res_id, ctr);
-        wave_trace_filter<2, 1, MINB, TILE, false><<<fgrid, kBlock, bytes, stream>>>(sc, qin, n_ptr, 0u, split, res_t, res_id, ctr);
+        wave_trace_filter<RPT, OPI, MINB, TILE, false><<<fgrid, kBlock, bytes, stream>>>(sc, qin, n_ptr, split, 0xffffffffu, res_t, res_id, packed, ctr);
+        wave_trace_filter<2, 1, MINB, TILE, false><<<fgrid, kBlock, bytes, stream>>>(sc, qin, n_ptr, 0u, split, res_t, res_id, packed, ctr);
     }
     return cudaGetLastError();
 }
@@ -1054,6 +1128,14 @@ uint32_t wave_max_generations(uint32_t max_bounces, uint32_t n_lights, int mode)
 static int env_int(const char* name, int dflt) {
     const char* v = getenv(name);
     return v && *v ? atoi(v) : dflt;
+}
+
+uint32_t wave_filter_tile_pad(uint32_t n_objs) { return (n_objs + RT_FILTER_TILE - 1) / RT_FILTER_TILE * RT_FILTER_TILE; }
+
+cudaError_t wave_pack_filter_tiles(const Scene& sc, float4* out, cudaStream_t stream) {
+    const uint32_t n_pad = wave_filter_tile_pad(sc.n_objs);
+    if (n_pad) filter_pack_tiles<<<(n_pad + 255) / 256, 256, 0, stream>>>(sc.cull, sc.n_objs, n_pad, sc.filter_h, out);
+    return cudaGetLastError();
 }
 
 cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb, int accel, const WaveGrids* grids, int sm_count,
@@ -1131,7 +1213,7 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
             // 4 rays per thread x 4 objects per iteration, 2 blocks per SM, 2048-object tiles: the fastest of the
             // configurations swept on the B200 (tools/build_filter_variants.sh; history in DESIGN.md)
             const cudaError_t fe = launch_filter<RT_FILTER_RPT, RT_FILTER_OPI, RT_FILTER_MINB, RT_FILTER_TILE>(sc, qin, nq, wb.res_t, wb.res_id,
-                                                                                                          fr.counters, count, sm_count, stream);
+                                                                                                          grids ? grids->filter_tiles : nullptr, fr.counters, count, sm_count, stream);
             if (fe != cudaSuccess) return fe;
             nl += 2;
         } else {

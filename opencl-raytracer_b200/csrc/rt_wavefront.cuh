@@ -23,7 +23,13 @@ struct WaveBuffers {
 struct WaveGrids {
     GridSet cam, lit;
     Grid3 g3;  // uniform grid for the rays without a common apex (valid == 0: they walk the BVH)
+    const float4* filter_tiles = nullptr;  // accel 1: the filter records packed into the tile layout (wave_pack_filter_tiles)
 };
+
+// accel 1 (wave_trace_filter): the scene's filter records in the layout its shared-memory tiles have, padded to whole tiles,
+// so that a tile is one bulk copy.  `out` holds 2 * wave_filter_tile_pad(n_objs) float4.
+uint32_t wave_filter_tile_pad(uint32_t n_objs);
+cudaError_t wave_pack_filter_tiles(const Scene& sc, float4* out, cudaStream_t stream);
 
 // Upper bound on the number of trace/advance generations of one frame.
 uint32_t wave_max_generations(uint32_t max_bounces, uint32_t n_lights, int mode);
