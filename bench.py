@@ -613,6 +613,43 @@ def main():
         except Exception as e:  # baseline infrastructure must never take the bench line down
             ref_ocl = {"unavailable": "error: %s" % e}
 
+    # ------------------------------------------------------------------ N > 1: the one-process multi-GPU paths, where the driver sees them
+    # (a) the C++ drop-in: build/rt_cli --gpus N (CudaRaytracer::UseDevices: one context + host thread per device) must write
+    # the very bytes the 1-GPU run writes; (b) two contexts of ONE process on two devices run the shared-memory-hungry filter
+    # kernel of the wavefront pipeline (function attributes are per device: round 1 opted in on the first device only).
+    one_process = None
+    if rank == 0 and world > 1:
+        import subprocess
+        import tempfile
+
+        one_process = {}
+        cli = os.path.join(ROOT, "build", "rt_cli")
+        scene = os.path.join(ROOT, "baseline", "_ref", "roundedCube.txt")
+        if os.path.exists(cli) and os.path.exists(scene):
+            outs = []
+            with tempfile.TemporaryDirectory() as td:
+                for g in (1, world):
+                    o = os.path.join(td, "r%d.ppm" % g)
+                    r = subprocess.run([cli, "--scene", scene, "--width", "640", "--height", "356", "--bounces", "30", "--gpus", str(g),
+                                        "--fast-ppm", "--out", o], capture_output=True, text=True, timeout=300)
+                    outs.append((r.returncode, open(o, "rb").read() if os.path.exists(o) else b"", r.stdout))
+            one_process["rt_cli_gpus"] = world
+            one_process["rt_cli_byte_identical"] = bool(outs[0][0] == 0 and outs[1][0] == 0 and outs[0][1] == outs[1][1] and len(outs[0][1]) > 0
+                                                        and ("Frame sharded over %d GPU(s)." % world) in outs[1][2])
+        else:
+            one_process["rt_cli_byte_identical"] = None
+        so, sl = scenes.synthetic_scene(3000, 300)
+        frames = []
+        for dev in (0, 1):
+            with lib.Context(dev) as cx:
+                cx.set_option(lib.OPT_PIPELINE, 1)
+                cx.upload_scene(so, sl)
+                cx.set_camera(320, 180, types.camera_zdir(180))
+                frames.append(cx.render(4, 2, 1).copy())
+        one_process["two_contexts_filter_kernel_equal"] = bool(np.array_equal(frames[0], frames[1]))
+        if one_process["rt_cli_byte_identical"] is False or not one_process["two_contexts_filter_kernel_equal"]:
+            sys.stderr.write("ONE-PROCESS MULTI-GPU CHECK FAILED: %s\n" % json.dumps(one_process))
+
     if rank == 0:
         out = {
             "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -651,6 +688,8 @@ def main():
             out["dynamic_scene"] = dynamic
         if small:
             out["configs"] = small
+        if one_process:
+            out["one_process_multi_gpu"] = one_process
         if ref_ocl:
             out["reference_opencl_gpu"] = ref_ocl
         sys.stdout.flush()

@@ -129,6 +129,9 @@ typedef enum rt_option {
                                   device (scenes that change every frame: ~1 ms instead of ~150 ms per 10^5 objects, a looser tree) */
     RT_OPT_LANES = 7,      /* 2 (default): camera launches of the wavefront pipeline run as two halves on two streams, each filling the
                               thin generation tails of the other; 1: one launch sequence */
+    RT_OPT_TAIL_GEN = 12,  /* wavefront pipeline: from this generation on (1 = after the primary rays, 1 + lights = after the first
+                              shading, ...) ONE kernel finishes every path that is still alive instead of a trace/advance pair per
+                              generation -- removes the latency-bound thin tail of small frames.  -1 (default) auto, 0 off */
     RT_OPT_DETECT_PINHOLE = 11, /* 1 (default): rt_set_rays recognises the pinhole grid main() builds (OpenCL-Raytracer.cpp:68-72) and
                                    switches to rt_set_camera (device ray generation, no 32 B/ray upload); 0: upload whatever arrives */
     RT_OPT_ZERO_COPY = 9,  /* rt_render into page-locked, device-addressable host memory (rt_host_alloc / rt_host_register / cudaHostAlloc):

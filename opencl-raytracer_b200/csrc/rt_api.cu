@@ -142,6 +142,7 @@ struct rt_ctx {
 
     // options
     int opt_detect_pinhole = 1;
+    int opt_tail_gen = -1;  // -1 auto; 0 off; g > 0: generations >= g of a launch sequence are finished by one wave_tail launch
     int opt_zero_copy = 0;  // 0 (default) never, 1 whenever the target is mapped pinned memory, -1 on the wavefront pipeline only -- measured slower, see rt_render
     int opt_pipeline = -1, opt_count = 0, opt_leaf = 1, opt_skip_dead = 1, opt_bands = 0, opt_builder = 0, opt_lanes = 0;
 
@@ -697,10 +698,10 @@ int ensure_wave_buffers(rt_ctx* c, uint64_t capacity, uint32_t gens, int n_seq, 
 // 42.3 (2: both finish together, the whole 9.4 ms copy is exposed) / 37.5 (4) / 36.9 (6) / 37.9 (8).  Stream priorities do
 // not order persistent kernels -- a resident low-priority CTA runs until its queue is empty -- and starting band k only
 // after the heavy generations of band k - 1 (an event chain) ordered the bands but cost more kernel time than it hid copy
-// (38.2 ms at 4 bands).  Hence: 6 bands when the frame goes to the host, 2 otherwise.
+// (38.2 ms at 4 bands).  With the tail launch (wave_tail) 4 bands measure best: 36.4 ms end to end.  Hence: 4 bands when the frame goes to the host, 2 otherwise.
 int auto_sequences(const rt_ctx* c, bool to_host, bool aov_only) {
     if (!c->use_camera || aov_only) return 1;
-    int n = to_host && c->opt_bands > 0 ? c->opt_bands : (c->opt_lanes > 0 ? c->opt_lanes : (to_host ? 6 : 2));
+    int n = to_host && c->opt_bands > 0 ? c->opt_bands : (c->opt_lanes > 0 ? c->opt_lanes : (to_host ? 4 : 2));
     n = std::min(n, rt_ctx::kMaxBands);
     const uint64_t px = local_pixels(c);
     while (n > 1 && (px / n < (1ull << 19) || band_units(c) < (uint32_t)(4 * n))) --n;  // at least 0.5 Mpixel and 4 units per band
@@ -748,6 +749,20 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
         const uint32_t gens = rt::wave_max_generations(max_bounces, c->scene.n_lights, mode);
         if (gens > kMaxWaveGenerations) return fail(RT_ERR_INVALID, "max_bounces x lights too large for the wavefront pipeline; use RT_OPT_PIPELINE 0");
         const int n_seq = auto_sequences(c, host_out != nullptr, aov_only);
+        static const int tail_env = [] {
+            const char* v = getenv("RT_TAIL_GEN");
+            return v && *v ? atoi(v) : -1;
+        }();
+        // auto: the smaller a launch sequence, the earlier its generations are thin -- one, two or three bounce levels
+        // ((1 + lights) generations each) run as trace / advance pairs, one wave_tail launch finishes the rest.  Swept on the
+        // 8K cfg5 frame and its 1/2, 1/4, 1/8 shards (tools/sweep_tail.py, profiles/r2_sweep_tail.txt): 32.9 -> 32.4 ms whole,
+        // 17.5 -> 17.0, 9.8 -> 9.0, 5.9 -> 4.85 ms for the shard one of 8 GPUs renders.
+        int tail_gen = c->opt_tail_gen >= 0 ? c->opt_tail_gen : tail_env;
+        if (tail_gen < 0) {
+            const uint64_t px_seq = local_pixels(c) / (uint64_t)n_seq;
+            const int levels = px_seq >= (12ull << 20) ? 3 : px_seq >= (6ull << 20) ? 2 : 1;
+            tail_gen = levels * (1 + (int)c->scene.n_lights);
+        }
         const uint32_t units = c->use_camera ? band_units(c) : 0u;
         rt::Frame fr[rt_ctx::kMaxBands];
         uint64_t offset[rt_ctx::kMaxBands], cap[rt_ctx::kMaxBands];
@@ -782,7 +797,7 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
             cudaStream_t st = n_seq == 1 ? c->stream : c->seq_stream[k];
             if (n_seq > 1) RT_CUDA(cudaStreamWaitEvent(st, c->ev0, 0));
             uint32_t nl = 0;
-            if (fr[k].n_local > 0) RT_CUDA(rt::wave_render(c->scene, fr[k], wb[k], accel, &wg, c->sm_count, &nl, st));
+            if (fr[k].n_local > 0) RT_CUDA(rt::wave_render(c->scene, fr[k], wb[k], accel, &wg, c->sm_count, &nl, st, tail_gen));
             c->last_launches += nl;
             if (n_seq > 1 || host_out) RT_CUDA(cudaEventRecord(c->band_done[k], st));
             if (host_out && fr[k].n_local > 0) {  // the band's rows go home under the kernels of the bands behind it
@@ -943,6 +958,10 @@ int rt_set_option(rt_ctx* c, int option, int64_t value) {
         case RT_OPT_READBACK_BANDS:
             if (value < 0 || value > rt_ctx::kMaxBands) return fail(RT_ERR_INVALID, "readback bands must be 0 (auto) or 1..16");
             c->opt_bands = (int)value;
+            return RT_OK;
+        case RT_OPT_TAIL_GEN:
+            if (value < -1 || value > 4096) return fail(RT_ERR_INVALID, "tail generation must be -1 (auto), 0 (off) or 1..4096");
+            c->opt_tail_gen = (int)value;
             return RT_OK;
         case RT_OPT_DETECT_PINHOLE:
             c->opt_detect_pinhole = value ? 1 : 0;

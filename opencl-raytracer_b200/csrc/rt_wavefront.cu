@@ -1115,6 +1115,67 @@ __global__ void __launch_bounds__(kBlock, RT_ADV_MINB) wave_advance(const Scene 
     if (COUNT) flush_local(lc, ctr);
 }
 
+// ------------------------------------------------------------------------------------------------ tail
+// The late generations of a frame are thin: a few thousand rays each, every kernel of the chain bound by the latency of its
+// longest ray, ~0.05-0.3 ms per generation whatever the GPU could do in that time -- the fixed cost that limits small frames
+// (a shard of an 8-GPU job, a readback band).  From generation `tail_gen` on, ONE launch finishes every path that is still
+// alive: a thread takes a task of that generation's queue and runs trace -> state machine -> trace ... in place until the
+// path writes its pixel (the megakernel's per-ray searches: rt_device.cuh trace_bvh, rt_pgrid.cuh trace_grid; the same
+// wave::step as wave_advance, so the same bits).  Warps fetch 32 tasks at a time.
+template <bool COUNT>
+__global__ void __launch_bounds__(128) wave_tail(const Scene sc, const GridSet lit, const WaveParams wp, const PathArrays pa, const TaskQueue qin,
+                                                  const uint32_t* __restrict__ n_in, uint32_t* __restrict__ fetch, float4* __restrict__ fb, Counters* ctr) {
+    const uint32_t nb = n_in[0], na = n_in[1];
+    const uint32_t n = nb + na;
+    if (n == 0u) return;
+    const unsigned lane = threadIdx.x & 31u;
+    LocalCounters lc;
+    const uint32_t back = wp.qcap - 1u;
+    for (;;) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(fetch, 32u);
+        base = __shfl_sync(kFull, base, 0);
+        if (base >= n) break;
+        const uint32_t i = base + lane;
+        if (i >= n) continue;
+        const uint32_t at = i < nb ? i : back - (i - nb);
+        Ray ray;
+        ray.s = qin.s[at];
+        ray.d = qin.d[at];
+        uint32_t pw = qin.path[at];
+        const uint32_t p = pw & RT_TASK_PATH_MASK;
+        for (;;) {
+            unsigned long long ne = 0, nn = 0, np = 0;
+            Hit res;
+            const uint32_t li = (pw >> RT_TASK_LIGHT_SHIFT) & 15u;
+            if ((pw & RT_TASK_ANYHIT) && li != RT_TASK_NO_GRID)
+                res = trace_grid<true>(sc, lit, 6u * li, ray, COUNT ? &np : nullptr, COUNT ? &ne : nullptr);
+            else if (pw & RT_TASK_ANYHIT)
+                res = trace_bvh<true>(sc, ray, 1.f, COUNT ? &ne : nullptr, COUNT ? &nn : nullptr);
+            else
+                res = trace_bvh<false>(sc, ray, RT_MAX_FLOAT, COUNT ? &ne : nullptr, COUNT ? &nn : nullptr);
+            if (COUNT) {
+                lc.exact_tests += ne;
+                lc.node_visits += nn;
+                lc.pair_tests += np;
+            }
+            if (res.id < 0) res.t = RT_MAX_FLOAT;
+            StepOut o;
+            wave::step<COUNT>(sc, wp, pa, p, false, ray, res, o, lc);
+            if (o.write && fb) fb[pa.out[p]] = o.px;
+            if (!o.emit) break;
+            bool to_a = false;
+            if (o.anyhit && o.light < RT_TASK_NO_GRID && ((wp.grid_lights >> o.light) & 1u)) {
+                const float chk = o.ray.s.x + o.ray.s.y + o.ray.s.z + o.ray.d.x + o.ray.d.y + o.ray.d.z;
+                to_a = fabsf(chk) < __int_as_float(0x7f800000);
+            }
+            ray = o.ray;
+            pw = p | ((to_a ? o.light : RT_TASK_NO_GRID) << RT_TASK_LIGHT_SHIFT) | (o.anyhit ? RT_TASK_ANYHIT : 0u);
+        }
+    }
+    if (COUNT) flush_local(lc, ctr);
+}
+
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------ host driver
@@ -1139,7 +1200,7 @@ cudaError_t wave_pack_filter_tiles(const Scene& sc, float4* out, cudaStream_t st
 }
 
 cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb, int accel, const WaveGrids* grids, int sm_count,
-                        uint32_t* launches, cudaStream_t stream) {
+                        uint32_t* launches, cudaStream_t stream, int tail_gen) {
     // warp-scheduler thresholds of wave_trace_bvh (tunable for experiments)
     static const int min_t = env_int("RT_WAVE_MIN_T", 12), drain_t = env_int("RT_WAVE_DRAIN", 4), refill_t = env_int("RT_WAVE_REFILL", 16);
     static const int g_min_t = env_int("RT_GRID_MIN_T", 12), g_drain_t = env_int("RT_GRID_DRAIN", 4), g_refill_t = env_int("RT_GRID_REFILL", 16);
@@ -1187,6 +1248,16 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
         const TaskQueue& qin = wb.q[g & 1u];
         const TaskQueue& qout = wb.q[(g + 1u) & 1u];
         uint32_t* nq = qcount + 2 * g;
+        if (tail_gen > 0 && g >= (uint32_t)tail_gen && accel >= 2 && !fr.hit_id) {  // one launch finishes what is left
+            const unsigned tgrid = (unsigned)sm_count * 8u;
+            const GridSet lit = use_grids ? grids->lit : GridSet{};
+            if (count)
+                wave_tail<true><<<tgrid, 128, 0, stream>>>(sc, lit, wp, wb.pa, qin, nq, fetch + 2 * g, fr.out, fr.counters);
+            else
+                wave_tail<false><<<tgrid, 128, 0, stream>>>(sc, lit, wp, wb.pa, qin, nq, fetch + 2 * g, fr.out, fr.counters);
+            ++nl;
+            break;
+        }
         // class A: generation 0 when the camera has a grid, later generations when a light has
         if ((g == 0 && cam_grid) || (g > 0 && light_grids)) {
             if (count)

@@ -36,8 +36,9 @@ uint32_t wave_max_generations(uint32_t max_bounces, uint32_t n_lights, int mode)
 
 // Enqueue every kernel of one frame on `stream` (no host synchronisation inside).
 // accel: 0 exact brute force, 1 filter (N-body tiles), 2 BVH, 3 perspective grids for camera rays and point-light shadow rays
-// (grids != nullptr) + BVH for everything else.  *launches receives the number of kernels enqueued.
+// (grids != nullptr) + BVH for everything else.  *launches receives the number of kernels enqueued.  tail_gen > 0 (BVH /
+// grid searches only): generations tail_gen, tail_gen + 1, ... are finished by one wave_tail launch.
 cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb, int accel, const WaveGrids* grids, int sm_count,
-                        uint32_t* launches, cudaStream_t stream);
+                        uint32_t* launches, cudaStream_t stream, int tail_gen = 0);
 
 }  // namespace rt

@@ -15,7 +15,7 @@ _PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 # RT_B200_LIB: an alternative build of the same library (kernel experiments); never a fallback
 LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_PKG, "librt_b200.so")
 
-OPT_PIPELINE, OPT_COUNT_RAYS, OPT_BVH_LEAF, OPT_SKIP_DEAD_RAYS, OPT_READBACK_BANDS, OPT_BVH_BUILDER, OPT_LANES, OPT_GRID_RES, OPT_ZERO_COPY, OPT_GRID3_DENSITY, OPT_DETECT_PINHOLE = 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11
+OPT_PIPELINE, OPT_COUNT_RAYS, OPT_BVH_LEAF, OPT_SKIP_DEAD_RAYS, OPT_READBACK_BANDS, OPT_BVH_BUILDER, OPT_LANES, OPT_GRID_RES, OPT_ZERO_COPY, OPT_GRID3_DENSITY, OPT_DETECT_PINHOLE, OPT_TAIL_GEN = 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12
 ACCEL_AUTO, ACCEL_BRUTE, ACCEL_CULL, ACCEL_BVH, ACCEL_GRID = -1, 0, 1, 2, 3
 
 # every symbol include/rt_b200.h declares (tests check the library exports all of them)

@@ -741,3 +741,53 @@ def test_scene_that_changes_every_frame(rt, oracle_mod):
             fresh.upload_scene(unknown, lights)
             fresh.set_camera(W, H, z)
             assert np.array_equal(dyn.render(4, 2, -1), fresh.render(4, 2, -1))
+
+
+def test_tail_launch_equals_generation_chain(rt, ctx, oracle_mod):
+    """RT_OPT_TAIL_GEN: from generation g on one launch finishes every live path (wave_tail) instead of a trace / advance pair
+    per generation.  Same frame, same ray counts, for every g, three lights (stale-specular walk), SHADE and SAR, both the
+    BVH and the grids."""
+    objs, lights = S.synthetic_scene(5000, 500, n_lights=3)
+    W, H = 200, 112
+    z, rays = frame_rays(W, H)
+    ctx.set_option(rt.OPT_PIPELINE, 1)
+    ctx.set_option(rt.OPT_COUNT_RAYS, 1)
+    ctx.upload_scene(objs, lights)
+    ctx.set_camera(W, H, z)
+    for mode, mb in ((2, 4), (1, 0)):
+        ref, hid, ht, st = oracle_mod.port_render(mode, mb, objs, lights, rays)
+        for accel in (2, 3):
+            ctx.set_option(rt.OPT_TAIL_GEN, 0)
+            chain = ctx.render(mb, mode, accel).copy()
+            s0 = ctx.stats()
+            assert_colours_close(chain, ref)
+            for g in (1, 2, 3, 4, 5, 8, 40):
+                ctx.set_option(rt.OPT_TAIL_GEN, g)
+                out = ctx.render(mb, mode, accel)
+                s = ctx.stats()
+                assert np.array_equal(out, chain), (mode, accel, g)
+                counts = (s.rays_primary, s.rays_shadow, s.rays_reflect, s.traced_shadow, s.traced_reflect, s.hit_pixels)
+                assert counts == (s0.rays_primary, s0.rays_shadow, s0.rays_reflect, s0.traced_shadow, s0.traced_reflect, s0.hit_pixels)
+                assert s.kernel_launches <= s0.kernel_launches
+    ctx.set_option(rt.OPT_TAIL_GEN, -1)
+
+
+def test_two_contexts_one_process_filter_kernel(rt):
+    """One process, one context per device (what CudaRaytracer::UseDevices does): the wavefront filter kernel needs the 64 KB
+    dynamic shared-memory opt-in on EVERY device it runs on, not only on the first one (advisor finding, round 1).  Needs two
+    GPUs; bench.py runs the same check at N > 1 where the driver sees it (`one_process_multi_gpu`)."""
+    import ctypes
+
+    n = ctypes.c_int(0)
+    assert rt.load().rt_device_count(ctypes.byref(n)) == 0
+    if n.value < 2:
+        pytest.skip("needs two GPUs")
+    objs, lights = S.synthetic_scene(3000, 300)
+    frames = []
+    for dev in (1, 0, 1):
+        with rt.Context(dev) as c:
+            c.set_option(rt.OPT_PIPELINE, 1)
+            c.upload_scene(objs, lights)
+            c.set_camera(320, 180, T.camera_zdir(180))
+            frames.append(c.render(4, 2, 1).copy())
+    assert np.array_equal(frames[0], frames[1]) and np.array_equal(frames[0], frames[2])
