@@ -701,9 +701,11 @@ int ensure_wave_buffers(rt_ctx* c, uint64_t capacity, uint32_t gens, int n_seq, 
 // (38.2 ms at 4 bands).  With the tail launch (wave_tail) 4 bands measure best: 36.4 ms end to end.  Hence: 4 bands when the frame goes to the host, 2 otherwise.
 int auto_sequences(const rt_ctx* c, bool to_host, bool aov_only) {
     if (!c->use_camera || aov_only) return 1;
-    int n = to_host && c->opt_bands > 0 ? c->opt_bands : (c->opt_lanes > 0 ? c->opt_lanes : (to_host ? 4 : 2));
-    n = std::min(n, rt_ctx::kMaxBands);
     const uint64_t px = local_pixels(c);
+    // to the host: 4 bands for 12 Mpixel and more, 2 below (tools/sweep_shard_bands.py, profiles/r2_sweep_shard_bands.txt: the
+    // 1/4 and 1/8 shards of the 8K frame gain nothing from more than 2, and every band is a dozen more launches per rank)
+    int n = to_host && c->opt_bands > 0 ? c->opt_bands : (c->opt_lanes > 0 ? c->opt_lanes : (to_host && px >= (12ull << 20) ? 4 : 2));
+    n = std::min(n, rt_ctx::kMaxBands);
     while (n > 1 && (px / n < (1ull << 19) || band_units(c) < (uint32_t)(4 * n))) --n;  // at least 0.5 Mpixel and 4 units per band
     return std::max(n, 1);
 }

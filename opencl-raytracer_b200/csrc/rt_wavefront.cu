@@ -179,12 +179,37 @@ constexpr int kPendCap = RT_PEND_CAP;  // queued candidates per lane (a lane sto
 
 // The reference arithmetic for one (ray, object) pair, kept out of line: it is long (two 4x4 transforms,
 // IEEE divides and a square root) and rare, and inlining it into the hot loops thrashes the instruction cache.
-__device__ __noinline__ void exact_pair_call(const Scene& sc, const float4 s, const float4 d, uint32_t obj, uint32_t type,
-                                             Hit& best, uint32_t& btype) {
+// The current best hit travels by VALUE: a reference parameter of a function that is not inlined forces the caller to keep
+// best.t in local memory, and the traversal loop then reloads it (LDL) in every node step.
+struct BestHit {
+    float t;
+    int32_t id;
+    uint32_t type;
+};
+__device__ __noinline__ BestHit exact_pair_value(const Scene& sc, const float4 s, const float4 d, uint32_t obj, uint32_t type, BestHit cur) {
     Ray r;
     r.s = s;
     r.d = d;
+    Hit best;
+    best.t = cur.t;
+    best.id = cur.id;
+    uint32_t btype = cur.type;
     exact_pair(sc, r, obj, type, best, btype);
+    cur.t = best.t;
+    cur.id = best.id;
+    cur.type = btype;
+    return cur;
+}
+__device__ __forceinline__ void exact_pair_call(const Scene& sc, const float4 s, const float4 d, uint32_t obj, uint32_t type, Hit& best,
+                                                uint32_t& btype) {
+    BestHit b;
+    b.t = best.t;
+    b.id = best.id;
+    b.type = btype;
+    b = exact_pair_value(sc, s, d, obj, type, b);
+    best.t = b.t;
+    best.id = b.id;
+    btype = b.type;
 }
 
 // Persistent warps.  Every lane owns one ray of the queue and is in one of four states:
@@ -1082,10 +1107,15 @@ __global__ void __launch_bounds__(kBlock, RT_ADV_MINB) wave_advance(const Scene 
         uint32_t p = 0;
         if (i < n) {
             const uint32_t at = i < nb ? (uint32_t)i : back - ((uint32_t)i - nb);
+            const uint32_t pw = qin.path[at];
+            p = pw & RT_TASK_PATH_MASK;
             Ray ray;
-            ray.s = qin.s[at];
-            ray.d = qin.d[at];
-            p = qin.path[at] & RT_TASK_PATH_MASK;
+            if (pw & RT_TASK_ANYHIT) {  // a shadow ray came back: the state machine needs its result, not the ray (32 B less per event)
+                ray.s = ray.d = make_float4(0.f, 0.f, 0.f, 0.f);
+            } else {
+                ray.s = qin.s[at];
+                ray.d = qin.d[at];
+            }
             Hit res;
             res.t = res_t[at];
             res.id = res_id[at];
