@@ -511,10 +511,11 @@ def main():
                         "frac": (exact_tests * FLOPS_ALGO_PAIR + shades * FLOPS_SHADE) / world / (ms_dev * 1e-3) / 1e12 / peak_tf if peak_tf else None},
         "hbm": {"framebuffer_bytes_per_launch": pixels * 16 / world, "achieved_gbs": pixels * 16 / world / (ms_dev * 1e-3) / 1e9,
                 "peak_gbs": peaks.get("hbm_gbs")},
-        "note": "BVH traversal is bound by divergent node fetches, not by FP32: ncu (profiles/r1_g_wave_trace_bvh_cfg5_8k.txt, "
-                "this frame, primary-ray launch) shows the L1 data pipe at 64 % of its wavefront peak and the issue slots at 74 %; "
-                "the FP32 fraction is reported for completeness, see roofline_brute for the FP32-bound kernel"
-        if accel_used >= 2 else "",
+        "note": ("the frame's dominant kernel is the BVH trace of the reflection rays (the rays through a common apex -- camera, point-light "
+                 "shadow -- look up a perspective grid instead: wave_trace_grid); it is bound by issue slots and divergent node fetches, not "
+                 "by FP32: ncu (profiles/r2_wave_trace_bvh_cfg5_8k.txt, this frame) shows issue slots 65 % busy, ALU pipe 46 % vs FMA 24 %, L1 "
+                 "wavefronts 59 % of peak, 22.5 of 32 lanes active; the FP32 fraction is reported for completeness, see roofline_brute for "
+                 "the FP32-bound kernel") if accel_used >= 2 else "",
     }
 
     # brute-force leg: the reference's O(rays x objects) search (filter + exact) on a bounded band of the same frame
@@ -671,8 +672,9 @@ def main():
                     "path": "rt_render into the caller's pinned frame" if world == 1 else
                             "every rank rt_render()s its row-blocks into one shared, page-locked host frame (own PCIe link per GPU)",
                     "ctor_plus_first_render_ms": cold_ms, "scene_h2d_bytes_once": int(len(objs)) * 276 + int(len(lights)) * 64,
-                    "note": "rt_render == IRaytracer::Render(): launch + blocking readback (bands of rows, copy overlapped with the next "
-                            "band's kernels); scene/camera resident as in the reference ctor, whose one-off cost is ctor_plus_first_render_ms"},
+                    "note": "rt_render == IRaytracer::Render(): launch + blocking readback (concurrent bands of rows on their own streams, a "
+                            "finished band is copied under the kernels of the others); scene/camera resident as in the reference ctor, whose "
+                            "one-off cost is ctor_plus_first_render_ms"},
             "gpu_launches": args.steps * launches_per_step,
             "rank_ms": rank_ms or None,
             "clocks": clocks,
