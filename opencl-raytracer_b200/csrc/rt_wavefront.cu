@@ -240,7 +240,11 @@ __global__ void __launch_bounds__(kBlock, RT_BVH_MINB) wave_trace_bvh(const Scen
     const unsigned lane = threadIdx.x & 31u, tid = threadIdx.x;
     LocalCounters lc;
 
-    bool have = false, tdone = false, anyhit = false;
+    // lane state: 0 idle, 1 traversing, 2 traversal finished (candidates may still be queued) -- one register, one compare per
+    // vote; tlim: the pruning limit (best t, capped at 1 for a shadow ray), kept up to date where best.t changes
+    int st = 0;
+    bool anyhit = false;
+    float tlim = RT_MAX_FLOAT;
     uint32_t task = 0;
     float ox = 0.f, oy = 0.f, oz = 0.f, idx = 0.f, idy = 0.f, idz = 0.f;
     Hit best;
@@ -255,15 +259,15 @@ __global__ void __launch_bounds__(kBlock, RT_BVH_MINB) wave_trace_bvh(const Scen
     for (;;) {
         // ---- refill
         {
-            const unsigned idle = __ballot_sync(kFull, !have);
-            const unsigned trav = __ballot_sync(kFull, have && !tdone);
+            const unsigned idle = __ballot_sync(kFull, st == 0);
+            const unsigned trav = __ballot_sync(kFull, st == 1);
             if (idle && !exhausted && (__popc(idle) >= refill_t || trav == 0u)) {
                 // (one same-address atomic per refill; reserving 32..256-ray chunks per warp instead -- guided
                 // self-scheduling -- was measured equal on the 8K frame, fixed chunks slower by their tails)
                 uint32_t base = 0;
                 if (lane == 0) base = atomicAdd(fetch, (uint32_t)__popc(idle));
                 base = __shfl_sync(kFull, base, 0);
-                if (!have) {
+                if (st == 0) {
                     const uint32_t i = base + (uint32_t)__popc(idle & lanemask_lt());
                     if (i < n) {
                         task = i;
@@ -280,8 +284,8 @@ __global__ void __launch_bounds__(kBlock, RT_BVH_MINB) wave_trace_bvh(const Scen
                         cur = sc.root;
                         sp = 0;
                         npend = 0;
-                        tdone = false;
-                        have = true;
+                        st = 1;
+                        tlim = anyhit ? 1.f : RT_MAX_FLOAT;
                         if (cur < 0) {  // the whole scene is one leaf (tiny scenes): test its objects in place
                             const uint32_t code = (uint32_t)(~cur);
                             const uint32_t first = code >> 4, cnt = sc.n_objs ? (code & 15u) + 1u : 0u;
@@ -289,30 +293,30 @@ __global__ void __launch_bounds__(kBlock, RT_BVH_MINB) wave_trace_bvh(const Scen
                                 exact_pair_call(sc, s, d, __ldg(sc.leaf_obj + first + j), __ldg(&sc.leaf_cull[first + j].type), best, btype);
                                 if (COUNT) lc.exact_tests++;
                             }
-                            tdone = true;
+                            st = 2;
                         }
                     }
                 }
                 if (base + (uint32_t)__popc(idle) >= n) exhausted = true;
             }
-            if (!__any_sync(kFull, have)) break;
+            if (!__any_sync(kFull, st != 0)) break;
         }
 
         // ---- node steps
         for (;;) {
             // a lane that holds a candidate waits for its exact test: nothing is traversed with a stale best t
-            const bool go = have && !tdone && npend == 0;
+            const bool go = st == 1 && npend == 0;
             const unsigned T = __ballot_sync(kFull, go);
             if (T == 0u) break;
             if (__popc(T) < min_t) {
-                if (__popc(__ballot_sync(kFull, have && npend > 0)) >= drain_t) break;
-                if (!exhausted && __popc(__ballot_sync(kFull, !have || (tdone && npend == 0))) >= refill_t) break;
+                if (__popc(__ballot_sync(kFull, npend > 0)) >= drain_t) break;
+                if (!exhausted && __popc(__ballot_sync(kFull, st == 0 || (st == 2 && npend == 0))) >= refill_t) break;
             }
             if (go) {
                 const float4* np = reinterpret_cast<const float4*>(sc.nodes + cur);
                 const float4 q0 = __ldg(np + 0), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
                 if (COUNT) lc.node_visits++;
-                const float tlimit = anyhit ? fminf(best.t, 1.f) : best.t;
+                const float tlimit = tlim;
                 float tn0, tn1;
                 // child 0: ctr (q0.x q0.y q0.z) ext (q0.w q1.x q1.y); child 1: ctr (q1.z q1.w q2.x) ext (q2.y q2.z q2.w)
                 bool h0 = cv::box_may_hit(ox, oy, oz, idx, idy, idz, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q3.z, tlimit, tn0);
@@ -331,6 +335,7 @@ __global__ void __launch_bounds__(kBlock, RT_BVH_MINB) wave_trace_bvh(const Scen
                             } else {  // buffer full (leaves larger than the buffer): test in place
                                 exact_pair_call(sc, q.s[task], q.d[task], __ldg(sc.leaf_obj + first + j),
                                                 __ldg(&sc.leaf_cull[first + j].type), best, btype);
+                                tlim = anyhit ? fminf(best.t, 1.f) : best.t;
                                 if (COUNT) lc.exact_tests++;
                             }
                         }
@@ -347,7 +352,7 @@ __global__ void __launch_bounds__(kBlock, RT_BVH_MINB) wave_trace_bvh(const Scen
                 } else if (sp > 0) {
                     cur = stack[--sp];
                 } else {
-                    tdone = true;
+                    st = 2;
                 }
             }
         }
@@ -356,27 +361,28 @@ __global__ void __launch_bounds__(kBlock, RT_BVH_MINB) wave_trace_bvh(const Scen
         // over its 32 lanes, owners merging the results -- was measured 1.5 % slower: the scan, the owner search and the
         // staging through shared memory cost more than the idle lanes)
         for (;;) {
-            const bool has = have && npend > 0;
+            const bool has = npend > 0;
             const unsigned P = __ballot_sync(kFull, has);
             if (P == 0u) break;
-            const unsigned T = __ballot_sync(kFull, have && !tdone && npend == 0);
+            const unsigned T = __ballot_sync(kFull, st == 1 && npend == 0);
             if (!(__popc(P) >= drain_t || T == 0u)) break;
             if (has) {
                 const uint32_t slot = pend[--npend][tid];
                 exact_pair_call(sc, q.s[task], q.d[task], __ldg(sc.leaf_obj + slot), __ldg(&sc.leaf_cull[slot].type), best, btype);
                 if (COUNT) lc.exact_tests++;
+                tlim = anyhit ? fminf(best.t, 1.f) : best.t;
                 if (anyhit && best.t < 1.f) {  // the shadow ray is decided (SAR:229)
-                    tdone = true;
+                    st = 2;
                     npend = 0;
                 }
             }
         }
 
         // ---- retire
-        if (have && tdone && npend == 0) {
+        if (st == 2 && npend == 0) {
             res_t[task] = best.id >= 0 ? best.t : RT_MAX_FLOAT;
             res_id[task] = best.id;
-            have = false;
+            st = 0;
         }
     }
     if (COUNT) flush_local(lc, ctr);
