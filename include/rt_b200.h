@@ -138,7 +138,7 @@ typedef enum rt_option {
                               the kernels store finished pixels straight into the caller's frame instead of a framebuffer in HBM that is
                               copied afterwards.  -1 (default): on the wavefront pipeline, 0: never, 1: on both pipelines */
     RT_OPT_GRID3_DENSITY = 10, /* RT_ACCEL_GRID: the rays without a common apex (reflection rays, ...) walk a uniform 3-D grid with this
-                                  many cells per 100 objects instead of the BVH; 0 (default) = BVH -- measured no faster on the headline scene.  Scenes whose lists come out
+                                  many cells per 100 objects (default 400) instead of the BVH; 0 = BVH.  Scenes whose lists come out
                                   long (clustered / very uneven object sizes) keep the BVH regardless. */
     RT_OPT_GRID_RES = 8,   /* cells per side of each of the six perspective grids around a light (default 512, 32..4096) */
     RT_OPT_READBACK_BANDS = 5  /* rt_render of a large camera frame (or shard of one): bands of rows / row-blocks whose readback

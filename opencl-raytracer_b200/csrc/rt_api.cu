@@ -130,12 +130,12 @@ struct rt_ctx {
     DevBuf<float4> d_filter_tiles;  // accel 1 on the wavefront pipeline: filter records in tile layout (rt_wavefront.cu)
     bool filter_tiles_dirty = true;
     // uniform 3-D grid (rt_grid3.cuh) for the rays without a common apex
-    DevBuf<uint32_t> g3_cell_start;
-    DevBuf<rt::Grid3Entry> g3_entries;
+    DevBuf<uint32_t> g3_cell_start, g3_entries;
+    DevBuf<rt::F4> d_aabb;
     rt::Grid3 g3 = {};
     bool g3_dirty = true;
     uint64_t g3_n_entries = 0;
-    int opt_grid3 = 0;  // cells per 100 objects; 0 (default): off, the BVH serves these rays -- measured: no faster (build_grid3)
+    int opt_grid3 = 400;  // cells per 100 objects (default 4 per object); 0: off, the BVH serves these rays
     uint32_t g_cam_w = 0, g_cam_h = 0;
     float g_cam_z = 0.f;
     int opt_grid_res = 512;
@@ -341,10 +341,10 @@ int build_grid_set(rt_ctx* c, rt_ctx::GridBufs& gb, std::vector<rt::PGrid>& grid
 // The uniform grid over the whole scene (rt_grid3.cuh): cubic cells, about opt_grid3 / 100 of them per object.  Not built --
 // the BVH stays in charge of the rays without a common apex -- when the lists come out long: objects that are large against
 // the cell (few big objects among many small ones, a clustered scene) would be entered into thousands of cells.
-// OFF BY DEFAULT.  Measured on the 8K cfg5 frame (profiles/r2_sweep_grid3.txt, r2_wave_trace_dda_cfg5_8k.txt): the walk needs
-// 15 cells and 38 filter tests per reflection ray where the BVH needs 52 node steps, but its two short code paths (cell step,
-// list entry) diverge inside the warp (10 and 17 of 32 lanes active), 5 800 thread instructions per ray against the BVH's
-// ~6 400: 33.2 ms per frame at the best density (4 cells per object) against 33.0 ms with the BVH.
+// Measured on the 8K cfg5 frame (profiles/r2_sweep_grid3.txt): the walk needs 18 cells and 23 filter tests per reflection ray
+// where the BVH needs 52 node steps of two inflated slab tests each; frame 31.9 ms (BVH) -> 27.3 ms at 4 cells per object
+// (1: 29.1, 2: 27.6, 8: 27.7, 16: 28.8) -> 24.9 ms with four resident CTAs per SM.  (A first version that entered objects by
+// the cube around their bounding SPHERE and recomputed the cell boundaries in every step was no faster than the BVH: 33.2 ms.)
 int build_grid3(rt_ctx* c) {
     c->g3 = rt::Grid3{};
     c->g3_dirty = false;
@@ -353,17 +353,18 @@ int build_grid3(rt_ctx* c) {
     if (c->opt_grid3 <= 0 || n_objs < 64 || c->hs.cull.size() < n_objs) return RT_OK;  // (a device-prepared scene has no host records)
     const float ext0 = 2.f * c->hs.scene_radius + 1.f;
     const float eps = 2e-5f * ext0 + 1e-4f;
-    double lo[3] = {1e30, 1e30, 1e30}, hi[3] = {-1e30, -1e30, -1e30}, rsum = 0;
+    double lo[3] = {1e30, 1e30, 1e30}, hi[3] = {-1e30, -1e30, -1e30};
     uint32_t live = 0;
+    if (c->hs.aabb.size() < n_objs) return RT_OK;
     for (uint32_t o = 0; o < n_objs; ++o) {
-        float r;
-        if (!rt::grid3_object_sphere(c->hs.cull[o], c->hs.omax, eps, r)) continue;
+        const rt::F4& hb = c->hs.aabb[o];
+        if (hb.w < 0.f || c->hs.cull[o].r2 < 0.f) continue;
         ++live;
-        rsum += r;
         const float ctr[3] = {c->hs.cull[o].cx, c->hs.cull[o].cy, c->hs.cull[o].cz};
+        const float half[3] = {hb.x, hb.y, hb.z};
         for (int k = 0; k < 3; ++k) {
-            lo[k] = std::min(lo[k], (double)ctr[k] - r);
-            hi[k] = std::max(hi[k], (double)ctr[k] + r);
+            lo[k] = std::min(lo[k], (double)ctr[k] - half[k] - eps);
+            hi[k] = std::max(hi[k], (double)ctr[k] + half[k] + eps);
         }
     }
     if (live < 64) return RT_OK;
@@ -388,13 +389,26 @@ int build_grid3(rt_ctx* c) {
     RT_CUDA(c->g_cursor.ensure((size_t)n_cells + 1));
     const size_t sb = rt::pgrid_scan_bytes(n_cells);
     RT_CUDA(c->g_scan.ensure(sb));
-    RT_CUDA(rt::grid3_count(g, c->d_cull.p, n_objs, c->hs.omax, c->g_cursor.p, c->g3_cell_start.p, c->g_scan.p, sb, c->stream));
+    RT_CUDA(c->d_aabb.upload(c->hs.aabb, c->stream));
+    RT_CUDA(rt::grid3_count(g, c->d_cull.p, reinterpret_cast<const float4*>(c->d_aabb.p), n_objs, c->g_cursor.p, c->g3_cell_start.p, c->g_scan.p, sb, c->stream));
     uint32_t total = 0;
     RT_CUDA(cudaMemcpyAsync(&total, c->g3_cell_start.p + n_cells, sizeof total, cudaMemcpyDeviceToHost, c->stream));
     RT_CUDA(cudaStreamSynchronize(c->stream));
-    if ((uint64_t)total > 64ull * live) return RT_OK;  // long lists: the BVH serves this scene better
+    if ((uint64_t)total > 64ull * live) return RT_OK;  // objects large against the cells: the BVH serves this scene better
+    {   // ... and so it does when the objects cluster: the list length an entry sees on average (sum len^2 / sum len) must stay
+        // small, or the walk degenerates into brute force inside the crowded cells
+        std::vector<uint32_t> cs((size_t)n_cells + 1);
+        RT_CUDA(cudaMemcpyAsync(cs.data(), c->g3_cell_start.p, cs.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+        RT_CUDA(cudaStreamSynchronize(c->stream));
+        double s2 = 0.0;
+        for (uint32_t k = 0; k < n_cells; ++k) {
+            const double len = (double)(cs[k + 1] - cs[k]);
+            s2 += len * len;
+        }
+        if (total > 0 && s2 / (double)total > 24.0) return RT_OK;
+    }
     RT_CUDA(c->g3_entries.ensure(std::max<size_t>(total, 1)));
-    RT_CUDA(rt::grid3_fill(g, c->d_cull.p, n_objs, c->hs.omax, c->g_cursor.p, c->g3_cell_start.p, c->g3_entries.p, c->stream));
+    RT_CUDA(rt::grid3_fill(g, c->d_cull.p, reinterpret_cast<const float4*>(c->d_aabb.p), n_objs, c->g_cursor.p, c->g3_cell_start.p, c->g3_entries.p, c->stream));
     RT_CUDA(cudaStreamSynchronize(c->stream));
     g.cell_start = c->g3_cell_start.p;
     g.entries = c->g3_entries.p;
@@ -923,7 +937,7 @@ int rt_destroy(rt_ctx* c) {
     c->d_sink.release();
     c->g_cam.grids.release(); c->g_cam.cell_start.release(); c->g_cam.entries.release();
     c->g_lit.grids.release(); c->g_lit.cell_start.release(); c->g_lit.entries.release();
-    c->g_cursor.release(); c->g_scan.release(); c->d_filter_tiles.release(); c->g3_cell_start.release(); c->g3_entries.release();
+    c->g_cursor.release(); c->g_scan.release(); c->d_filter_tiles.release(); c->g3_cell_start.release(); c->g3_entries.release(); c->d_aabb.release();
     c->w_acc.release(); c->w_refl.release(); c->w_P.release(); c->w_Nm.release(); c->w_Rc.release(); c->w_out.release();
     for (int i = 0; i < 2; ++i) { c->w_qs[i].release(); c->w_qd[i].release(); c->w_qpath[i].release(); }
     c->w_res_t.release(); c->w_res_id.release(); c->w_counts.release();

@@ -80,88 +80,61 @@ __global__ void __launch_bounds__(kB) pgrid_sort(const uint32_t* __restrict__ ce
     }
 }
 
-// ---- uniform 3-D grid (rt_grid3.cuh): one thread per object, the cells its conservative bounding sphere's box touches
+// ---- uniform 3-D grid (rt_grid3.cuh): one thread per object, the cells its conservative (noise-inflated) box touches
 template <bool FILL>
-__global__ void __launch_bounds__(kB) grid3_scatter(const Grid3 g, const CullRec* __restrict__ cull, const uint32_t n_objs, const float omax,
-                                                    uint32_t* __restrict__ cursor, const uint32_t* __restrict__ cell_start, Grid3Entry* __restrict__ entries) {
+__global__ void __launch_bounds__(kB) grid3_scatter(const Grid3 g, const CullRec* __restrict__ cull, const float4* __restrict__ aabb, const uint32_t n_objs,
+                                                    uint32_t* __restrict__ cursor, const uint32_t* __restrict__ cell_start, uint32_t* __restrict__ entries) {
     const uint32_t obj = blockIdx.x * kB + threadIdx.x;
     if (obj >= n_objs) return;
     const CullRec cr = cull[obj];
-    float r;
-    if (!grid3_object_sphere(cr, omax, g.eps, r)) return;
+    const float4 hb = aabb[obj];
     int lo[3], hi[3];
-    grid3_object_cells(g, cr, r, lo, hi);
-    Grid3Entry en;
-    en.cx = cr.cx; en.cy = cr.cy; en.cz = cr.cz; en.r2 = cr.r2; en.h = cr.h;
-    en.obj = obj; en.type = cr.type; en.pad = 0u;
+    if (!grid3_object_cells(g, cr, hb.x, hb.y, hb.z, hb.w, lo, hi)) return;
     for (int z = lo[2]; z <= hi[2]; ++z)
         for (int y = lo[1]; y <= hi[1]; ++y)
             for (int x = lo[0]; x <= hi[0]; ++x) {
                 const uint32_t cell = ((uint32_t)z * g.ny + (uint32_t)y) * g.nx + (uint32_t)x;
                 const uint32_t k = atomicAdd(cursor + cell, 1u);
-                if (FILL) entries[cell_start[cell] + k] = en;
+                if (FILL) entries[cell_start[cell] + k] = obj;
             }
 }
 
 // One thread per cell: ascending object index (deterministic whatever order the atomics ran in).
-__global__ void __launch_bounds__(kB) grid3_sort(const uint32_t* __restrict__ cell_start, const uint32_t n_cells, Grid3Entry* __restrict__ entries) {
+__global__ void __launch_bounds__(kB) grid3_sort(const uint32_t* __restrict__ cell_start, const uint32_t n_cells, uint32_t* __restrict__ entries) {
     const uint32_t c = blockIdx.x * kB + threadIdx.x;
     if (c >= n_cells) return;
     const uint32_t b = cell_start[c], n = cell_start[c + 1] - b;
-    Grid3Entry* e = entries + b;
-    if (n <= 48u) {
-        for (uint32_t i = 1; i < n; ++i) {
-            const Grid3Entry x = e[i];
-            uint32_t j = i;
-            while (j > 0 && x.obj < e[j - 1].obj) {
-                e[j] = e[j - 1];
-                --j;
-            }
-            e[j] = x;
+    uint32_t* e = entries + b;
+    for (uint32_t i = 1; i < n; ++i) {  // lists are short by construction (the builder rejects grids with long ones)
+        const uint32_t x = e[i];
+        uint32_t j = i;
+        while (j > 0 && x < e[j - 1]) {
+            e[j] = e[j - 1];
+            --j;
         }
-        return;
-    }
-    auto sift = [&](uint32_t start, uint32_t end) {
-        uint32_t root = start;
-        for (;;) {
-            uint32_t child = 2 * root + 1;
-            if (child >= end) break;
-            if (child + 1 < end && e[child].obj < e[child + 1].obj) ++child;
-            if (!(e[root].obj < e[child].obj)) break;
-            const Grid3Entry t = e[root];
-            e[root] = e[child];
-            e[child] = t;
-            root = child;
-        }
-    };
-    for (uint32_t s = n / 2; s-- > 0;) sift(s, n);
-    for (uint32_t end = n - 1; end > 0; --end) {
-        const Grid3Entry t = e[0];
-        e[0] = e[end];
-        e[end] = t;
-        sift(0, end);
+        e[j] = x;
     }
 }
 
 }  // namespace
 
-cudaError_t grid3_count(const Grid3& g, const CullRec* d_cull, uint32_t n_objs, float omax, uint32_t* d_cursor, uint32_t* d_cell_start,
+cudaError_t grid3_count(const Grid3& g, const CullRec* d_cull, const float4* d_aabb, uint32_t n_objs, uint32_t* d_cursor, uint32_t* d_cell_start,
                         void* scan_tmp, size_t scan_bytes, cudaStream_t stream) {
     const uint32_t n_cells = g.nx * g.ny * g.nz;
     cudaError_t e = cudaMemsetAsync(d_cursor, 0, sizeof(uint32_t) * ((size_t)n_cells + 1), stream);
     if (e != cudaSuccess) return e;
-    if (n_objs) grid3_scatter<false><<<(n_objs + kB - 1) / kB, kB, 0, stream>>>(g, d_cull, n_objs, omax, d_cursor, nullptr, nullptr);
+    if (n_objs) grid3_scatter<false><<<(n_objs + kB - 1) / kB, kB, 0, stream>>>(g, d_cull, d_aabb, n_objs, d_cursor, nullptr, nullptr);
     e = cub::DeviceScan::ExclusiveSum(scan_tmp, scan_bytes, d_cursor, d_cell_start, (int)(n_cells + 1), stream);
     if (e != cudaSuccess) return e;
     return cudaGetLastError();
 }
 
-cudaError_t grid3_fill(const Grid3& g, const CullRec* d_cull, uint32_t n_objs, float omax, uint32_t* d_cursor, const uint32_t* d_cell_start,
-                       Grid3Entry* d_entries, cudaStream_t stream) {
+cudaError_t grid3_fill(const Grid3& g, const CullRec* d_cull, const float4* d_aabb, uint32_t n_objs, uint32_t* d_cursor, const uint32_t* d_cell_start,
+                       uint32_t* d_entries, cudaStream_t stream) {
     const uint32_t n_cells = g.nx * g.ny * g.nz;
     cudaError_t e = cudaMemsetAsync(d_cursor, 0, sizeof(uint32_t) * ((size_t)n_cells + 1), stream);
     if (e != cudaSuccess) return e;
-    if (n_objs) grid3_scatter<true><<<(n_objs + kB - 1) / kB, kB, 0, stream>>>(g, d_cull, n_objs, omax, d_cursor, d_cell_start, d_entries);
+    if (n_objs) grid3_scatter<true><<<(n_objs + kB - 1) / kB, kB, 0, stream>>>(g, d_cull, d_aabb, n_objs, d_cursor, d_cell_start, d_entries);
     if (n_cells) grid3_sort<<<(n_cells + kB - 1) / kB, kB, 0, stream>>>(d_cell_start, n_cells, d_entries);
     return cudaGetLastError();
 }

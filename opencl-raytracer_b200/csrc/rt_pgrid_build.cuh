@@ -19,10 +19,11 @@ cudaError_t pgrid_count(const PGrid* d_grids, uint32_t n_grids, uint32_t n_cells
 cudaError_t pgrid_fill(const PGrid* d_grids, uint32_t n_grids, uint32_t n_cells, const CullRec* d_cull, uint32_t n_objs, float omax,
                        uint32_t* d_cursor, const uint32_t* d_cell_start, GridEntry* d_entries, cudaStream_t stream);
 
-// The uniform 3-D grid (rt_grid3.cuh), same two passes; g.cell_start / g.entries are not read.
-cudaError_t grid3_count(const Grid3& g, const CullRec* d_cull, uint32_t n_objs, float omax, uint32_t* d_cursor, uint32_t* d_cell_start,
+// The uniform 3-D grid (rt_grid3.cuh), same two passes; g.cell_start / g.entries are not read.  d_aabb: per object the
+// noise-inflated half extents (HostScene::aabb).
+cudaError_t grid3_count(const Grid3& g, const CullRec* d_cull, const float4* d_aabb, uint32_t n_objs, uint32_t* d_cursor, uint32_t* d_cell_start,
                         void* scan_tmp, size_t scan_bytes, cudaStream_t stream);
-cudaError_t grid3_fill(const Grid3& g, const CullRec* d_cull, uint32_t n_objs, float omax, uint32_t* d_cursor, const uint32_t* d_cell_start,
-                       Grid3Entry* d_entries, cudaStream_t stream);
+cudaError_t grid3_fill(const Grid3& g, const CullRec* d_cull, const float4* d_aabb, uint32_t n_objs, uint32_t* d_cursor, const uint32_t* d_cell_start,
+                       uint32_t* d_entries, cudaStream_t stream);
 
 }  // namespace rt

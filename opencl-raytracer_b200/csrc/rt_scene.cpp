@@ -419,6 +419,7 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
     out.mv.resize(4 * (size_t)n_objs);
     out.mat.resize(3 * (size_t)n_objs);
     out.cull.resize(n_objs);
+    out.aabb.assign(n_objs, F4{0.f, 0.f, 0.f, -1.f});
     out.lights.resize(4 * (size_t)n_lights);
 
     for (uint32_t i = 0; i < n_lights; ++i) {
@@ -592,6 +593,10 @@ int build_scene(const rt_object* objs, uint32_t n_objs, const rt_light* lights, 
         b.R = (g.R * (1.0 + 1e-6) + pad) * rscale;
         b.g = gg;
         b.f = ff;
+        {
+            const double infl = ff * (omax + cn) * 1.0001;
+            out.aabb[i] = F4{up(b.half[0] + infl + 2.0 * U * cn), up(b.half[1] + infl + 2.0 * U * cn), up(b.half[2] + infl + 2.0 * U * cn), 1.f};
+        }
         cr.cx = (float)g.c[0];
         cr.cy = (float)g.c[1];
         cr.cz = (float)g.c[2];

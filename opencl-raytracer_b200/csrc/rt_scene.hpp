@@ -31,6 +31,8 @@ struct HostScene {
     std::vector<F4> mv;    // 4 per object
     std::vector<F4> mat;   // 3 per object
     std::vector<CullRec> cull;
+    std::vector<F4> aabb;  // per object: half extents of its box INCLUDING the noise inflation f * (omax + |c|) a ray from anywhere
+                           // in the scene can need (the uniform grid enters objects by this box; w unused); zeros = never hit
     std::vector<BvhNode> nodes;
     std::vector<uint32_t> leaf_obj;
     std::vector<CullRec> leaf_cull;

@@ -535,7 +535,7 @@ __global__ void __launch_bounds__(kBlock, RT_GRID_MINB) wave_trace_grid(const Sc
 // exact tests.  An iteration of the walk loop moves a lane whose list is used up into the next cell AND tests one entry, so
 // the two short code paths do not alternate between warp votes.
 #ifndef RT_DDA_MINB
-#define RT_DDA_MINB 3
+#define RT_DDA_MINB 4  // 64 registers: the walk is latency bound, a fourth resident CTA is worth 9 % (27.2 -> 24.9 ms per frame; 5: 25.8)
 #endif
 template <bool COUNT>
 __global__ void __launch_bounds__(kBlock, RT_DDA_MINB) wave_trace_dda(const Scene sc, const Grid3 g, const TaskQueue q, const uint32_t* __restrict__ n_ptr,
@@ -546,32 +546,33 @@ __global__ void __launch_bounds__(kBlock, RT_DDA_MINB) wave_trace_dda(const Scen
     const unsigned lane = threadIdx.x & 31u;
     LocalCounters lc;
     const uint32_t kNone = 0xffffffffu;
+    const float4* cull4 = reinterpret_cast<const float4*>(sc.cull);
 
-    bool have = false, anyhit = false, done = false;
+    int st = 0;  // 0 idle, 1 walking, 2 walk finished
+    bool anyhit = false;
     uint32_t at = 0;
     float ox = 0.f, oy = 0.f, oz = 0.f, ux = 0.f, uy = 0.f, uz = 0.f;
     Dda w;
-    w.ix = w.iy = w.iz = w.bx = w.by = w.bz = w.hx = w.hy = w.hz = w.t_end = 0.f;
-    w.cx = w.cy = w.cz = w.sx = w.sy = w.sz = 0;
+    w.tmx = w.tmy = w.tmz = w.dtx = w.dty = w.dtz = w.t_end = 0.f;
+    w.rx = w.ry = w.rz = w.lx = w.ly = w.lz = 0;
+    w.cell = 0u;
     Hit best;
     best.t = RT_MAX_FLOAT;
     best.id = -1;
     uint32_t btype = 0, cur = 0, end = 0, pend = kNone, ptype = 0;
-    uint32_t mb0 = kNone, mb1 = kNone, mb2 = kNone, mb3 = kNone;  // the last objects this ray ran the exact test on
-    float4 ea = make_float4(0.f, 0.f, 0.f, 0.f), eb = ea;         // the list entry at `cur`, fetched one step ahead
-    const float4* ent4 = reinterpret_cast<const float4*>(g.entries);
+    uint32_t mb0 = kNone, mb1 = kNone, mb2 = kNone;  // the last objects this ray ran the exact test on
     bool exhausted = false;
 
     for (;;) {
         // ---- refill
         {
-            const unsigned idle = __ballot_sync(kFull, !have);
-            const unsigned walk = __ballot_sync(kFull, have && pend == kNone && !done);
+            const unsigned idle = __ballot_sync(kFull, st == 0);
+            const unsigned walk = __ballot_sync(kFull, st == 1 && pend == kNone);
             if (idle && !exhausted && (__popc(idle) >= refill_t || walk == 0u)) {
                 uint32_t base = 0;
                 if (lane == 0) base = atomicAdd(fetch, (uint32_t)__popc(idle));
                 base = __shfl_sync(kFull, base, 0);
-                if (!have) {
+                if (st == 0) {
                     const uint32_t i = base + (uint32_t)__popc(idle & lanemask_lt());
                     if (i < n) {
                         at = i;
@@ -583,9 +584,8 @@ __global__ void __launch_bounds__(kBlock, RT_DDA_MINB) wave_trace_dda(const Scen
                         best.id = -1;
                         btype = 0;
                         pend = kNone;
-                        mb0 = mb1 = mb2 = mb3 = kNone;
-                        have = true;
-                        done = false;
+                        mb0 = mb1 = mb2 = kNone;
+                        st = 1;
                         cur = end = 0;
                         const float chk = ray.s.x + ray.s.y + ray.s.z + ray.d.x + ray.d.y + ray.d.z;
                         if (!(fabsf(chk) < __int_as_float(0x7f800000))) {
@@ -594,71 +594,59 @@ __global__ void __launch_bounds__(kBlock, RT_DDA_MINB) wave_trace_dda(const Scen
                                 exact_pair_call(sc, ray.s, ray.d, k, __ldg(&sc.cull[k].type), best, btype);
                                 if (COUNT) lc.exact_tests++;
                             }
-                            done = true;
+                            st = 2;
                         } else if (!dda_start(g, ray, anyhit ? 1.f : RT_MAX_FLOAT, w)) {
-                            done = true;  // misses the grid
+                            st = 2;  // misses the grid
                         } else {
                             ox = ray.s.x; oy = ray.s.y; oz = ray.s.z;
                             const float l = sqrtf(fmaf(ray.d.z, ray.d.z, fmaf(ray.d.y, ray.d.y, ray.d.x * ray.d.x)));
                             const float il = 1.f / l;
                             ux = ray.d.x * il; uy = ray.d.y * il; uz = ray.d.z * il;
-                            const uint32_t cell = dda_cell(g, w);
-                            cur = __ldg(g.cell_start + cell);
-                            end = __ldg(g.cell_start + cell + 1);
+                            cur = __ldg(g.cell_start + w.cell);
+                            end = __ldg(g.cell_start + w.cell + 1);
                             if (COUNT) lc.node_visits++;
-                            if (cur < end) {
-                                ea = __ldg(ent4 + 2 * (size_t)cur);
-                                eb = __ldg(ent4 + 2 * (size_t)cur + 1);
-                            }
                         }
                     }
                 }
                 if (base + (uint32_t)__popc(idle) >= n) exhausted = true;
             }
-            if (!__any_sync(kFull, have)) break;
+            if (!__any_sync(kFull, st != 0)) break;
         }
 
-        // ---- walk
+        // ---- walk: a lane whose list is used up moves on by one cell (a dozen instructions), then every lane with an entry
+        // left tests one
         for (;;) {
-            const bool go = have && pend == kNone && !done;
+            const bool go = st == 1 && pend == kNone;
             const unsigned T = __ballot_sync(kFull, go);
             if (T == 0u) break;
             if (__popc(T) < min_t) {
-                if (__popc(__ballot_sync(kFull, have && pend != kNone)) >= drain_t) break;
-                if (!exhausted && __popc(__ballot_sync(kFull, !have || (pend == kNone && done))) >= refill_t) break;
+                if (__popc(__ballot_sync(kFull, pend != kNone)) >= drain_t) break;
+                if (!exhausted && __popc(__ballot_sync(kFull, st == 0 || (st == 2 && pend == kNone))) >= refill_t) break;
             }
             if (go) {
                 if (cur >= end) {  // next cell
-                    int axis;
-                    const float t_exit = dda_exit(w, axis);
-                    // every object whose hit point lies before the exit of the cell just finished has been seen
-                    if ((best.id >= 0 && best.t < t_exit * (1.f - 1e-5f)) || t_exit > w.t_end || !dda_step(g, w, axis)) {
-                        done = true;
+                    bool out;
+                    const float t_exit = dda_advance(w, out);
+                    // every object whose hit point lies before the exit of the cell just left has been seen
+                    if ((best.id >= 0 && best.t < t_exit * (1.f - 1e-5f)) || t_exit > w.t_end || out) {
+                        st = 2;
                     } else {
-                        const uint32_t cell = dda_cell(g, w);
-                        cur = __ldg(g.cell_start + cell);
-                        end = __ldg(g.cell_start + cell + 1);
+                        cur = __ldg(g.cell_start + w.cell);
+                        end = __ldg(g.cell_start + w.cell + 1);
                         if (COUNT) lc.node_visits++;
-                        if (cur < end) {
-                            ea = __ldg(ent4 + 2 * (size_t)cur);
-                            eb = __ldg(ent4 + 2 * (size_t)cur + 1);
-                        }
                     }
-                } else {  // one entry: the record fetched last time round, the next one is requested before it is looked at
-                    const float4 a = ea, b = eb;
+                }
+                if (st == 1 && cur < end) {
+                    const uint32_t obj = __ldg(g.entries + cur);
                     ++cur;
-                    if (cur < end) {
-                        ea = __ldg(ent4 + 2 * (size_t)cur);
-                        eb = __ldg(ent4 + 2 * (size_t)cur + 1);
-                    }
+                    const float4 a = __ldg(cull4 + 2 * (size_t)obj), b = __ldg(cull4 + 2 * (size_t)obj + 1);
                     if (COUNT) lc.pair_tests++;
                     const float x = a.x - ox, y = a.y - oy, z = a.z - oz;
                     const float oc2 = fmaf(z, z, fmaf(y, y, x * x));
                     const float dt = fmaf(z, uz, fmaf(y, uy, x * ux));
-                    const uint32_t obj = __float_as_uint(b.y);
-                    if (!(fmaf(-dt, dt, oc2 * b.x) > a.w) && obj != mb0 && obj != mb1 && obj != mb2 && obj != mb3) {  // cv::sphere_may_hit
+                    if (!(fmaf(-dt, dt, oc2 * b.x) > a.w) && obj != mb0 && obj != mb1 && obj != mb2) {  // cv::sphere_may_hit
                         pend = obj;
-                        ptype = __float_as_uint(b.z);
+                        ptype = __float_as_uint(b.w);
                     }
                 }
             }
@@ -666,25 +654,25 @@ __global__ void __launch_bounds__(kBlock, RT_DDA_MINB) wave_trace_dda(const Scen
 
         // ---- exact tests: when enough lanes hold a survivor, or nobody can walk on
         {
-            const bool has = have && pend != kNone;
+            const bool has = pend != kNone;
             const unsigned P = __ballot_sync(kFull, has);
-            const unsigned W = __ballot_sync(kFull, have && pend == kNone && !done);
+            const unsigned W = __ballot_sync(kFull, st == 1 && pend == kNone);
             if (P != 0u && (__popc(P) >= drain_t || W == 0u)) {
                 if (has) {
                     exact_pair_call(sc, q.s[at], q.d[at], pend, ptype, best, btype);
                     if (COUNT) lc.exact_tests++;
-                    mb3 = mb2; mb2 = mb1; mb1 = mb0; mb0 = pend;
+                    mb2 = mb1; mb1 = mb0; mb0 = pend;
                     pend = kNone;
-                    if (anyhit && best.t < 1.f) done = true;  // the shadow ray is decided (SAR:229)
+                    if (anyhit && best.t < 1.f) st = 2;  // the shadow ray is decided (SAR:229)
                 }
             }
         }
 
         // ---- retire
-        if (have && pend == kNone && done) {
+        if (st == 2 && pend == kNone) {
             res_t[at] = best.id >= 0 ? best.t : RT_MAX_FLOAT;
             res_id[at] = best.id;
-            have = false;
+            st = 0;
         }
     }
     if (COUNT) flush_local(lc, ctr);

@@ -85,26 +85,24 @@ struct HostGrids {
     }
 };
 
-// Host stand-in for the device builder of the uniform 3-D grid (rt_pgrid.cu), same per-object functions.
+// Host stand-in for the device builder of the uniform 3-D grid (rt_pgrid.cu), same per-object function.
 struct HostGrid3 {
-    std::vector<uint32_t> cell_start;
-    std::vector<rt::Grid3Entry> entries;
+    std::vector<uint32_t> cell_start, entries;
     rt::Grid3 g{};
     void build(const rt::HostScene& hs, float cells_per_object) {
         double lo[3] = {1e30, 1e30, 1e30}, hi[3] = {-1e30, -1e30, -1e30};
         uint32_t live = 0;
-        std::vector<float> rad(hs.n_objs, -1.f);
         const float ext0 = 2.f * hs.scene_radius + 1.f;
         const float eps = 2e-5f * ext0 + 1e-4f;
         for (uint32_t o = 0; o < hs.n_objs; ++o) {
-            float r;
-            if (!rt::grid3_object_sphere(hs.cull[o], hs.omax, eps, r)) continue;
-            rad[o] = r;
+            const rt::F4& hb = hs.aabb[o];
+            if (hb.w < 0.f || hs.cull[o].r2 < 0.f) continue;
             ++live;
             const float c[3] = {hs.cull[o].cx, hs.cull[o].cy, hs.cull[o].cz};
+            const float half[3] = {hb.x, hb.y, hb.z};
             for (int k = 0; k < 3; ++k) {
-                lo[k] = std::min(lo[k], (double)c[k] - r);
-                hi[k] = std::max(hi[k], (double)c[k] + r);
+                lo[k] = std::min(lo[k], (double)c[k] - half[k] - eps);
+                hi[k] = std::max(hi[k], (double)c[k] + half[k] + eps);
             }
         }
         if (!live) return;
@@ -122,9 +120,9 @@ struct HostGrid3 {
         const uint32_t cells = g.nx * g.ny * g.nz;
         std::vector<std::vector<uint32_t>> lists(cells);
         for (uint32_t o = 0; o < hs.n_objs; ++o) {
-            if (rad[o] < 0.f) continue;
             int l[3], u[3];
-            rt::grid3_object_cells(g, hs.cull[o], rad[o], l, u);
+            const rt::F4& hb = hs.aabb[o];
+            if (!rt::grid3_object_cells(g, hs.cull[o], hb.x, hb.y, hb.z, hb.w, l, u)) continue;
             for (int z = l[2]; z <= u[2]; ++z)
                 for (int y = l[1]; y <= u[1]; ++y)
                     for (int x = l[0]; x <= u[0]; ++x) lists[((uint32_t)z * g.ny + y) * g.nx + x].push_back(o);
@@ -132,12 +130,9 @@ struct HostGrid3 {
         cell_start.assign(cells + 1, 0);
         for (uint32_t c = 0; c < cells; ++c) {
             cell_start[c + 1] = cell_start[c] + (uint32_t)lists[c].size();
-            for (uint32_t o : lists[c]) {
-                const rt::CullRec& cr = hs.cull[o];
-                entries.push_back(rt::Grid3Entry{cr.cx, cr.cy, cr.cz, cr.r2, cr.h, o, cr.type, 0u});
-            }
+            entries.insert(entries.end(), lists[c].begin(), lists[c].end());
         }
-        if (entries.empty()) entries.push_back(rt::Grid3Entry{});
+        if (entries.empty()) entries.push_back(0);
         g.cell_start = cell_start.data();
         g.entries = entries.data();
         g.valid = 1;

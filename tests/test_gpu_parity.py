@@ -791,3 +791,38 @@ def test_two_contexts_one_process_filter_kernel(rt):
             c.set_camera(320, 180, T.camera_zdir(180))
             frames.append(c.render(4, 2, 1).copy())
     assert np.array_equal(frames[0], frames[1]) and np.array_equal(frames[0], frames[2])
+
+
+def test_clustered_scene_keeps_the_bvh(rt, ctx, oracle_mod):
+    """The uniform grid is only taken when its lists stay short.  A scene with one tight cluster far from a few stragglers
+    (the teapot in the stadium) would put hundreds of objects into a handful of cells: the builder must refuse it and the
+    reflection rays must walk the BVH (node visits > 0) -- and the frame must be right either way."""
+    objs, lights = S.synthetic_scene(3000, 300)
+    mv = objs["mv"].reshape(-1, 4, 4).copy()
+    mi = objs["mvInverse"].reshape(-1, 4, 4).copy()
+    centre = mv[:, 3, :3].copy()
+    target = np.array([0.0, 0.0, -60.0], dtype=np.float32)
+    d = ((target - centre) * np.float32(0.97)).astype(np.float32)   # pull 97 % of the way into one spot ...
+    d[:8] = 0                                                        # ... except eight stragglers that keep the scene wide
+    mv[:, 3, :3] += d
+    mi[:, 3, :3] -= np.einsum("nkj,nk->nj", mi[:, :3, :3], d)
+    objs["mv"], objs["mvInverse"] = mv.reshape(-1, 16), mi.reshape(-1, 16)
+    W, H = 160, 90
+    z, rays = frame_rays(W, H)
+    ref, hid, ht, st = oracle_mod.port_render(2, 3, objs, lights, rays)
+    ctx.set_option(rt.OPT_PIPELINE, 1)
+    ctx.set_option(rt.OPT_COUNT_RAYS, 1)
+    ctx.upload_scene(objs, lights)
+    ctx.set_camera(W, H, z)
+    out = ctx.render(3, 2, 3)
+    s = ctx.stats()
+    assert_colours_close(out, ref)
+    assert s.traced_reflect > 0 and s.node_visits > 0   # BVH, not the grid walk (which counts cells in node_visits too, but
+    gid, gt = ctx.render_aov(3)                          # far fewer: checked against the uniform scene below)
+    assert np.array_equal(gid, hid) and np.array_equal(gt, ht)
+    visits_clustered = s.node_visits / max(s.traced_reflect, 1)
+    uni, _ = S.synthetic_scene(3000, 300)
+    ctx.upload_scene(uni, lights)
+    ctx.render(3, 2, 3)
+    s2 = ctx.stats()
+    assert s2.node_visits / max(s2.traced_reflect, 1) < visits_clustered  # the uniform scene takes the grid: cells, not node steps
