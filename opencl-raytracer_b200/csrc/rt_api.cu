@@ -702,22 +702,20 @@ int ensure_wave_buffers(rt_ctx* c, uint64_t capacity, uint32_t gens, int n_seq, 
     return RT_OK;
 }
 
-// How many launch sequences a camera render is cut into (wavefront pipeline).  The frame -- or this context's shard of it --
-// is split into bands of rows / owned row-blocks, and ALL bands are enqueued at once, each on its own stream, the streams in
-// descending priority: band 0's blocks are scheduled first, the blocks of the later bands move into every slot it leaves free
-// -- the thin tail of each of its generations, the latency-bound last generations -- and the bands finish roughly in order.
-// rt_render copies a band to the host as soon as it is done, under the kernels of the bands still running.  (Round 1 ran
-// the bands one after the other, two lanes each: every band paid the ~2 ms of its thin generations again.)  Measured on the
-// 8K cfg5 frame (profiles/r2_sweep_bands.txt): kernels alone 33.0 ms with 2 sequences, 33.6 with 1, 34.3 with 6; end to end
-// 42.3 (2: both finish together, the whole 9.4 ms copy is exposed) / 37.5 (4) / 36.9 (6) / 37.9 (8).  Stream priorities do
-// not order persistent kernels -- a resident low-priority CTA runs until its queue is empty -- and starting band k only
-// after the heavy generations of band k - 1 (an event chain) ordered the bands but cost more kernel time than it hid copy
-// (38.2 ms at 4 bands).  With the tail launch (wave_tail) 4 bands measure best: 36.4 ms end to end.  Hence: 4 bands when the frame goes to the host, 2 otherwise.
+// How a camera render is cut into launch sequences (wavefront pipeline).
+//  * Frame stays on the device (rt_render_device): 2 concurrent sequences (lanes) on two streams -- the blocks of one fill the
+//    thin generation tails of the other.
+//  * Frame goes to the host (rt_render): bands of rows / owned row-blocks ONE AFTER THE OTHER, each as two lanes; a finished
+//    band is copied (copy stream) under the kernels of the next one, so the bands shrink geometrically and only the small last
+//    copy is exposed.  Measured on the 8K cfg5 frame, kernels 24.9 ms, copy 9.4 ms (profiles/r2_sweep_bands.txt): 28.2 ms end
+//    to end with 4 bands shrinking by 3.5 (no copy at all: 27.6 -- what is left is the fixed cost of four sequences, not the
+//    copy); all bands concurrent on their own streams (RT_BAND_MODE=0): 29.1 ms -- stream priorities do not order persistent
+//    kernels, the bands finish together and 3.2 ms of copy stay exposed; an SM copy kernel into the mapped frame instead of the
+//    copy engine: 35.7 ms; an event chain that starts band k after the heavy generations of band k - 1: slower still.
 int auto_sequences(const rt_ctx* c, bool to_host, bool aov_only) {
     if (!c->use_camera || aov_only) return 1;
     const uint64_t px = local_pixels(c);
-    // to the host: 4 bands for 12 Mpixel and more, 2 below (tools/sweep_shard_bands.py, profiles/r2_sweep_shard_bands.txt: the
-    // 1/4 and 1/8 shards of the 8K frame gain nothing from more than 2, and every band is a dozen more launches per rank)
+    // (concurrent layout) to the host: 4 bands for 12 Mpixel and more, 2 below
     int n = to_host && c->opt_bands > 0 ? c->opt_bands : (c->opt_lanes > 0 ? c->opt_lanes : (to_host && px >= (12ull << 20) ? 4 : 2));
     n = std::min(n, rt_ctx::kMaxBands);
     while (n > 1 && (px / n < (1ull << 19) || band_units(c) < (uint32_t)(4 * n))) --n;  // at least 0.5 Mpixel and 4 units per band
@@ -764,34 +762,71 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
     if (pipeline == 1) {
         const uint32_t gens = rt::wave_max_generations(max_bounces, c->scene.n_lights, mode);
         if (gens > kMaxWaveGenerations) return fail(RT_ERR_INVALID, "max_bounces x lights too large for the wavefront pipeline; use RT_OPT_PIPELINE 0");
-        const int n_seq = auto_sequences(c, host_out != nullptr, aov_only);
+        // ---- the launch plan: bands (units [b0, b1) of the frame, copied to the host as a whole) made of lanes (launch sequences)
+        struct Seq {
+            uint32_t u0, u1;
+            int stream, band;
+        };
+        Seq seq[rt_ctx::kMaxBands];
+        uint32_t band_u[rt_ctx::kMaxBands + 1];
+        int n_seq = 0;
+        const uint32_t units = c->use_camera ? band_units(c) : 0u;
+        const uint64_t unit_px = (uint64_t)c->width * (c->n_shards <= 1 ? 1u : c->block_rows);
+        static const int band_mode_env = [] {
+            const char* v = getenv("RT_BAND_MODE");
+            return v && *v ? atoi(v) : -1;
+        }();
+        static const double band_ratio_env = [] {
+            const char* v = getenv("RT_BAND_RATIO");
+            return v && *v ? atof(v) : 0.0;
+        }();
+        const bool sequential = host_out != nullptr && c->use_camera && !aov_only && (band_mode_env < 0 ? true : band_mode_env == 1);
+        if (sequential) {
+            // bands one after the other, each as two lanes on two streams; the copy of band b runs under the kernels of band
+            // b + 1, so the bands shrink geometrically by (copy time : kernel time) and only the small last copy is exposed
+            int nb = c->opt_bands > 0 ? c->opt_bands : (local_pixels(c) >= (12ull << 20) ? 4 : 2);
+            nb = std::min(nb, rt_ctx::kMaxBands / 2);
+            while (nb > 1 && units < (uint32_t)(4 * nb)) --nb;
+            const double ratio = band_ratio_env > 0.0 ? band_ratio_env : (nb >= 4 ? 3.5 : 2.5);
+            band_u[0] = 0;
+            for (int b = 0; b < nb; ++b) {
+                uint32_t u0, u1;
+                plan_band(units, b, nb, ratio, &u0, &u1);
+                band_u[b + 1] = u1;
+                const int lanes = c->opt_lanes == 1 ? 1 : ((u1 - u0) >= 8 && (uint64_t)(u1 - u0) * unit_px >= (1ull << 20) ? 2 : 1);
+                for (int l = 0; l < lanes; ++l) {
+                    seq[n_seq].u0 = u0 + (uint32_t)((uint64_t)(u1 - u0) * l / lanes);
+                    seq[n_seq].u1 = u0 + (uint32_t)((uint64_t)(u1 - u0) * (l + 1) / lanes);
+                    seq[n_seq].stream = l;
+                    seq[n_seq].band = b;
+                    ++n_seq;
+                }
+            }
+        } else {
+            // concurrent equal bands, one stream each
+            n_seq = auto_sequences(c, host_out != nullptr, aov_only);
+            for (int k = 0; k < n_seq; ++k) {
+                seq[k].u0 = (uint32_t)((uint64_t)units * k / n_seq);
+                seq[k].u1 = (uint32_t)((uint64_t)units * (k + 1) / n_seq);
+                seq[k].stream = k;
+                seq[k].band = k;
+                band_u[k] = seq[k].u0;
+                band_u[k + 1] = seq[k].u1;
+            }
+        }
         static const int tail_env = [] {
             const char* v = getenv("RT_TAIL_GEN");
             return v && *v ? atoi(v) : -1;
         }();
-        // auto: the smaller a launch sequence, the earlier its generations are thin -- one, two or three bounce levels
-        // ((1 + lights) generations each) run as trace / advance pairs, one wave_tail launch finishes the rest.  Swept on the
-        // 8K cfg5 frame and its 1/2, 1/4, 1/8 shards (tools/sweep_tail.py, profiles/r2_sweep_tail.txt): 32.9 -> 32.4 ms whole,
-        // 17.5 -> 17.0, 9.8 -> 9.0, 5.9 -> 4.85 ms for the shard one of 8 GPUs renders.
-        int tail_gen = c->opt_tail_gen >= 0 ? c->opt_tail_gen : tail_env;
-        if (tail_gen < 0) {
-            const uint64_t px_seq = local_pixels(c) / (uint64_t)n_seq;
-            const int levels = px_seq >= (12ull << 20) ? 3 : px_seq >= (6ull << 20) ? 2 : 1;
-            tail_gen = levels * (1 + (int)c->scene.n_lights);
-        }
-        const uint32_t units = c->use_camera ? band_units(c) : 0u;
         rt::Frame fr[rt_ctx::kMaxBands];
         uint64_t offset[rt_ctx::kMaxBands], cap[rt_ctx::kMaxBands];
-        uint32_t ub[rt_ctx::kMaxBands + 1];
         uint64_t total = 0;
         for (int k = 0; k < n_seq; ++k) {
-            ub[k] = (uint32_t)((uint64_t)units * k / n_seq);
-            ub[k + 1] = (uint32_t)((uint64_t)units * (k + 1) / n_seq);
             if (c->use_camera)
-                fill_frame_desc(c, fr[k], max_bounces, mode, out, ub[k], ub[k + 1]);
+                fill_frame_desc(c, fr[k], max_bounces, mode, out, seq[k].u0, seq[k].u1);
             else
                 fill_frame_desc(c, fr[k], max_bounces, mode, out);
-            if (c->use_camera && ub[k + 1] == ub[k]) fr[k].n_local = 0;
+            if (c->use_camera && seq[k].u1 == seq[k].u0) fr[k].n_local = 0;
             if (aov_only) {
                 fr[k].hit_id = c->d_hit_id.p;
                 fr[k].hit_t = c->d_hit_t.p;
@@ -809,26 +844,48 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
         wg.g3 = c->g3;
         wg.filter_tiles = c->d_filter_tiles.p;
         RT_CUDA(cudaEventRecord(c->ev0, c->stream));  // every sequence starts after what was queued before this render
+        auto copy_rows = [&](uint64_t first, uint64_t cnt) -> cudaError_t {
+            return cudaMemcpyAsync(host_out + 4 * first, c->d_fb.p + first, cnt * sizeof(float4), cudaMemcpyDeviceToHost, c->copy_stream);
+        };
+        bool waited[rt_ctx::kMaxBands] = {};
         for (int k = 0; k < n_seq; ++k) {
-            cudaStream_t st = n_seq == 1 ? c->stream : c->seq_stream[k];
-            if (n_seq > 1) RT_CUDA(cudaStreamWaitEvent(st, c->ev0, 0));
+            cudaStream_t st = n_seq == 1 ? c->stream : c->seq_stream[seq[k].stream];
+            if (n_seq > 1 && !waited[seq[k].stream]) {
+                RT_CUDA(cudaStreamWaitEvent(st, c->ev0, 0));
+                waited[seq[k].stream] = true;
+            }
+            // auto tail: the smaller a launch sequence, the earlier its generations are thin.  Swept on the 8K cfg5 frame and its
+            // 1/2, 1/4, 1/8 shards (tools/sweep_tail.py, profiles/r2_sweep_tail.txt, two lights: 3 generations per bounce level):
+            // whole frame 25.2 (chain only) -> 24.8 ms with the tail from generation 9, half 13.6 -> 13.2 (9), quarter 7.9 -> 7.35 (7),
+            // eighth 4.87 -> 4.31 (4..7); too early a tail costs more than it saves (whole frame from generation 3: 30.7 ms) because
+            // the per-thread searches of wave_tail do not have the warp scheduling of the trace kernels.
+            int tail_gen = c->opt_tail_gen >= 0 ? c->opt_tail_gen : tail_env;
+            if (tail_gen < 0) {
+                const uint64_t px_seq = fr[k].n_local;
+                const int per_level = 1 + (int)c->scene.n_lights;
+                tail_gen = px_seq >= (6ull << 20) ? 3 * per_level : px_seq >= (1ull << 20) ? 2 * per_level + 1 : per_level + 1;
+            }
             uint32_t nl = 0;
             if (fr[k].n_local > 0) RT_CUDA(rt::wave_render(c->scene, fr[k], wb[k], accel, &wg, c->sm_count, &nl, st, tail_gen));
             c->last_launches += nl;
             if (n_seq > 1 || host_out) RT_CUDA(cudaEventRecord(c->band_done[k], st));
-            if (host_out && fr[k].n_local > 0) {  // the band's rows go home under the kernels of the bands behind it
-                RT_CUDA(cudaStreamWaitEvent(c->copy_stream, c->band_done[k], 0));
+            const bool band_complete = k + 1 == n_seq || seq[k + 1].band != seq[k].band;
+            if (host_out && band_complete) {  // the band's rows go home under the kernels of the bands behind it
+                for (int j = k; j >= 0 && seq[j].band == seq[k].band; --j) RT_CUDA(cudaStreamWaitEvent(c->copy_stream, c->band_done[j], 0));
+                const uint32_t b0 = c->use_camera ? band_u[seq[k].band] : 0u, b1 = c->use_camera ? band_u[seq[k].band + 1] : 0u;
                 if (!c->use_camera) {
-                    RT_CUDA(cudaMemcpyAsync(host_out, c->d_fb.p, c->n_rays * sizeof(float4), cudaMemcpyDeviceToHost, c->copy_stream));
+                    if (c->n_rays) RT_CUDA(cudaMemcpyAsync(host_out, c->d_fb.p, c->n_rays * sizeof(float4), cudaMemcpyDeviceToHost, c->copy_stream));
+                } else if (b1 == b0) {
+                    // empty band
                 } else if (c->n_shards <= 1) {
-                    const uint64_t first = (uint64_t)ub[k] * c->width, cnt = (uint64_t)(ub[k + 1] - ub[k]) * c->width;
-                    RT_CUDA(cudaMemcpyAsync(host_out + 4 * first, c->d_fb.p + first, cnt * sizeof(float4), cudaMemcpyDeviceToHost, c->copy_stream));
+                    const uint64_t first = (uint64_t)b0 * c->width, cnt = (uint64_t)(b1 - b0) * c->width;
+                    RT_CUDA(copy_rows(first, cnt));
                 } else {
-                    for (uint32_t u = ub[k]; u < ub[k + 1]; ++u) {
+                    for (uint32_t u = b0; u < b1; ++u) {
                         const uint32_t row = (c->shard + u * c->n_shards) * c->block_rows;
                         if (row >= c->height) break;
                         const uint64_t first = (uint64_t)row * c->width, cnt = (uint64_t)std::min(c->block_rows, c->height - row) * c->width;
-                        RT_CUDA(cudaMemcpyAsync(host_out + 4 * first, c->d_fb.p + first, cnt * sizeof(float4), cudaMemcpyDeviceToHost, c->copy_stream));
+                        RT_CUDA(copy_rows(first, cnt));
                     }
                 }
             }

@@ -1147,7 +1147,7 @@ __global__ void __launch_bounds__(kBlock, RT_ADV_MINB) wave_advance(const Scene 
 // path writes its pixel (the megakernel's per-ray searches: rt_device.cuh trace_bvh, rt_pgrid.cuh trace_grid; the same
 // wave::step as wave_advance, so the same bits).  Warps fetch 32 tasks at a time.
 template <bool COUNT>
-__global__ void __launch_bounds__(128) wave_tail(const Scene sc, const GridSet lit, const WaveParams wp, const PathArrays pa, const TaskQueue qin,
+__global__ void __launch_bounds__(128) wave_tail(const Scene sc, const GridSet lit, const Grid3 g3, const WaveParams wp, const PathArrays pa, const TaskQueue qin,
                                                   const uint32_t* __restrict__ n_in, uint32_t* __restrict__ fetch, float4* __restrict__ fb, Counters* ctr) {
     const uint32_t nb = n_in[0], na = n_in[1];
     const uint32_t n = nb + na;
@@ -1174,6 +1174,10 @@ __global__ void __launch_bounds__(128) wave_tail(const Scene sc, const GridSet l
             const uint32_t li = (pw >> RT_TASK_LIGHT_SHIFT) & 15u;
             if ((pw & RT_TASK_ANYHIT) && li != RT_TASK_NO_GRID)
                 res = trace_grid<true>(sc, lit, 6u * li, ray, COUNT ? &np : nullptr, COUNT ? &ne : nullptr);
+            else if (g3.valid && (pw & RT_TASK_ANYHIT))
+                res = trace_grid3<true>(sc, g3, ray, 1.f, COUNT ? &np : nullptr, COUNT ? &ne : nullptr, COUNT ? &nn : nullptr);
+            else if (g3.valid)
+                res = trace_grid3<false>(sc, g3, ray, RT_MAX_FLOAT, COUNT ? &np : nullptr, COUNT ? &ne : nullptr, COUNT ? &nn : nullptr);
             else if (pw & RT_TASK_ANYHIT)
                 res = trace_bvh<true>(sc, ray, 1.f, COUNT ? &ne : nullptr, COUNT ? &nn : nullptr);
             else
@@ -1275,10 +1279,11 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
         if (tail_gen > 0 && g >= (uint32_t)tail_gen && accel >= 2 && !fr.hit_id) {  // one launch finishes what is left
             const unsigned tgrid = (unsigned)sm_count * 8u;
             const GridSet lit = use_grids ? grids->lit : GridSet{};
+            const Grid3 g3 = use_grids ? grids->g3 : Grid3{};
             if (count)
-                wave_tail<true><<<tgrid, 128, 0, stream>>>(sc, lit, wp, wb.pa, qin, nq, fetch + 2 * g, fr.out, fr.counters);
+                wave_tail<true><<<tgrid, 128, 0, stream>>>(sc, lit, g3, wp, wb.pa, qin, nq, fetch + 2 * g, fr.out, fr.counters);
             else
-                wave_tail<false><<<tgrid, 128, 0, stream>>>(sc, lit, wp, wb.pa, qin, nq, fetch + 2 * g, fr.out, fr.counters);
+                wave_tail<false><<<tgrid, 128, 0, stream>>>(sc, lit, g3, wp, wb.pa, qin, nq, fetch + 2 * g, fr.out, fr.counters);
             ++nl;
             break;
         }
