@@ -395,7 +395,7 @@ __global__ void __launch_bounds__(kBlock, RT_BVH_MINB) wave_trace_bvh(const Scen
 // bounding-sphere filter, and a survivor waits for the warp's next round of exact tests.  Rays of one 8x4 pixel tile
 // share their cell, so a warp of primary rays walks its list in lockstep with broadcast loads.
 #ifndef RT_GRID_MINB
-#define RT_GRID_MINB 4
+#define RT_GRID_MINB 5  // 48 registers (4: 56); the list walk waits on L2, a fifth CTA is worth 0.4 ms per frame
 #endif
 template <bool COUNT>
 __global__ void __launch_bounds__(kBlock, RT_GRID_MINB) wave_trace_grid(const Scene sc, const GridSet cam, const GridSet lit, const TaskQueue q,
@@ -1079,7 +1079,8 @@ cudaError_t launch_filter(const Scene& sc, const TaskQueue& qin, const uint32_t*
 
 // ------------------------------------------------------------------------------------------------ advance
 #ifndef RT_ADV_MINB
-#define RT_ADV_MINB 3  // resident CTAs per SM the advance kernel is compiled for (80 registers; 2 and 4 measured slower)
+#define RT_ADV_MINB 4  // resident CTAs per SM the advance kernel is compiled for (64 registers; latency bound: 3 -> 4 is 24.9 -> 24.0 ms per
+                       // frame in round 2, 5 the same as 4)
 #endif
 template <bool COUNT>
 __global__ void __launch_bounds__(kBlock, RT_ADV_MINB) wave_advance(const Scene sc, const WaveParams wp, const PathArrays pa, const TaskQueue qin,
@@ -1269,7 +1270,7 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
     const unsigned dgrid = (unsigned)sm_count * RT_DDA_MINB;
     static const int d_min_t = env_int("RT_DDA_MIN_T", 12), d_drain_t = env_int("RT_DDA_DRAIN", 4), d_refill_t = env_int("RT_DDA_REFILL", 16);
     const unsigned sgrid = (unsigned)sm_count * 8u;    // grid-stride kernels
-    static const int adv_mult = env_int("RT_ADV_GRID", 3);  // = resident CTAs per SM; 3..32 measured within 1 %
+    static const int adv_mult = env_int("RT_ADV_GRID", RT_ADV_MINB);  // = resident CTAs per SM; 3..32 measured within 1 %
     const unsigned agrid = (unsigned)sm_count * (unsigned)adv_mult;  // wave_advance
     const bool count = fr.counters != nullptr;
     for (uint32_t g = 0; g < gens; ++g) {
