@@ -42,6 +42,7 @@ FLOPS_FILTER = 14.0   # bounding-sphere filter, expanded form: 7 fma per (ray, o
 FLOPS_EXACT = 78.0    # reference arithmetic of one ray x object test as written
 FLOPS_NODE = 52.0     # two inflated slab tests of one BVH node: 10 FADD + 6 FMUL + 18 FFMA in the SASS of wave_trace_bvh
                       # (profiles/r2_sass_wave_trace_bvh_node_step.txt); the 7 min/max and 4 compares are not counted
+FLOPS_CELL = 6.0      # one step of the uniform-grid walk (three compares, an add, the termination test)
 FLOPS_SHADE = 100.0   # Phong terms per (hit, light)
 FLOPS_ALGO_PAIR = 54.5  # minimal affine ray x object test
 
@@ -303,6 +304,7 @@ def main():
     rays_reference = r_prim + r_shadow + r_refl
     accel_used = st.accel_used
     pipeline_used = st.pipeline_used
+    grid_walk = bool(st.grid_walk_used)
     launches_per_step = st.kernel_launches
     ctx.set_option(lib.OPT_COUNT_RAYS, 0)
 
@@ -485,8 +487,8 @@ def main():
     kernel_names = ({0: "wave_trace_brute", 1: "wave_trace_filter", 2: "wave_trace_bvh", 3: "wave_trace_bvh"} if pipeline_used == 1 else
                     {0: "render_mega<brute>", 1: "render_mega<filter>", 2: "render_mega<bvh>"})
     shades = t_shadow  # one Phong evaluation per traced shadow ray
-    if accel_used == 3:  # perspective grids (filter tests per list entry) + BVH for the rays without a common apex
-        flops = node_visits * FLOPS_NODE + pair_tests * FLOPS_FILTER + exact_tests * FLOPS_EXACT + shades * FLOPS_SHADE
+    if accel_used == 3:  # perspective grids (filter tests per list entry) + uniform-grid walk or BVH for the rays without a common apex
+        flops = node_visits * (FLOPS_CELL if grid_walk else FLOPS_NODE) + pair_tests * FLOPS_FILTER + exact_tests * FLOPS_EXACT + shades * FLOPS_SHADE
     elif accel_used == 2:
         flops = node_visits * FLOPS_NODE + exact_tests * (FLOPS_EXACT + FLOPS_FILTER) + shades * FLOPS_SHADE
     elif accel_used == 1:
@@ -498,9 +500,10 @@ def main():
     # shard's launches move other bytes)
     traffic, traffic_src = (None, None)
     if world == 1 and pipeline_used == 1 and args.workload == "cfg5-box":
-        traffic, traffic_src = ncu_traffic({2: "r1_g_wave_trace_bvh_cfg5_8k.txt", 3: "r2_wave_trace_bvh_cfg5_8k.txt"}.get(accel_used, "none"))
+        traffic, traffic_src = ncu_traffic({2: "r1_g_wave_trace_bvh_cfg5_8k.txt",
+                                            3: "r2_wave_trace_dda_v2_cfg5_8k.txt" if grid_walk else "r2_wave_trace_bvh_cfg5_8k.txt"}.get(accel_used, "none"))
     roofline = {
-        "kernel": kernel_names[accel_used], "bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
+        "kernel": "wave_trace_dda" if (accel_used == 3 and grid_walk and pipeline_used == 1) else kernel_names[accel_used], "bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
         "frac": achieved_tf / peak_tf if peak_tf else None, "traffic": traffic, "traffic_source": traffic_src,
         "peak_source": "rt_measure_fp32_peak (register-only loops, this GPU, this run: scalar FFMA %.1f, packed FFMA2 %.1f TFLOP/s; "
                        "the larger is the peak and implies %.0f MHz)" % (peak_scalar, peak_packed, peak_mhz),
@@ -511,11 +514,11 @@ def main():
                         "frac": (exact_tests * FLOPS_ALGO_PAIR + shades * FLOPS_SHADE) / world / (ms_dev * 1e-3) / 1e12 / peak_tf if peak_tf else None},
         "hbm": {"framebuffer_bytes_per_launch": pixels * 16 / world, "achieved_gbs": pixels * 16 / world / (ms_dev * 1e-3) / 1e9,
                 "peak_gbs": peaks.get("hbm_gbs")},
-        "note": ("the frame's dominant kernel is the BVH trace of the reflection rays (the rays through a common apex -- camera, point-light "
-                 "shadow -- look up a perspective grid instead: wave_trace_grid); it is bound by issue slots and divergent node fetches, not "
-                 "by FP32: ncu (profiles/r2_wave_trace_bvh_cfg5_8k.txt, this frame) shows issue slots 65 % busy, ALU pipe 46 % vs FMA 24 %, L1 "
-                 "wavefronts 59 % of peak, 22.5 of 32 lanes active; the FP32 fraction is reported for completeness, see roofline_brute for "
-                 "the FP32-bound kernel") if accel_used >= 2 else "",
+        "note": ("the frame's dominant kernel is the trace of the reflection rays -- a uniform-grid walk (wave_trace_dda) where the scene "
+                 "allows it, else the BVH (wave_trace_bvh); the rays through a common apex -- camera, point-light shadow -- look up a "
+                 "perspective grid instead (wave_trace_grid).  These searches are bound by latency and issue slots, not by FP32 (ncu "
+                 "summaries under profiles/r2_*); the FP32 fraction is reported for completeness, see roofline_brute for the FP32-bound "
+                 "kernel") if accel_used >= 2 else "",
     }
 
     # brute-force leg: the reference's O(rays x objects) search (filter + exact) on a bounded band of the same frame
@@ -656,7 +659,7 @@ def main():
             "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": dict(config, accel=["brute", "filter", "bvh", "perspective grids + bvh"][accel_used], pipeline=["megakernel", "wavefront"][pipeline_used],
+            "config": dict(config, accel=["brute", "filter", "bvh", "perspective grids + " + ("uniform-grid walk" if grid_walk else "bvh")][accel_used], pipeline=["megakernel", "wavefront"][pipeline_used],
                            sharding="row-blocks of %d rows round-robin over %d ranks, peer stores into rank 0 (CUDA IPC)" % (args.block_rows, world)
                            if world > 1 else "single GPU",
                            l2="framebuffer %d MB > L2; 256 MB memset between steps flushes L2 (scene is re-read from HBM each step)" % (W * H * 16 >> 20),

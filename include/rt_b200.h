@@ -116,7 +116,8 @@ typedef struct rt_stats {
     uint32_t kernel_launches;
     uint32_t accel_used;     /* rt_accel actually used                                       */
     uint32_t pipeline_used;  /* 0 = megakernel, 1 = wavefront                                */
-    uint32_t reserved;
+    uint32_t grid_walk_used; /* RT_ACCEL_GRID: 1 = the rays without a common apex walked the uniform grid (node_visits then counts
+                              * cells), 0 = they walked the BVH */
 } rt_stats;
 
 /* Integer options for rt_set_option. */

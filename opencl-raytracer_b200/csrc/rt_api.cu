@@ -632,6 +632,7 @@ int collect_stats(rt_ctx* c, int accel, uint64_t pixels, uint32_t launches) {
     st.kernel_launches = c->last_launches ? c->last_launches : launches;
     st.accel_used = (uint32_t)accel;
     st.pipeline_used = (uint32_t)c->last_pipeline;
+    st.grid_walk_used = (accel == RT_ACCEL_GRID && c->last_pipeline == 1 && c->g3.valid) ? 1u : 0u;
     if (c->opt_count) {
         rt::Counters h;
         RT_CUDA(cudaMemcpyAsync(&h, c->d_counters.p, sizeof h, cudaMemcpyDeviceToHost, c->stream));

@@ -35,11 +35,11 @@ class Stats(C.Structure):
         ("pixels", C.c_uint64), ("hit_pixels", C.c_uint64),
         ("kernel_ms", C.c_float), ("total_ms", C.c_float),
         ("kernel_launches", C.c_uint32), ("accel_used", C.c_uint32), ("pipeline_used", C.c_uint32),
-        ("reserved", C.c_uint32),
+        ("grid_walk_used", C.c_uint32),
     ]
 
     def as_dict(self):
-        return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
+        return {k: getattr(self, k) for k, _ in self._fields_ }
 
     @property
     def rays_traced(self):
