@@ -67,7 +67,11 @@ struct DevBuf {
 struct rt_ctx {
     int device = 0;
     cudaStream_t stream = nullptr, copy_stream = nullptr;
-    cudaEvent_t copy_done = nullptr;
+    cudaEvent_t copy_done = nullptr, copy_t0 = nullptr, copy_t1 = nullptr;
+    // readback bands: kernel time : copy time per unit of the frame, measured on the previous frame (an idle PCIe link gives ~2.6
+    // for the 8K cfg5 frame; eight ranks sharing the host's ingest bandwidth ~1) -- the bands shrink by this factor
+    double band_ratio = 3.0;
+    uint32_t band0_units = 0, band_units_total = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
     static const int kMaxBands = 16;
     cudaEvent_t band_done[kMaxBands] = {};
@@ -785,10 +789,11 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
         if (sequential) {
             // bands one after the other, each as two lanes on two streams; the copy of band b runs under the kernels of band
             // b + 1, so the bands shrink geometrically by (copy time : kernel time) and only the small last copy is exposed
-            int nb = c->opt_bands > 0 ? c->opt_bands : (local_pixels(c) >= (12ull << 20) ? 4 : 2);
+            // 4 bands for a large frame, and for a shard whose copy is as slow as its kernels (ranks sharing the host's ingest)
+            int nb = c->opt_bands > 0 ? c->opt_bands : ((local_pixels(c) >= (12ull << 20) || c->band_ratio < 1.5) ? 4 : 2);
             nb = std::min(nb, rt_ctx::kMaxBands / 2);
             while (nb > 1 && units < (uint32_t)(4 * nb)) --nb;
-            const double ratio = band_ratio_env > 0.0 ? band_ratio_env : (nb >= 4 ? 3.5 : 2.5);
+            const double ratio = band_ratio_env > 0.0 ? band_ratio_env : std::min(8.0, std::max(1.0, c->band_ratio * (nb >= 4 ? 1.4 : 1.0)));
             band_u[0] = 0;
             for (int b = 0; b < nb; ++b) {
                 uint32_t u0, u1;
@@ -873,6 +878,8 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
             const bool band_complete = k + 1 == n_seq || seq[k + 1].band != seq[k].band;
             if (host_out && band_complete) {  // the band's rows go home under the kernels of the bands behind it
                 for (int j = k; j >= 0 && seq[j].band == seq[k].band; --j) RT_CUDA(cudaStreamWaitEvent(c->copy_stream, c->band_done[j], 0));
+                const bool time_it = sequential && seq[k].band == 0;
+                if (time_it) RT_CUDA(cudaEventRecord(c->copy_t0, c->copy_stream));
                 const uint32_t b0 = c->use_camera ? band_u[seq[k].band] : 0u, b1 = c->use_camera ? band_u[seq[k].band + 1] : 0u;
                 if (!c->use_camera) {
                     if (c->n_rays) RT_CUDA(cudaMemcpyAsync(host_out, c->d_fb.p, c->n_rays * sizeof(float4), cudaMemcpyDeviceToHost, c->copy_stream));
@@ -889,8 +896,14 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
                         RT_CUDA(copy_rows(first, cnt));
                     }
                 }
+                if (time_it) {
+                    RT_CUDA(cudaEventRecord(c->copy_t1, c->copy_stream));
+                    c->band0_units = b1 - b0;
+                    c->band_units_total = units;
+                }
             }
         }
+        if (!sequential) c->band0_units = 0;
         if (n_seq > 1)
             for (int k = 0; k < n_seq; ++k) RT_CUDA(cudaStreamWaitEvent(c->stream, c->band_done[k], 0));
         RT_CUDA(cudaEventRecord(c->ev1, c->stream));
@@ -974,7 +987,8 @@ int rt_create(rt_ctx** out, int device) {
         bands_ok = cudaEventCreateWithFlags(&c->band_done[i], cudaEventDisableTiming) == cudaSuccess &&
                    cudaStreamCreateWithPriority(&c->seq_stream[i], cudaStreamNonBlocking, std::min(prio_hi + i, prio_lo)) == cudaSuccess;
     }
-    bands_ok = bands_ok && cudaEventCreateWithFlags(&c->copy_done, cudaEventDisableTiming) == cudaSuccess;
+    bands_ok = bands_ok && cudaEventCreateWithFlags(&c->copy_done, cudaEventDisableTiming) == cudaSuccess &&
+               cudaEventCreate(&c->copy_t0) == cudaSuccess && cudaEventCreate(&c->copy_t1) == cudaSuccess;
     if (!bands_ok || cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&c->ev0) != cudaSuccess ||
         cudaEventCreate(&c->ev1) != cudaSuccess || cudaEventCreate(&c->ev2) != cudaSuccess) {
         delete c;
@@ -1007,6 +1021,8 @@ int rt_destroy(rt_ctx* c) {
         if (c->seq_stream[i]) cudaStreamDestroy(c->seq_stream[i]);
     }
     if (c->copy_done) cudaEventDestroy(c->copy_done);
+    if (c->copy_t0) cudaEventDestroy(c->copy_t0);
+    if (c->copy_t1) cudaEventDestroy(c->copy_t1);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -1215,6 +1231,15 @@ int rt_render(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float* host_
     RT_CUDA(cudaEventElapsedTime(&ms2, c->ev0, c->ev2));
     c->stats.kernel_ms = ms;  // all bands' kernels (copies of finished bands run underneath)
     c->stats.total_ms = ms2;
+    if (c->band0_units && c->band_units_total && c->last_pipeline == 1) {  // next frame's band split
+        float cp = 0.f;
+        if (cudaEventElapsedTime(&cp, c->copy_t0, c->copy_t1) == cudaSuccess && cp > 0.f && ms > 0.f) {
+            const double r = ((double)ms / c->band_units_total) / ((double)cp / c->band0_units);
+            c->band_ratio = std::min(8.0, std::max(1.0, 0.5 * c->band_ratio + 0.5 * r));
+        } else {
+            (void)cudaGetLastError();
+        }
+    }
     return RT_OK;
 }
 
