@@ -1,5 +1,6 @@
 #!/usr/bin/env python
-"""Small renders through every kernel family (wavefront bvh / filter / brute, megakernel, both tree builders), each checked
+"""Small renders through every kernel family (wavefront grids + grid walk / bvh / filter / brute, tail launch, megakernel, both
+scene builders), each checked
 against the oracle (ids / t bit-exact, colours 1e-4).  Written to be run under compute-sanitizer
 (`compute-sanitizer --tool memcheck|racecheck python tools/sanitize.py`); the tool is closed on this GPU pool, so the
 script only serves as a quick all-paths parity check on the box."""
@@ -28,7 +29,7 @@ for pipeline in (1, 0):  # wavefront, megakernel
             ctx.set_option(lib.OPT_BVH_BUILDER, builder)
             ctx.upload_scene(objs, lights)
             ctx.set_camera(W, H, z)
-            for accel in ((0, 1, 2) if builder == 0 else (2,)):
+            for accel in ((0, 1, 2, 3) if builder == 0 else (2, 3)):
                 out = ctx.render(3, 2, accel)
                 gid, gt = ctx.render_aov(accel)
                 assert np.array_equal(gid, hid) and np.array_equal(gt, ht), (pipeline, builder, accel)
