@@ -194,6 +194,25 @@ int rt_render_aov(rt_ctx* ctx, int accel, int32_t* host_hit_id, float* host_hit_
 /* Nearest hit of arbitrary host rays against the uploaded scene. */
 int rt_trace(rt_ctx* ctx, const rt_ray* host_rays, uint64_t n_rays, int accel, int32_t* host_hit_id, float* host_hit_t);
 
+/* rt_trace for callers that may not allocate device memory (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  No counterpart in the reference.  Same kernel and
+ * same results as rt_trace, but the call runs no cudaMalloc / cudaFree or other allocating routine: the rays and the results are
+ * staged in a fixed `static __device__` array inside the library, RT_TRACE_STATIC_BYTES (10 MiB) that every GPU which
+ * loads the library holds until the process exits.
+ *   - n_rays > RT_TRACE_STATIC_MAX_RAYS is rejected with RT_ERR_UNSUPPORTED (split the batch, or use rt_trace).
+ *   - The scene must be resident and prepared for the rays' origins (rt_upload_scene done; origins no farther from the
+ *     world origin than the scene's own extent, or than the rays of an earlier rt_trace / rt_set_rays): otherwise
+ *     RT_ERR_UNSUPPORTED instead of a re-preparation, which would allocate.
+ *   - Every context and every call on a GPU shares the one array, which keeps the last call's contents (each call overwrites
+ *     all it reads back).  The call returns after its results reached the host, so calls in sequence are safe; calls that
+ *     overlap on the same GPU -- other host threads, other contexts -- race and must be serialised by the caller.
+ *   - n_rays == 0 only resolves the array's device address for the context's GPU (cudaGetSymbolAddress, once per device),
+ *     so that a caller can do this set-up outside the region where even that is unwelcome.
+ *   - No rt_stats are produced. */
+#define RT_TRACE_STATIC_MAX_RAYS 262144u
+#define RT_TRACE_STATIC_BYTES (RT_TRACE_STATIC_MAX_RAYS * 40ull)
+int rt_trace_static(rt_ctx* ctx, const rt_ray* host_rays, uint64_t n_rays, int accel, int32_t* host_hit_id, float* host_hit_t);
+
 int rt_get_stats(rt_ctx* ctx, rt_stats* out);
 
 /* Device version of PPMExporter.cpp:19-21 quantisation, min(255, (int)floorf(c * 255.f)) per channel, packed rgb8

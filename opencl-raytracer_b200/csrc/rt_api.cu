@@ -9,6 +9,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -1341,6 +1342,88 @@ int rt_trace(rt_ctx* c, const rt_ray* host_rays, uint64_t n, int accel, int32_t*
     float ms = 0.f;
     RT_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
     c->stats.kernel_ms = c->stats.total_ms = ms;
+    return RT_OK;
+}
+
+// ---- rt_trace without any allocation.  rt_trace stages the rays and the results in three buffers it cudaMallocs and frees on
+// every call; callers that may not allocate get the same kernel with the staging in a fixed array that is part of the library's
+// image: every GPU that loads librt_b200.so holds RT_TRACE_STATIC_BYTES (10 MiB) of it until the process exits.  The array is
+// shared by every context and every call on a device and keeps the previous call's contents: the kernel overwrites every
+// element the call reads back (nothing has to start at zero), but calls that overlap on one GPU race.
+}  // extern "C"
+
+namespace {
+
+constexpr uint64_t kStaticRays = RT_TRACE_STATIC_MAX_RAYS;
+constexpr uint64_t kStaticOffIds = kStaticRays * sizeof(rt::Ray);                 // rays first (32 B each) ...
+constexpr uint64_t kStaticOffTs = kStaticOffIds + kStaticRays * sizeof(int32_t);  // ... then the hit ids, then t
+constexpr uint64_t kStaticBytes = kStaticOffTs + kStaticRays * sizeof(float);
+static_assert(kStaticBytes == RT_TRACE_STATIC_BYTES, "rt_b200.h states the size of the static scratch");
+static_assert(kStaticOffIds % 256 == 0 && kStaticOffTs % 256 == 0, "sub-buffers keep the array's alignment");
+
+static __device__ __align__(256) unsigned char g_trace_scratch[kStaticBytes];
+
+// In host code `g_trace_scratch` is only a handle of the symbol: its device address differs per GPU and comes from
+// cudaGetSymbolAddress with that GPU current.  Looked up once per device.
+constexpr int kMaxStaticDevices = 64;
+std::mutex g_static_mutex;
+unsigned char* g_static_addr[kMaxStaticDevices] = {};
+
+int static_scratch(int device, unsigned char** out) {
+    if (device < 0 || device >= kMaxStaticDevices) return fail(RT_ERR_UNSUPPORTED, "rt_trace_static: device index beyond 63");
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (!g_static_addr[device]) {
+        cudaError_t e = cudaSetDevice(device);
+        void* p = nullptr;
+        if (e == cudaSuccess) e = cudaGetSymbolAddress(&p, g_trace_scratch);
+        if (e != cudaSuccess || !p)
+            return fail(RT_ERR_CUDA, std::string("rt_trace_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+        g_static_addr[device] = static_cast<unsigned char*>(p);
+    }
+    *out = g_static_addr[device];
+    return RT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rt_trace_static(rt_ctx* c, const rt_ray* host_rays, uint64_t n, int accel, int32_t* host_hit_id, float* host_hit_t) {
+    if (!c) return fail(RT_ERR_INVALID, "null context");
+    if (accel < RT_ACCEL_AUTO || accel > RT_ACCEL_GRID) return fail(RT_ERR_INVALID, "bad accel");
+    if (n > kStaticRays)
+        return fail(RT_ERR_UNSUPPORTED, "rt_trace_static: " + std::to_string(n) + " rays exceed the static scratch of " +
+                                            std::to_string(kStaticRays) + " rays (RT_TRACE_STATIC_MAX_RAYS); split the batch or use rt_trace");
+    if (n && (!host_rays || !host_hit_id || !host_hit_t)) return fail(RT_ERR_INVALID, "null argument");
+    RT_CUDA(cudaSetDevice(c->device));
+    unsigned char* scratch = nullptr;
+    int rc = static_scratch(c->device, &scratch);  // n == 0: the per-device set-up alone
+    if (rc != RT_OK || n == 0) return rc;
+    double omax2 = 0.0;
+    for (uint64_t i = 0; i < n; ++i) {
+        const float* s = host_rays[i].start;
+        if (!(fabsf(s[3] - 1.f) <= 1e-4f) || host_rays[i].direction[3] != 0.f)
+            return fail(RT_ERR_UNSUPPORTED, "ray " + std::to_string(i) + ": start.w must be 1 and direction.w 0 (Ray3D.hpp:9)");
+        omax2 = std::max(omax2, (double)s[0] * s[0] + (double)s[1] * s[1] + (double)s[2] * s[2]);
+    }
+    if (!(omax2 < 1e30)) return fail(RT_ERR_UNSUPPORTED, "non-finite ray origin");
+    // The scene must already be resident and prepared for origins this far out: preparing it again would allocate.
+    if (!c->have_scene) return fail(RT_ERR_INVALID, "rt_trace_static: no scene uploaded");
+    if (c->scene_dirty || !((float)sqrt(omax2) <= c->hs.omax))
+        return fail(RT_ERR_UNSUPPORTED, "rt_trace_static: the resident scene is not prepared for these rays (origins up to " +
+                                            std::to_string(sqrt(omax2)) + " from the world origin, scene prepared for " +
+                                            std::to_string(c->hs.omax) + "): call rt_trace or rt_set_rays once with such rays first");
+    accel = pick_accel(c, accel);
+    if (accel == RT_ACCEL_GRID) accel = RT_ACCEL_BVH;  // arbitrary rays have no common apex
+    rt::Ray* d_rays = reinterpret_cast<rt::Ray*>(scratch);
+    int32_t* d_ids = reinterpret_cast<int32_t*>(scratch + kStaticOffIds);
+    float* d_ts = reinterpret_cast<float*>(scratch + kStaticOffTs);
+    cudaError_t e = cudaMemcpyAsync(d_rays, host_rays, n * sizeof(rt_ray), cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) e = rt::launch_trace(c->scene, d_rays, n, accel, d_ids, d_ts, nullptr, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(host_hit_id, d_ids, n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(host_hit_t, d_ts, n * sizeof(float), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    if (e != cudaSuccess) return fail(RT_ERR_CUDA, std::string("rt_trace_static: ") + cudaGetErrorString(e));
     return RT_OK;
 }
 

@@ -16,12 +16,13 @@ _PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_PKG, "librt_b200.so")
 
 OPT_PIPELINE, OPT_COUNT_RAYS, OPT_BVH_LEAF, OPT_SKIP_DEAD_RAYS, OPT_READBACK_BANDS, OPT_BVH_BUILDER, OPT_LANES, OPT_GRID_RES, OPT_ZERO_COPY, OPT_GRID3_DENSITY, OPT_DETECT_PINHOLE, OPT_TAIL_GEN = 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12
+TRACE_STATIC_MAX_RAYS = 262144
 ACCEL_AUTO, ACCEL_BRUTE, ACCEL_CULL, ACCEL_BVH, ACCEL_GRID = -1, 0, 1, 2, 3
 
 # every symbol include/rt_b200.h declares (tests check the library exports all of them)
 ABI_SYMBOLS = (
     "rt_last_error", "rt_abi_version", "rt_device_count", "rt_create", "rt_destroy", "rt_set_option", "rt_upload_scene", "rt_set_rays",
-    "rt_set_camera", "rt_get_camera", "rt_set_shard", "rt_render", "rt_render_device", "rt_framebuffer", "rt_render_aov", "rt_trace",
+    "rt_set_camera", "rt_get_camera", "rt_set_shard", "rt_render", "rt_render_device", "rt_framebuffer", "rt_render_aov", "rt_trace", "rt_trace_static",
     "rt_get_stats", "rt_quantize_rgb8", "rt_host_alloc", "rt_host_free", "rt_host_register", "rt_host_unregister", "rt_measure_fp32_peak", "rt_fp32_peak_detail",
     "rt_ipc_export_framebuffer", "rt_ipc_open", "rt_ipc_close", "rt_readback", "rt_host_build_bvh", "rt_plan_bands",
 )
@@ -88,6 +89,7 @@ def load():
             "rt_readback": [vp, vp],
             "rt_render_aov": [vp, i32, vp, vp],
             "rt_trace": [vp, vp, u64, i32, vp, vp],
+            "rt_trace_static": [vp, vp, u64, i32, vp, vp],
             "rt_get_stats": [vp, C.POINTER(Stats)],
             "rt_quantize_rgb8": [vp, vp, u64, vp, C.POINTER(u64)],
             "rt_host_alloc": [C.POINTER(vp), u64],
@@ -287,6 +289,15 @@ class Context:
         hid = np.empty(len(rays), dtype=np.int32)
         ht = np.empty(len(rays), dtype=np.float32)
         _check(load().rt_trace(self._h, _ptr(rays), len(rays), accel, _ptr(hid), _ptr(ht)))
+        return hid, ht
+
+    def trace_static(self, rays: np.ndarray, accel: int = -1):
+        """rt_trace_static: the same search with no device allocation in the call (static scratch in the library,
+        at most TRACE_STATIC_MAX_RAYS rays; calls that overlap on one GPU race)."""
+        rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
+        hid = np.empty(len(rays), dtype=np.int32)
+        ht = np.empty(len(rays), dtype=np.float32)
+        _check(load().rt_trace_static(self._h, _ptr(rays), len(rays), accel, _ptr(hid), _ptr(ht)))
         return hid, ht
 
     def stats(self) -> Stats:
