@@ -139,6 +139,10 @@ struct rt_ctx {
     DevBuf<rt::F4> d_aabb;
     rt::Grid3 g3 = {};
     bool g3_dirty = true;
+    // a scene prepared on the device (RT_OPT_BVH_BUILDER 1) leaves the inflated boxes in d_aabb and their bounds here
+    bool dev_boxes = false;
+    double dev_box_lo[3] = {0, 0, 0}, dev_box_hi[3] = {0, 0, 0};
+    uint32_t dev_live = 0;
     uint64_t g3_n_entries = 0;
     int opt_grid3 = 400;  // cells per 100 objects (default 4 per object); 0: off, the BVH serves these rays
     uint32_t g_cam_w = 0, g_cam_h = 0;
@@ -208,6 +212,8 @@ int sync_scene_device(rt_ctx* c) {
     RT_CUDA(c->d_mat.ensure(3 * (size_t)n));
     RT_CUDA(c->d_cull.ensure(n));
     RT_CUDA(c->d_lbvh_leaves.ensure(n));
+    RT_CUDA(c->d_aabb.ensure(n));
+    c->dev_boxes = false;
     RT_CUDA(c->d_bounds_scratch.ensure(rt::bounds_scratch_bytes(n)));
     RT_CUDA(c->d_bounds_globals.ensure(1));
     rt::BoundsGlobals g;
@@ -227,7 +233,8 @@ int sync_scene_device(rt_ctx* c) {
     int rc = bad(g);
     if (rc != RT_OK) return rc;
     const double omax = std::max(1.05 * g.r0 + 1.0, (double)c->omax_user * 1.0001 + 1e-3);  // rt_scene.cpp
-    RT_CUDA(rt::bounds_pass2_launch(c->d_objs.p, n, c->d_bounds_scratch.p, omax, c->d_cull.p, c->d_lbvh_leaves.p, c->d_bounds_globals.p, c->stream));
+    RT_CUDA(rt::bounds_pass2_launch(c->d_objs.p, n, c->d_bounds_scratch.p, omax, c->d_cull.p, c->d_lbvh_leaves.p,
+                                    reinterpret_cast<float4*>(c->d_aabb.p), c->d_bounds_globals.p, c->stream));
     RT_CUDA(cudaMemcpyAsync(&g, c->d_bounds_globals.p, sizeof g, cudaMemcpyDeviceToHost, c->stream));
     RT_CUDA(cudaStreamSynchronize(c->stream));
     rc = bad(g);
@@ -252,7 +259,11 @@ int sync_scene_device(rt_ctx* c) {
     for (int k = 0; k < 3; ++k) {
         c->hs.lbvh_lo[k] = rt::bounds_decode_ordered(g.lo[k]);
         c->hs.lbvh_hi[k] = rt::bounds_decode_ordered(g.hi[k]);
+        c->dev_box_lo[k] = rt::bounds_decode_ordered(g.box_lo[k]);
+        c->dev_box_hi[k] = rt::bounds_decode_ordered(g.box_hi[k]);
     }
+    c->dev_live = g.live;
+    c->dev_boxes = true;
     const size_t sb = rt::lbvh_scratch_bytes(n);
     RT_CUDA(c->d_lbvh_scratch.ensure(sb));
     RT_CUDA(c->d_nodes.ensure(n - 1));
@@ -271,6 +282,7 @@ int sync_scene(rt_ctx* c) {
     if (!c->scene_dirty && need_omax <= c->hs.omax) return RT_OK;
     if (c->opt_builder == 1 && c->objs.size() >= 2 && c->objs.size() < (1u << 27)) return sync_scene_device(c);
     std::string err;
+    c->dev_boxes = false;
     const int rc = rt::build_scene(c->objs.data(), (uint32_t)c->objs.size(), c->lights.data(), (uint32_t)c->lights.size(),
                                    c->omax_user, c->opt_builder == 1 ? 0 : c->opt_leaf, c->hs, err);
     if (rc != RT_OK) return fail(rc, err);
@@ -355,21 +367,29 @@ int build_grid3(rt_ctx* c) {
     c->g3_dirty = false;
     c->g3_n_entries = 0;
     const uint32_t n_objs = c->hs.n_objs;
-    if (c->opt_grid3 <= 0 || n_objs < 64 || c->hs.cull.size() < n_objs) return RT_OK;  // (a device-prepared scene has no host records)
+    if (c->opt_grid3 <= 0 || n_objs < 64) return RT_OK;
     const float ext0 = 2.f * c->hs.scene_radius + 1.f;
     const float eps = 2e-5f * ext0 + 1e-4f;
     double lo[3] = {1e30, 1e30, 1e30}, hi[3] = {-1e30, -1e30, -1e30};
     uint32_t live = 0;
-    if (c->hs.aabb.size() < n_objs) return RT_OK;
-    for (uint32_t o = 0; o < n_objs; ++o) {
-        const rt::F4& hb = c->hs.aabb[o];
-        if (hb.w < 0.f || c->hs.cull[o].r2 < 0.f) continue;
-        ++live;
-        const float ctr[3] = {c->hs.cull[o].cx, c->hs.cull[o].cy, c->hs.cull[o].cz};
-        const float half[3] = {hb.x, hb.y, hb.z};
+    if (c->dev_boxes) {  // prepared on the device (rt_bounds.cu pass 2): boxes already in d_aabb, their bounds came back with the globals
+        live = c->dev_live;
         for (int k = 0; k < 3; ++k) {
-            lo[k] = std::min(lo[k], (double)ctr[k] - half[k] - eps);
-            hi[k] = std::max(hi[k], (double)ctr[k] + half[k] + eps);
+            lo[k] = c->dev_box_lo[k] - eps;
+            hi[k] = c->dev_box_hi[k] + eps;
+        }
+    } else {
+        if (c->hs.cull.size() < n_objs || c->hs.aabb.size() < n_objs) return RT_OK;
+        for (uint32_t o = 0; o < n_objs; ++o) {
+            const rt::F4& hb = c->hs.aabb[o];
+            if (hb.w < 0.f || c->hs.cull[o].r2 < 0.f) continue;
+            ++live;
+            const float ctr[3] = {c->hs.cull[o].cx, c->hs.cull[o].cy, c->hs.cull[o].cz};
+            const float half[3] = {hb.x, hb.y, hb.z};
+            for (int k = 0; k < 3; ++k) {
+                lo[k] = std::min(lo[k], (double)ctr[k] - half[k] - eps);
+                hi[k] = std::max(hi[k], (double)ctr[k] + half[k] + eps);
+            }
         }
     }
     if (live < 64) return RT_OK;
@@ -394,7 +414,7 @@ int build_grid3(rt_ctx* c) {
     RT_CUDA(c->g_cursor.ensure((size_t)n_cells + 1));
     const size_t sb = rt::pgrid_scan_bytes(n_cells);
     RT_CUDA(c->g_scan.ensure(sb));
-    RT_CUDA(c->d_aabb.upload(c->hs.aabb, c->stream));
+    if (!c->dev_boxes) RT_CUDA(c->d_aabb.upload(c->hs.aabb, c->stream));
     RT_CUDA(rt::grid3_count(g, c->d_cull.p, reinterpret_cast<const float4*>(c->d_aabb.p), n_objs, c->g_cursor.p, c->g3_cell_start.p, c->g_scan.p, sb, c->stream));
     uint32_t total = 0;
     RT_CUDA(cudaMemcpyAsync(&total, c->g3_cell_start.p + n_cells, sizeof total, cudaMemcpyDeviceToHost, c->stream));

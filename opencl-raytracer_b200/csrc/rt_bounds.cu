@@ -94,14 +94,14 @@ __device__ void fail_at(BoundsGlobals* g, uint32_t i, int code) {
 __device__ void atomic_max_pos(double* addr, double v) {  // v >= 0: the bit patterns order like the values
     atomicMax(reinterpret_cast<unsigned long long*>(addr), (unsigned long long)__double_as_longlong(v));
 }
+// ordered-integer image of a float: monotone for all finite values
+__device__ __forceinline__ int ordered_key(float f) {
+    const int i = __float_as_int(f);
+    return i >= 0 ? i : (int)(0x80000000u - (unsigned)i);
+}
 __device__ void atomic_minmax_float(float* lo, float* hi, float v) {
-    // ordered-integer image of a float: monotone for all finite values
-    auto key = [](float f) {
-        const int i = __float_as_int(f);
-        return i >= 0 ? i : (int)(0x80000000u - (unsigned)i);
-    };
-    atomicMin(reinterpret_cast<int*>(lo), key(v));
-    atomicMax(reinterpret_cast<int*>(hi), key(v));
+    atomicMin(reinterpret_cast<int*>(lo), ordered_key(v));
+    atomicMax(reinterpret_cast<int*>(hi), ordered_key(v));
 }
 
 // ---- pass 1: repack + geometry (rt_scene.cpp pass 1)
@@ -196,7 +196,7 @@ __global__ void __launch_bounds__(kB) bounds_pass1(const rt_object* __restrict__
 
 // ---- pass 2: padded bounds, filter record, tree leaf (rt_scene.cpp pass 2 + the lbvh_leaves block)
 __global__ void __launch_bounds__(kB) bounds_pass2(const rt_object* __restrict__ objs, const uint32_t n, const Geo* __restrict__ geo, const double omax,
-                                                   CullRec* __restrict__ cull, LbvhLeaf* __restrict__ leaves, BoundsGlobals* g) {
+                                                   CullRec* __restrict__ cull, LbvhLeaf* __restrict__ leaves, float4* __restrict__ aabb, BoundsGlobals* g) {
     const uint32_t i = blockIdx.x * kB + threadIdx.x;
     if (i >= n) return;
     const uint32_t type = objs[i].type;
@@ -216,6 +216,7 @@ __global__ void __launch_bounds__(kB) bounds_pass2(const rt_object* __restrict__
         lf.half[0] = lf.half[1] = lf.half[2] = 0.f;
         lf.f = 0.f;
         leaves[i] = lf;
+        aabb[i] = make_float4(0.f, 0.f, 0.f, -1.f);
         atomic_minmax_float(&g->lo[0], &g->hi[0], 0.f);
         atomic_minmax_float(&g->lo[1], &g->hi[1], 0.f);
         atomic_minmax_float(&g->lo[2], &g->hi[2], 0.f);
@@ -258,6 +259,18 @@ __global__ void __launch_bounds__(kB) bounds_pass2(const rt_object* __restrict__
     }
     lf.f = up(ff);
     leaves[i] = lf;
+    {   // the box a ray from anywhere in the scene can need (rt_scene.cpp pass 2: HostScene::aabb) and the bounds of all of them
+        const double infl = ff * (omax + cn) * 1.0001;
+        float hb[3];
+        const float ctr[3] = {cr.cx, cr.cy, cr.cz};
+        for (int k = 0; k < 3; ++k) {
+            hb[k] = up(half[k] + infl + 2.0 * U * cn);
+            atomicMin(reinterpret_cast<int*>(&g->box_lo[k]), ordered_key(__fsub_rd(ctr[k], hb[k])));
+            atomicMax(reinterpret_cast<int*>(&g->box_hi[k]), ordered_key(__fadd_ru(ctr[k], hb[k])));
+        }
+        aabb[i] = make_float4(hb[0], hb[1], hb[2], 1.f);
+        atomicAdd(&g->live, 1u);
+    }
     atomicMin(reinterpret_cast<unsigned*>(&g->h_min), __float_as_uint(cr.h));   // 0 < h <= 1: bit patterns order like the values
     atomicMax(reinterpret_cast<unsigned*>(&g->f_max), __float_as_uint(lf.f));
 }
@@ -276,7 +289,10 @@ void bounds_globals_init(BoundsGlobals* h) {
     for (int k = 0; k < 3; ++k) {
         reinterpret_cast<int*>(h->lo)[k] = big;
         reinterpret_cast<int*>(h->hi)[k] = -big;
+        reinterpret_cast<int*>(h->box_lo)[k] = big;
+        reinterpret_cast<int*>(h->box_hi)[k] = -big;
     }
+    h->live = 0;
 }
 
 float bounds_decode_ordered(float stored) {
@@ -294,9 +310,9 @@ cudaError_t bounds_pass1_launch(const rt_object* d_objs, uint32_t n, float4* min
     return cudaGetLastError();
 }
 
-cudaError_t bounds_pass2_launch(const rt_object* d_objs, uint32_t n, const void* scratch, double omax, CullRec* cull, LbvhLeaf* leaves, BoundsGlobals* d_g,
-                                cudaStream_t stream) {
-    if (n) bounds_pass2<<<(n + kB - 1) / kB, kB, 0, stream>>>(d_objs, n, reinterpret_cast<const Geo*>(scratch), omax, cull, leaves, d_g);
+cudaError_t bounds_pass2_launch(const rt_object* d_objs, uint32_t n, const void* scratch, double omax, CullRec* cull, LbvhLeaf* leaves, float4* aabb,
+                                BoundsGlobals* d_g, cudaStream_t stream) {
+    if (n) bounds_pass2<<<(n + kB - 1) / kB, kB, 0, stream>>>(d_objs, n, reinterpret_cast<const Geo*>(scratch), omax, cull, leaves, aabb, d_g);
     return cudaGetLastError();
 }
 

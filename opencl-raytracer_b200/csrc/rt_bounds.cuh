@@ -19,6 +19,8 @@ struct BoundsGlobals {
     unsigned long long first_bad;  // (object index << 8) | code of the first object outside the supported domain, ~0: none
     float h_min, f_max;            // smallest filter coefficient h, largest noise coefficient f
     float lo[3], hi[3];            // bounds of the leaf centres, stored as ordered integers (bounds_decode_ordered)
+    float box_lo[3], box_hi[3];    // bounds of the noise-inflated boxes of the live objects (uniform grid, rt_grid3.cuh), same coding
+    uint32_t live;                 // objects that can be hit
 };
 
 size_t bounds_scratch_bytes(uint32_t n_objs);
@@ -29,7 +31,8 @@ float bounds_decode_ordered(float stored);
 cudaError_t bounds_pass1_launch(const rt_object* d_objs, uint32_t n, float4* minv, float4* mv, float4* mat, void* scratch, BoundsGlobals* d_g,
                                 cudaStream_t stream);
 // pass 2 (needs omax, a function of pass 1's r0): filter records and the leaves of the device tree builder
-cudaError_t bounds_pass2_launch(const rt_object* d_objs, uint32_t n, const void* scratch, double omax, CullRec* cull, LbvhLeaf* leaves, BoundsGlobals* d_g,
-                                cudaStream_t stream);
+// aabb: per object the half extents of its box including the noise inflation (HostScene::aabb), w < 0: never hit
+cudaError_t bounds_pass2_launch(const rt_object* d_objs, uint32_t n, const void* scratch, double omax, CullRec* cull, LbvhLeaf* leaves, float4* aabb,
+                                BoundsGlobals* d_g, cudaStream_t stream);
 
 }  // namespace rt
