@@ -67,8 +67,13 @@ struct DevBuf {
 
 struct rt_ctx {
     int device = 0;
-    cudaStream_t stream = nullptr, copy_stream = nullptr;
-    cudaEvent_t copy_done = nullptr, copy_t0 = nullptr, copy_t1 = nullptr;
+    cudaStream_t stream = nullptr, copy_stream = nullptr, copy_stream2 = nullptr;  // copy_stream2: readback of the odd lane's bands (staggered plan)
+    cudaEvent_t copy_done = nullptr, copy_done2 = nullptr, copy_t0 = nullptr, copy_t1 = nullptr;
+    // RT_SEQ_TRACE=1: start / end of every launch sequence and the end of its band's copy, printed by rt_render (diagnostics)
+    cudaEvent_t tr_start[16] = {}, tr_end[16] = {}, tr_copy[16] = {};
+    int tr_n = 0;
+    int last_n_seq = 0;  // launch sequences of the last rt_render (their band_done events time the end of the kernels)
+    uint32_t tr_units[16] = {};
     // readback bands: kernel time : copy time per unit of the frame, measured on the previous frame (an idle PCIe link gives ~2.6
     // for the 8K cfg5 frame; eight ranks sharing the host's ingest bandwidth ~1) -- the bands shrink by this factor
     double band_ratio = 3.0;
@@ -806,15 +811,62 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
             const char* v = getenv("RT_BAND_RATIO");
             return v && *v ? atof(v) : 0.0;
         }();
-        const bool sequential = host_out != nullptr && c->use_camera && !aov_only && (band_mode_env < 0 ? true : band_mode_env == 1);
-        if (sequential) {
+        // experiment knobs, read on every render so that one process can sweep them
+        auto env_num = [](const char* name, double dflt) {
+            const char* v = getenv(name);
+            return v && *v ? atof(v) : dflt;
+        };
+        int stagger_k = (int)env_num("RT_STAGGER_K", -1);  // -1: auto; 0 / 1: off (bands of two equal lanes); K > 1: K sequences
+        double stagger_q = env_num("RT_STAGGER_Q", 0.0);
+        const int stagger_s = std::max(1, std::min(4, (int)env_num("RT_STAGGER_S", 3)));
+        if (c->opt_bands > 0 && stagger_k < 0) stagger_k = c->opt_bands;  // RT_OPT_READBACK_BANDS = number of sequences
+        if (!(stagger_q > 0.0)) {
+            // each sequence is `q` of the one before.  Copy much faster than the kernels (one GPU on an idle link, kernel : copy
+            // time 2.5): 0.7, so that only a small last copy is exposed.  Copy as slow as the kernels or slower (8 ranks share the
+            // host's ~100 GB/s of ingest: 66 MB per rank take 5.4 ms, the kernels 4.3): equal sequences, and many -- the frame is
+            // then home one copy time after the FIRST sequence has finished, so that one has to be small.
+            stagger_q = std::min(1.0, std::max(0.7, 1.3 - 0.3 * c->band_ratio));
+        }
+        if (stagger_k < 0) {
+            // auto: six sequences (eight when they are about equal), fewer when the smallest one would fall below 0.4 Mpixel
+            stagger_k = stagger_q > 0.85 ? 8 : 6;
+            const double px = (double)units * (double)unit_px;
+            auto smallest = [&](int k) {
+                double sum = 0.0, w = 1.0;
+                for (int i = 0; i < k; ++i, w *= stagger_q) sum += w;
+                return px * (w / stagger_q) / sum;
+            };
+            while (stagger_k > 2 && smallest(stagger_k) < 400000.0) --stagger_k;
+        }
+        const bool sequential = host_out != nullptr && c->use_camera && !aov_only && (band_mode_env < 0 ? true : band_mode_env >= 1);
+        const bool staggered = sequential && stagger_k > 1;
+        if (staggered) {
+            // every launch sequence is a band of its own; sizes shrink geometrically, streams alternate: a sequence's thin last
+            // generations run under the heavy first generations of the next sequence on the other stream
+            int nb = std::min(stagger_k, (int)rt_ctx::kMaxBands);
+            while (nb > 1 && units < (uint32_t)(4 * nb)) --nb;
+            double total_w = 0.0, w = 1.0;
+            for (int b = 0; b < nb; ++b, w *= stagger_q) total_w += w;
+            double acc = 0.0;
+            w = 1.0;
+            band_u[0] = 0;
+            for (int b = 0; b < nb; ++b, w *= stagger_q) {
+                acc += w;
+                band_u[b + 1] = b == nb - 1 ? units : std::max(band_u[b], std::min(units, (uint32_t)(acc / total_w * units + 0.5)));
+                seq[n_seq].u0 = band_u[b];
+                seq[n_seq].u1 = band_u[b + 1];
+                seq[n_seq].stream = b % stagger_s;
+                seq[n_seq].band = b;
+                ++n_seq;
+            }
+        } else if (sequential) {
             // bands one after the other, each as two lanes on two streams; the copy of band b runs under the kernels of band
             // b + 1, so the bands shrink geometrically by (copy time : kernel time) and only the small last copy is exposed
             // 4 bands for a large frame, and for a shard whose copy is as slow as its kernels (ranks sharing the host's ingest)
             int nb = c->opt_bands > 0 ? c->opt_bands : ((local_pixels(c) >= (12ull << 20) || c->band_ratio < 1.5) ? 4 : 2);
             nb = std::min(nb, rt_ctx::kMaxBands / 2);
             while (nb > 1 && units < (uint32_t)(4 * nb)) --nb;
-            const double ratio = band_ratio_env > 0.0 ? band_ratio_env : std::min(8.0, std::max(1.0, c->band_ratio * (nb >= 4 ? 1.4 : 1.0)));
+            const double ratio = band_ratio_env > 0.0 ? band_ratio_env : std::min(8.0, std::max(1.0, std::max(1.0, c->band_ratio) * (nb >= 4 ? 1.4 : 1.0)));
             band_u[0] = 0;
             for (int b = 0; b < nb; ++b) {
                 uint32_t u0, u1;
@@ -871,8 +923,9 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
         wg.g3 = c->g3;
         wg.filter_tiles = c->d_filter_tiles.p;
         RT_CUDA(cudaEventRecord(c->ev0, c->stream));  // every sequence starts after what was queued before this render
+        cudaStream_t cps = c->copy_stream;  // the copy stream of the band in hand
         auto copy_rows = [&](uint64_t first, uint64_t cnt) -> cudaError_t {
-            return cudaMemcpyAsync(host_out + 4 * first, c->d_fb.p + first, cnt * sizeof(float4), cudaMemcpyDeviceToHost, c->copy_stream);
+            return cudaMemcpyAsync(host_out + 4 * first, c->d_fb.p + first, cnt * sizeof(float4), cudaMemcpyDeviceToHost, cps);
         };
         bool waited[rt_ctx::kMaxBands] = {};
         for (int k = 0; k < n_seq; ++k) {
@@ -892,18 +945,31 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
                 const int per_level = 1 + (int)c->scene.n_lights;
                 tail_gen = px_seq >= (6ull << 20) ? 3 * per_level : px_seq >= (1ull << 20) ? 2 * per_level + 1 : per_level + 1;
             }
+            static const bool trace_env = getenv("RT_SEQ_TRACE") != nullptr;
+            if (trace_env && host_out) {
+                if (!c->tr_start[k]) {
+                    RT_CUDA(cudaEventCreate(&c->tr_start[k]));
+                    RT_CUDA(cudaEventCreate(&c->tr_end[k]));
+                    RT_CUDA(cudaEventCreate(&c->tr_copy[k]));
+                }
+                RT_CUDA(cudaEventRecord(c->tr_start[k], st));
+                c->tr_units[k] = seq[k].u1 - seq[k].u0;
+                c->tr_n = n_seq;
+            }
             uint32_t nl = 0;
             if (fr[k].n_local > 0) RT_CUDA(rt::wave_render(c->scene, fr[k], wb[k], accel, &wg, c->sm_count, &nl, st, tail_gen));
             c->last_launches += nl;
             if (n_seq > 1 || host_out) RT_CUDA(cudaEventRecord(c->band_done[k], st));
+            if (trace_env && host_out) RT_CUDA(cudaEventRecord(c->tr_end[k], st));
             const bool band_complete = k + 1 == n_seq || seq[k + 1].band != seq[k].band;
             if (host_out && band_complete) {  // the band's rows go home under the kernels of the bands behind it
-                for (int j = k; j >= 0 && seq[j].band == seq[k].band; --j) RT_CUDA(cudaStreamWaitEvent(c->copy_stream, c->band_done[j], 0));
+                cps = staggered && (seq[k].stream & 1) ? c->copy_stream2 : c->copy_stream;
+                for (int j = k; j >= 0 && seq[j].band == seq[k].band; --j) RT_CUDA(cudaStreamWaitEvent(cps, c->band_done[j], 0));
                 const bool time_it = sequential && seq[k].band == 0;
-                if (time_it) RT_CUDA(cudaEventRecord(c->copy_t0, c->copy_stream));
+                if (time_it) RT_CUDA(cudaEventRecord(c->copy_t0, cps));
                 const uint32_t b0 = c->use_camera ? band_u[seq[k].band] : 0u, b1 = c->use_camera ? band_u[seq[k].band + 1] : 0u;
                 if (!c->use_camera) {
-                    if (c->n_rays) RT_CUDA(cudaMemcpyAsync(host_out, c->d_fb.p, c->n_rays * sizeof(float4), cudaMemcpyDeviceToHost, c->copy_stream));
+                    if (c->n_rays) RT_CUDA(cudaMemcpyAsync(host_out, c->d_fb.p, c->n_rays * sizeof(float4), cudaMemcpyDeviceToHost, cps));
                 } else if (b1 == b0) {
                     // empty band
                 } else if (c->n_shards <= 1) {
@@ -917,20 +983,26 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
                         RT_CUDA(copy_rows(first, cnt));
                     }
                 }
+                if (trace_env) RT_CUDA(cudaEventRecord(c->tr_copy[k], cps));
                 if (time_it) {
-                    RT_CUDA(cudaEventRecord(c->copy_t1, c->copy_stream));
+                    RT_CUDA(cudaEventRecord(c->copy_t1, cps));
                     c->band0_units = b1 - b0;
                     c->band_units_total = units;
                 }
             }
         }
         if (!sequential) c->band0_units = 0;
+        c->last_n_seq = host_out ? n_seq : 0;
         if (n_seq > 1)
             for (int k = 0; k < n_seq; ++k) RT_CUDA(cudaStreamWaitEvent(c->stream, c->band_done[k], 0));
         RT_CUDA(cudaEventRecord(c->ev1, c->stream));
         if (host_out) {
             RT_CUDA(cudaEventRecord(c->copy_done, c->copy_stream));
             RT_CUDA(cudaStreamWaitEvent(c->stream, c->copy_done, 0));
+            if (staggered) {
+                RT_CUDA(cudaEventRecord(c->copy_done2, c->copy_stream2));
+                RT_CUDA(cudaStreamWaitEvent(c->stream, c->copy_done2, 0));
+            }
             RT_CUDA(cudaEventRecord(c->ev2, c->stream));
         }
         return RT_OK;
@@ -1001,14 +1073,16 @@ int rt_create(rt_ctx** out, int device) {
     c->sm_count = prop.multiProcessorCount;
     memset(&c->stats, 0, sizeof c->stats);
     memset(&c->scene, 0, sizeof c->scene);
-    bool bands_ok = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) == cudaSuccess;
+    bool bands_ok = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) == cudaSuccess &&
+                    cudaStreamCreateWithFlags(&c->copy_stream2, cudaStreamNonBlocking) == cudaSuccess;
     int prio_lo = 0, prio_hi = 0;  // numerically lower = higher priority
     if (cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi) != cudaSuccess) prio_lo = prio_hi = 0;
     for (int i = 0; i < rt_ctx::kMaxBands && bands_ok; ++i) {
-        bands_ok = cudaEventCreateWithFlags(&c->band_done[i], cudaEventDisableTiming) == cudaSuccess &&
+        bands_ok = cudaEventCreate(&c->band_done[i]) == cudaSuccess &&  // timed: the end of the kernels is the latest of them
                    cudaStreamCreateWithPriority(&c->seq_stream[i], cudaStreamNonBlocking, std::min(prio_hi + i, prio_lo)) == cudaSuccess;
     }
     bands_ok = bands_ok && cudaEventCreateWithFlags(&c->copy_done, cudaEventDisableTiming) == cudaSuccess &&
+               cudaEventCreateWithFlags(&c->copy_done2, cudaEventDisableTiming) == cudaSuccess &&
                cudaEventCreate(&c->copy_t0) == cudaSuccess && cudaEventCreate(&c->copy_t1) == cudaSuccess;
     if (!bands_ok || cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&c->ev0) != cudaSuccess ||
         cudaEventCreate(&c->ev1) != cudaSuccess || cudaEventCreate(&c->ev2) != cudaSuccess) {
@@ -1042,9 +1116,11 @@ int rt_destroy(rt_ctx* c) {
         if (c->seq_stream[i]) cudaStreamDestroy(c->seq_stream[i]);
     }
     if (c->copy_done) cudaEventDestroy(c->copy_done);
+    if (c->copy_done2) cudaEventDestroy(c->copy_done2);
     if (c->copy_t0) cudaEventDestroy(c->copy_t0);
     if (c->copy_t1) cudaEventDestroy(c->copy_t1);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    if (c->copy_stream2) cudaStreamDestroy(c->copy_stream2);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
     return RT_OK;
@@ -1242,21 +1318,48 @@ int rt_render(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float* host_
     }
     // kernels + copy: on the wavefront pipeline the frame is cut into concurrent bands whose copies overlap the kernels of
     // the bands behind them (render_on_device)
+    const auto enq0 = std::chrono::steady_clock::now();
     rc = render_on_device(c, max_bounces, mode, accel, c->d_fb.p, &used, false, host_out);
     if (rc != RT_OK) return rc;
+    const double enq_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - enq0).count();
     RT_CUDA(cudaStreamSynchronize(c->stream));
     rc = collect_stats(c, used, local_pixels(c), 1);
     if (rc != RT_OK) return rc;
     float ms = 0.f, ms2 = 0.f;
     RT_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
     RT_CUDA(cudaEventElapsedTime(&ms2, c->ev0, c->ev2));
+    // the end of the kernels = the latest sequence end (ev1 sits in a stream of its own and can be held up behind the copies
+    // when the streams outnumber the hardware queues)
+    if (c->last_pipeline == 1 && c->last_n_seq > 0) {
+        float kmax = 0.f;
+        for (int k = 0; k < c->last_n_seq; ++k) {
+            float t = 0.f;
+            if (cudaEventElapsedTime(&t, c->ev0, c->band_done[k]) == cudaSuccess) kmax = std::max(kmax, t);
+            else (void)cudaGetLastError();
+        }
+        if (kmax > 0.f) ms = std::min(ms, kmax);
+    }
     c->stats.kernel_ms = ms;  // all bands' kernels (copies of finished bands run underneath)
     c->stats.total_ms = ms2;
+    if (c->tr_n > 0 && getenv("RT_SEQ_TRACE")) {
+        fprintf(stderr, "[rt seq trace] dev %d shard %u/%u kernels %.2f total %.2f host enqueue %.2f ms, %u launches\n", c->device, c->shard, c->n_shards, ms, ms2,
+                enq_ms, c->last_launches);
+        for (int k = 0; k < c->tr_n; ++k) {
+            float a = 0.f, b = 0.f, cp = -1.f;
+            cudaEventElapsedTime(&a, c->ev0, c->tr_start[k]);
+            cudaEventElapsedTime(&b, c->ev0, c->tr_end[k]);
+            if (cudaEventElapsedTime(&cp, c->ev0, c->tr_copy[k]) != cudaSuccess) {
+                (void)cudaGetLastError();
+                cp = -1.f;
+            }
+            fprintf(stderr, "  seq %d units %u start %.2f end %.2f copy_end %.2f\n", k, c->tr_units[k], a, b, cp);
+        }
+    }
     if (c->band0_units && c->band_units_total && c->last_pipeline == 1) {  // next frame's band split
         float cp = 0.f;
         if (cudaEventElapsedTime(&cp, c->copy_t0, c->copy_t1) == cudaSuccess && cp > 0.f && ms > 0.f) {
             const double r = ((double)ms / c->band_units_total) / ((double)cp / c->band0_units);
-            c->band_ratio = std::min(8.0, std::max(1.0, 0.5 * c->band_ratio + 0.5 * r));
+            c->band_ratio = std::min(8.0, std::max(0.3, 0.5 * c->band_ratio + 0.5 * r));
         } else {
             (void)cudaGetLastError();
         }
