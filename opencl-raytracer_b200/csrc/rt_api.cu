@@ -78,6 +78,11 @@ struct rt_ctx {
     // for the 8K cfg5 frame; eight ranks sharing the host's ingest bandwidth ~1) -- the bands shrink by this factor
     double band_ratio = 3.0;
     uint32_t band0_units = 0, band_units_total = 0;
+    // staggered plan: every band's copy is timed (start = band finished and copy stream free), the kernel : copy ratio of the
+    // next frame comes from all of them -- one band's copy time depends on what the other ranks happen to copy meanwhile
+    cudaEvent_t cp_s[16] = {}, cp_e[16] = {};
+    uint32_t cp_units[16] = {};
+    int cp_n = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
     static const int kMaxBands = 16;
     cudaEvent_t band_done[kMaxBands] = {};
@@ -967,6 +972,13 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
                 for (int j = k; j >= 0 && seq[j].band == seq[k].band; --j) RT_CUDA(cudaStreamWaitEvent(cps, c->band_done[j], 0));
                 const bool time_it = sequential && seq[k].band == 0;
                 if (time_it) RT_CUDA(cudaEventRecord(c->copy_t0, cps));
+                if (staggered) {
+                    if (!c->cp_s[k]) {
+                        RT_CUDA(cudaEventCreate(&c->cp_s[k]));
+                        RT_CUDA(cudaEventCreate(&c->cp_e[k]));
+                    }
+                    RT_CUDA(cudaEventRecord(c->cp_s[k], cps));
+                }
                 const uint32_t b0 = c->use_camera ? band_u[seq[k].band] : 0u, b1 = c->use_camera ? band_u[seq[k].band + 1] : 0u;
                 if (!c->use_camera) {
                     if (c->n_rays) RT_CUDA(cudaMemcpyAsync(host_out, c->d_fb.p, c->n_rays * sizeof(float4), cudaMemcpyDeviceToHost, cps));
@@ -984,6 +996,10 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
                     }
                 }
                 if (trace_env) RT_CUDA(cudaEventRecord(c->tr_copy[k], cps));
+                if (staggered) {
+                    RT_CUDA(cudaEventRecord(c->cp_e[k], cps));
+                    c->cp_units[k] = band_u[seq[k].band + 1] - band_u[seq[k].band];
+                }
                 if (time_it) {
                     RT_CUDA(cudaEventRecord(c->copy_t1, cps));
                     c->band0_units = b1 - b0;
@@ -992,6 +1008,7 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
             }
         }
         if (!sequential) c->band0_units = 0;
+        c->cp_n = staggered ? n_seq : 0;
         c->last_n_seq = host_out ? n_seq : 0;
         if (n_seq > 1)
             for (int k = 0; k < n_seq; ++k) RT_CUDA(cudaStreamWaitEvent(c->stream, c->band_done[k], 0));
@@ -1119,6 +1136,13 @@ int rt_destroy(rt_ctx* c) {
     if (c->copy_done2) cudaEventDestroy(c->copy_done2);
     if (c->copy_t0) cudaEventDestroy(c->copy_t0);
     if (c->copy_t1) cudaEventDestroy(c->copy_t1);
+    for (int i = 0; i < 16; ++i) {
+        if (c->cp_s[i]) cudaEventDestroy(c->cp_s[i]);
+        if (c->cp_e[i]) cudaEventDestroy(c->cp_e[i]);
+        if (c->tr_start[i]) cudaEventDestroy(c->tr_start[i]);
+        if (c->tr_end[i]) cudaEventDestroy(c->tr_end[i]);
+        if (c->tr_copy[i]) cudaEventDestroy(c->tr_copy[i]);
+    }
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->copy_stream2) cudaStreamDestroy(c->copy_stream2);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -1342,8 +1366,8 @@ int rt_render(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float* host_
     c->stats.kernel_ms = ms;  // all bands' kernels (copies of finished bands run underneath)
     c->stats.total_ms = ms2;
     if (c->tr_n > 0 && getenv("RT_SEQ_TRACE")) {
-        fprintf(stderr, "[rt seq trace] dev %d shard %u/%u kernels %.2f total %.2f host enqueue %.2f ms, %u launches\n", c->device, c->shard, c->n_shards, ms, ms2,
-                enq_ms, c->last_launches);
+        fprintf(stderr, "[rt seq trace] dev %d shard %u/%u kernels %.2f total %.2f host enqueue %.2f ms, %u launches, ratio %.2f\n", c->device, c->shard,
+                c->n_shards, ms, ms2, enq_ms, c->last_launches, c->band_ratio);
         for (int k = 0; k < c->tr_n; ++k) {
             float a = 0.f, b = 0.f, cp = -1.f;
             cudaEventElapsedTime(&a, c->ev0, c->tr_start[k]);
@@ -1355,7 +1379,22 @@ int rt_render(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float* host_
             fprintf(stderr, "  seq %d units %u start %.2f end %.2f copy_end %.2f\n", k, c->tr_units[k], a, b, cp);
         }
     }
-    if (c->band0_units && c->band_units_total && c->last_pipeline == 1) {  // next frame's band split
+    if (c->cp_n > 0 && c->band_units_total && c->last_pipeline == 1) {  // next frame's plan: all bands' copy times against the kernels
+        double dur = 0.0, un = 0.0;
+        for (int k = 0; k < c->cp_n; ++k) {
+            float t = 0.f;
+            if (c->cp_units[k] && cudaEventElapsedTime(&t, c->cp_s[k], c->cp_e[k]) == cudaSuccess && t > 0.f) {
+                dur += t;
+                un += c->cp_units[k];
+            } else {
+                (void)cudaGetLastError();
+            }
+        }
+        if (dur > 0.0 && un > 0.0 && ms > 0.f) {
+            const double r = ((double)ms / c->band_units_total) / (dur / un);
+            c->band_ratio = std::min(8.0, std::max(0.3, 0.5 * c->band_ratio + 0.5 * r));
+        }
+    } else if (c->band0_units && c->band_units_total && c->last_pipeline == 1) {  // next frame's band split
         float cp = 0.f;
         if (cudaEventElapsedTime(&cp, c->copy_t0, c->copy_t1) == cudaSuccess && cp > 0.f && ms > 0.f) {
             const double r = ((double)ms / c->band_units_total) / ((double)cp / c->band0_units);
