@@ -128,8 +128,9 @@ typedef enum rt_option {
     RT_OPT_SKIP_DEAD_RAYS = 4, /* 1 (default): do not trace rays whose result is dead; 0: trace every ray the reference traces */
     RT_OPT_BVH_BUILDER = 6,    /* 0 (default): binned SAH on the host in rt_upload_scene; 1: Morton-order radix tree built on the
                                   device (scenes that change every frame: ~1 ms instead of ~150 ms per 10^5 objects, a looser tree) */
-    RT_OPT_LANES = 7,      /* 2 (default): camera launches of the wavefront pipeline run as two halves on two streams, each filling the
-                              thin generation tails of the other; 1: one launch sequence */
+    RT_OPT_LANES = 7,      /* frames that stay on the device (rt_render_device): 2 (default) = the camera launches of the wavefront
+                              pipeline run as two halves on two streams, each filling the thin generation tails of the other;
+                              1: one launch sequence */
     RT_OPT_TAIL_GEN = 12,  /* wavefront pipeline: from this generation on (1 = after the primary rays, 1 + lights = after the first
                               shading, ...) ONE kernel finishes every path that is still alive instead of a trace/advance pair per
                               generation -- removes the latency-bound thin tail of small frames.  -1 (default) auto, 0 off */
@@ -142,9 +143,12 @@ typedef enum rt_option {
                                   many cells per 100 objects (default 400) instead of the BVH; 0 = BVH.  Scenes whose lists come out
                                   long (clustered / very uneven object sizes) keep the BVH regardless. */
     RT_OPT_GRID_RES = 8,   /* cells per side of each of the six perspective grids around a light (default 512, 32..4096) */
-    RT_OPT_READBACK_BANDS = 5  /* rt_render of a large camera frame (or shard of one): bands of rows / row-blocks whose readback
-                                  overlaps the next band's kernels, shrinking geometrically by the measured kernel : copy time
-                                  ratio of the previous frame.  0 (default) = 2 bands, n = n bands,
+    RT_OPT_READBACK_BANDS = 5  /* rt_render of a camera frame (or shard of one) on the wavefront pipeline: the frame is cut into n launch
+                                  sequences of rows / row-blocks, each its own readback band, dealt round-robin to three streams;
+                                  a finished band is copied under the kernels of the others.  Sizes shrink geometrically (x 0.7)
+                                  where the copy is faster than the kernels, and are equal where it is not (ranks sharing the
+                                  host's ingest bandwidth) -- decided from the copy and kernel times of the previous frame.
+                                  0 (default) = auto (6-8 sequences, fewer for small shards), n = n sequences,
                                   1 = render everything, then copy it */
 } rt_option;
 
@@ -256,7 +260,8 @@ int rt_host_build_bvh(const rt_object* objs, uint32_t n_objs, const rt_light* li
                       uint64_t leaf_capacity);
 
 /* Host-only: how rt_render cuts a camera frame (n_shards == 1: its rows; else the row-blocks shard owns) into n_bands readback
- * bands shrinking by `ratio` (RT_OPT_READBACK_BANDS).  bounds[0 .. n_bands]: band b covers units bounds[b] .. bounds[b+1]. */
+ * bands shrinking by `ratio` (the two-lane band plan, RT_BAND_MODE=1 RT_STAGGER_K=0; the default plan is described at
+ * RT_OPT_READBACK_BANDS).  bounds[0 .. n_bands]: band b covers units bounds[b] .. bounds[b+1]. */
 int rt_plan_bands(uint32_t height, uint32_t block_rows, uint32_t shard, uint32_t n_shards, int n_bands, double ratio, uint32_t* bounds);
 
 /* Register-only FFMA loop: measured FP32 peak of this device in TFLOP/s (roofline denominator). */

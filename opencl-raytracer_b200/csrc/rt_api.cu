@@ -741,13 +741,17 @@ int ensure_wave_buffers(rt_ctx* c, uint64_t capacity, uint32_t gens, int n_seq, 
 // How a camera render is cut into launch sequences (wavefront pipeline).
 //  * Frame stays on the device (rt_render_device): 2 concurrent sequences (lanes) on two streams -- the blocks of one fill the
 //    thin generation tails of the other.
-//  * Frame goes to the host (rt_render): bands of rows / owned row-blocks ONE AFTER THE OTHER, each as two lanes; a finished
-//    band is copied (copy stream) under the kernels of the next one, so the bands shrink geometrically and only the small last
-//    copy is exposed.  Measured on the 8K cfg5 frame, kernels 24.9 ms, copy 9.4 ms (profiles/r2_sweep_bands.txt): 28.2 ms end
-//    to end with 4 bands shrinking by 3.5 (no copy at all: 27.6 -- what is left is the fixed cost of four sequences, not the
-//    copy); all bands concurrent on their own streams (RT_BAND_MODE=0): 29.1 ms -- stream priorities do not order persistent
-//    kernels, the bands finish together and 3.2 ms of copy stay exposed; an SM copy kernel into the mapped frame instead of the
-//    copy engine: 35.7 ms; an event chain that starts band k after the heavy generations of band k - 1: slower still.
+//  * Frame goes to the host (rt_render): the frame (or the shard's row-blocks) is cut into launch sequences, each its own readback
+//    band with its own copy, dealt round-robin to three streams (two copy streams); a finished band goes home under the kernels
+//    of the others.  Sizes: each sequence 0.7 of the one before where the copy is faster than the kernels -- the thin last
+//    generations of a sequence run under the heavy first ones of the next, only the small last copy is exposed; equal sizes where
+//    the copy is the slower side (8 ranks share ~100 GB/s of host ingest: the frame is home one copy time after the FIRST band
+//    finished).  Measured on the 8K cfg5 frame, kernels 23.5 ms, copy 9.4 ms (profiles/r2_sweep_stagger.txt,
+//    r2_sweep_shard_stagger.txt, r2_sweep_bands.txt): **26.2 ms** end to end with 6 sequences x 0.7 on 3 streams; bands of two
+//    equal lanes one after the other (the lanes reach their thin generations together, every band pays them again): 28.2 ms;
+//    all bands concurrent on their own streams (RT_BAND_MODE=0): 29.1 ms -- stream priorities do not order persistent kernels,
+//    the bands finish together; an SM copy kernel into the mapped frame instead of the copy engine: 35.7 ms; an event chain
+//    that starts band k after the heavy generations of band k - 1: slower still.  8 GPUs: 8.9 -> 7.1 ms, 4: 12.9 -> 10.6 ms.
 int auto_sequences(const rt_ctx* c, bool to_host, bool aov_only) {
     if (!c->use_camera || aov_only) return 1;
     const uint64_t px = local_pixels(c);
