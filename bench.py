@@ -675,8 +675,8 @@ def main():
                     "path": "rt_render into the caller's pinned frame" if world == 1 else
                             "every rank rt_render()s its row-blocks into one shared, page-locked host frame (own PCIe link per GPU)",
                     "ctor_plus_first_render_ms": cold_ms, "scene_h2d_bytes_once": int(len(objs)) * 276 + int(len(lights)) * 64,
-                    "note": "rt_render == IRaytracer::Render(): launch + blocking readback (concurrent bands of rows on their own streams, a "
-                            "finished band is copied under the kernels of the others); scene/camera resident as in the reference ctor, whose "
+                    "note": "rt_render == IRaytracer::Render(): launch + blocking readback (the frame is cut into launch sequences of shrinking size "
+                            "on three streams, a finished one is copied under the kernels of the others); scene/camera resident as in the reference ctor, whose "
                             "one-off cost is ctor_plus_first_render_ms"},
             "gpu_launches": args.steps * launches_per_step,
             "rank_ms": rank_ms or None,
