@@ -264,6 +264,13 @@ int rt_host_build_bvh(const rt_object* objs, uint32_t n_objs, const rt_light* li
  * RT_OPT_READBACK_BANDS).  bounds[0 .. n_bands]: band b covers units bounds[b] .. bounds[b+1]. */
 int rt_plan_bands(uint32_t height, uint32_t block_rows, uint32_t shard, uint32_t n_shards, int n_bands, double ratio, uint32_t* bounds);
 
+/* Host-only: the default readback plan of rt_render (RT_OPT_READBACK_BANDS): the rows of a width x height frame (n_shards == 1) or
+ * the row-blocks `shard` owns are cut into launch sequences, each its own readback band.  n_sequences 0 = auto, q 0 = size ratio
+ * of consecutive sequences from kernel_copy_ratio (what rt_render measures per frame: 2.5 on one GPU, ~1.2 when 8 ranks share
+ * the host).  bounds must hold 17 entries; *n_out sequences, sequence b covers units bounds[b] .. bounds[b+1].  For tests. */
+int rt_plan_sequences(uint32_t width, uint32_t height, uint32_t block_rows, uint32_t shard, uint32_t n_shards, int n_sequences, double q,
+                      double kernel_copy_ratio, uint32_t* bounds, int* n_out);
+
 /* Register-only FFMA loop: measured FP32 peak of this device in TFLOP/s (roofline denominator). */
 int rt_measure_fp32_peak(rt_ctx* ctx, float* tflops, float* sm_mhz_hint);
 /* The two loops of the last rt_measure_fp32_peak separately: scalar FFMA, packed FFMA2 (its result is their maximum). */

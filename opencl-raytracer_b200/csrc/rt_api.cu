@@ -613,6 +613,51 @@ void plan_band(uint32_t units, int band, int n_bands, double ratio, uint32_t* u0
 }
 uint32_t band_units(const rt_ctx* c) { return plan_units(c->height, c->block_rows, c->shard, c->n_shards); }
 
+// The staggered readback plan of rt_render: `units` (rows, or owned row-blocks) of `unit_px` pixels each are cut into launch
+// sequences, each its own readback band.  k_req > 1 fixes their number, q_req > 0 the size ratio of consecutive sequences;
+// otherwise both follow `ratio`, the measured kernel : copy time per unit of the previous frames.  Returns the number of
+// sequences K (<= max_k) and bounds[0 .. K].
+int plan_sequences(uint32_t units, uint64_t unit_px, int k_req, double q_req, double ratio, int max_k, uint32_t* bounds, double* q_out) {
+    double q = q_req;
+    if (!(q > 0.0)) {
+        // each sequence is `q` of the one before.  Copy much faster than the kernels (one GPU on an idle link, kernel : copy
+        // time 2.5): 0.7, so that only a small last copy is exposed.  Copy as slow as the kernels or slower (8 ranks share the
+        // host's ~100 GB/s of ingest: 66 MB per rank take 5.4 ms, the kernels 4.3): equal sequences, and many -- the frame is
+        // then home one copy time after the FIRST sequence has finished, so that one has to be small.
+        q = std::min(1.0, std::max(0.7, 1.3 - 0.3 * ratio));
+    }
+    int k = k_req;
+    if (k < 1) {
+        // auto: six sequences (eight when they are about equal), fewer when the smallest one would fall below 0.4 Mpixel
+        k = q > 0.85 ? 8 : 6;
+        const double px = (double)units * (double)unit_px;
+        auto smallest = [&](int n) {
+            double sum = 0.0, w = 1.0;
+            for (int i = 0; i < n; ++i, w *= q) sum += w;
+            return px * (w / q) / sum;
+        };
+        while (k > 2 && smallest(k) < 400000.0) --k;
+    }
+    k = std::min(k, max_k);
+    while (k > 1 && units < (uint32_t)(4 * k)) --k;
+    k = std::max(k, 1);
+    double total_w = 0.0, w = 1.0;
+    for (int b = 0; b < k; ++b, w *= q) total_w += w;
+    double acc = 0.0;
+    w = 1.0;
+    bounds[0] = 0;
+    for (int b = 0; b < k; ++b, w *= q) {
+        acc += w;
+        bounds[b + 1] = b == k - 1 ? units : std::max(bounds[b], std::min(units, (uint32_t)(acc / total_w * units + 0.5)));
+    }
+    int n = 0;  // sequences that rounding left empty are dropped
+    for (int b = 0; b < k; ++b)
+        if (bounds[b + 1] > bounds[n]) bounds[++n] = bounds[b + 1];
+    if (n == 0) bounds[++n] = units;
+    if (q_out) *q_out = q;
+    return n;
+}
+
 // Number of bands when the caller leaves it open: two.  One more band costs its ramp-up and thin last generations
 // again (0.8 ms of an 8K frame on one GPU, 1.4 ms at 8 GPUs) and hides less than that in every configuration measured
 // (1, 2, 4, 8 GPUs); a cost model on the measured copy time is not robust, because that time depends on how many ranks
@@ -829,39 +874,13 @@ int render_on_device(rt_ctx* c, uint32_t max_bounces, int mode, int accel, float
         double stagger_q = env_num("RT_STAGGER_Q", 0.0);
         const int stagger_s = std::max(1, std::min(4, (int)env_num("RT_STAGGER_S", 3)));
         if (c->opt_bands > 0 && stagger_k < 0) stagger_k = c->opt_bands;  // RT_OPT_READBACK_BANDS = number of sequences
-        if (!(stagger_q > 0.0)) {
-            // each sequence is `q` of the one before.  Copy much faster than the kernels (one GPU on an idle link, kernel : copy
-            // time 2.5): 0.7, so that only a small last copy is exposed.  Copy as slow as the kernels or slower (8 ranks share the
-            // host's ~100 GB/s of ingest: 66 MB per rank take 5.4 ms, the kernels 4.3): equal sequences, and many -- the frame is
-            // then home one copy time after the FIRST sequence has finished, so that one has to be small.
-            stagger_q = std::min(1.0, std::max(0.7, 1.3 - 0.3 * c->band_ratio));
-        }
-        if (stagger_k < 0) {
-            // auto: six sequences (eight when they are about equal), fewer when the smallest one would fall below 0.4 Mpixel
-            stagger_k = stagger_q > 0.85 ? 8 : 6;
-            const double px = (double)units * (double)unit_px;
-            auto smallest = [&](int k) {
-                double sum = 0.0, w = 1.0;
-                for (int i = 0; i < k; ++i, w *= stagger_q) sum += w;
-                return px * (w / stagger_q) / sum;
-            };
-            while (stagger_k > 2 && smallest(stagger_k) < 400000.0) --stagger_k;
-        }
         const bool sequential = host_out != nullptr && c->use_camera && !aov_only && (band_mode_env < 0 ? true : band_mode_env >= 1);
-        const bool staggered = sequential && stagger_k > 1;
+        const bool staggered = sequential && (stagger_k < 0 || stagger_k > 1);
         if (staggered) {
             // every launch sequence is a band of its own; sizes shrink geometrically, streams alternate: a sequence's thin last
-            // generations run under the heavy first generations of the next sequence on the other stream
-            int nb = std::min(stagger_k, (int)rt_ctx::kMaxBands);
-            while (nb > 1 && units < (uint32_t)(4 * nb)) --nb;
-            double total_w = 0.0, w = 1.0;
-            for (int b = 0; b < nb; ++b, w *= stagger_q) total_w += w;
-            double acc = 0.0;
-            w = 1.0;
-            band_u[0] = 0;
-            for (int b = 0; b < nb; ++b, w *= stagger_q) {
-                acc += w;
-                band_u[b + 1] = b == nb - 1 ? units : std::max(band_u[b], std::min(units, (uint32_t)(acc / total_w * units + 0.5)));
+            // generations run under the heavy first generations of the next sequence on another stream
+            const int nb = plan_sequences(units, unit_px, stagger_k, stagger_q, c->band_ratio, (int)rt_ctx::kMaxBands, band_u, nullptr);
+            for (int b = 0; b < nb; ++b) {
                 seq[n_seq].u0 = band_u[b];
                 seq[n_seq].u1 = band_u[b + 1];
                 seq[n_seq].stream = b % stagger_s;
@@ -1645,6 +1664,17 @@ int rt_plan_bands(uint32_t height, uint32_t block_rows, uint32_t shard, uint32_t
         plan_band(units, b, n_bands, ratio, &u0, &u1);
         bounds[b + 1] = u1;
     }
+    return RT_OK;
+}
+
+int rt_plan_sequences(uint32_t width, uint32_t height, uint32_t block_rows, uint32_t shard, uint32_t n_shards, int n_sequences, double q,
+                      double kernel_copy_ratio, uint32_t* bounds, int* n_out) {
+    if (!bounds || !n_out || n_sequences < 0 || n_sequences > rt_ctx::kMaxBands || !(q >= 0.0) || q > 1.0 || !(kernel_copy_ratio > 0.0) || width == 0 ||
+        block_rows == 0 || n_shards == 0 || shard >= n_shards)
+        return fail(RT_ERR_INVALID, "bad sequence plan arguments");
+    const uint32_t units = plan_units(height, block_rows, shard, n_shards);
+    const uint64_t unit_px = (uint64_t)width * (n_shards <= 1 ? 1u : block_rows);
+    *n_out = plan_sequences(units, unit_px, n_sequences, q, kernel_copy_ratio, (int)rt_ctx::kMaxBands, bounds, nullptr);
     return RT_OK;
 }
 

@@ -24,7 +24,7 @@ ABI_SYMBOLS = (
     "rt_last_error", "rt_abi_version", "rt_device_count", "rt_create", "rt_destroy", "rt_set_option", "rt_upload_scene", "rt_set_rays",
     "rt_set_camera", "rt_get_camera", "rt_set_shard", "rt_render", "rt_render_device", "rt_framebuffer", "rt_render_aov", "rt_trace", "rt_trace_static",
     "rt_get_stats", "rt_quantize_rgb8", "rt_host_alloc", "rt_host_free", "rt_host_register", "rt_host_unregister", "rt_measure_fp32_peak", "rt_fp32_peak_detail",
-    "rt_ipc_export_framebuffer", "rt_ipc_open", "rt_ipc_close", "rt_readback", "rt_host_build_bvh", "rt_plan_bands",
+    "rt_ipc_export_framebuffer", "rt_ipc_open", "rt_ipc_close", "rt_readback", "rt_host_build_bvh", "rt_plan_bands", "rt_plan_sequences",
 )
 
 
@@ -103,6 +103,7 @@ def load():
             "rt_ipc_close": [vp, vp],
             "rt_host_build_bvh": [vp, u32, vp, u32, C.c_float, i32, i32, C.POINTER(BvhInfo), vp, u64, vp, u64],
             "rt_plan_bands": [u32, u32, u32, u32, i32, C.c_double, vp],
+            "rt_plan_sequences": [u32, u32, u32, u32, u32, i32, C.c_double, C.c_double, vp, vp],
         }
         for name, args in sigs.items():
             fn = getattr(lib, name)
@@ -140,6 +141,15 @@ def host_build_bvh(objs: np.ndarray, lights: np.ndarray, omax_user: float = 0.0,
     _check(lib.rt_host_build_bvh(_ptr(objs), len(objs), _ptr(lights), len(lights), omax_user, leaf_size, threads, C.byref(info),
                                  _ptr(nodes), nodes.nbytes, _ptr(leaf), len(leaf)))
     return info, nodes, leaf
+
+
+def plan_sequences(width: int, height: int, block_rows: int = 1, shard: int = 0, n_shards: int = 1, n_sequences: int = 0, q: float = 0.0,
+                   kernel_copy_ratio: float = 3.0) -> np.ndarray:
+    """Boundaries (rows, or owned row-blocks of a shard) of the launch sequences of a default rt_render (rt_plan_sequences)."""
+    b = np.zeros(17, dtype=np.uint32)
+    n = C.c_int(0)
+    _check(load().rt_plan_sequences(width, height, block_rows, shard, n_shards, n_sequences, q, kernel_copy_ratio, _ptr(b), C.byref(n)))
+    return b[: n.value + 1].copy()
 
 
 def plan_bands(height: int, block_rows: int, shard: int, n_shards: int, n_bands: int, ratio: float) -> np.ndarray:

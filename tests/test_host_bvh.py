@@ -145,3 +145,37 @@ def test_readback_band_plan_partitions_the_frame(rt):
                         assert abs(sizes[0] / max(sizes[1], 1) - ratio) < 0.1 * ratio + 0.6
     with pytest.raises(rt.RtError):
         rt.plan_bands(100, 16, 3, 2, 2, 7.0)
+
+
+def test_launch_sequence_plan_of_the_default_readback(rt):
+    """rt_plan_sequences: how a default rt_render cuts its frame into launch sequences (each a readback band) -- contiguous,
+    complete, never growing; shrinking by 0.7 where the copy is fast, equal and more numerous where it is slow; fewer for
+    small shards; at least four units per sequence."""
+    W = 7680
+    for height, br, ns in ((4320, 1, 1), (4320, 16, 2), (4320, 16, 8), (2069, 16, 2), (37, 16, 3), (5, 16, 1), (180, 1, 1)):
+        for shard in range(ns):
+            n_blocks = -(-height // br)
+            units = height if ns == 1 else len(range(shard, n_blocks, ns))
+            for ratio in (0.3, 0.9, 1.25, 2.5, 8.0):
+                for k in (0, 1, 2, 5, 16):
+                    b = rt.plan_sequences(W, height, br, shard, ns, k, 0.0, ratio).astype(np.int64)
+                    sizes = np.diff(b)
+                    assert b[0] == 0 and b[-1] == units and np.all(sizes >= 0)
+                    n = len(sizes)
+                    assert 1 <= n <= 16 and (k == 0 or n <= max(k, 1)) and (n == 1 or units >= 4 * n)
+                    if n > 1:
+                        assert np.all(sizes[:-1] + 1 >= sizes[1:]) and sizes[-1] > 0  # rounding may move one unit
+    # one GPU, idle link: six sequences, each 0.7 of the one before
+    s = np.diff(rt.plan_sequences(W, 4320, kernel_copy_ratio=2.5).astype(np.int64))
+    assert len(s) == 6 and np.allclose(s[1:] / s[:-1], 0.7, atol=0.02)
+    # one of eight ranks behind a shared host: (nearly) equal sequences, more of them, none below 0.4 Mpixel
+    s = np.diff(rt.plan_sequences(W, 4320, 16, 3, 8, kernel_copy_ratio=1.0).astype(np.int64))
+    assert len(s) >= 7 and s.max() - s.min() <= 1 and s.min() * 16 * W >= 400000
+    # a small frame is not cut into crumbs
+    assert len(rt.plan_sequences(320, 180, kernel_copy_ratio=2.5)) - 1 <= 2
+    # explicit ratio
+    s = np.diff(rt.plan_sequences(W, 4320, n_sequences=4, q=0.5).astype(np.int64))
+    assert len(s) == 4 and np.allclose(s[1:] / s[:-1], 0.5, atol=0.02)
+    for bad in (dict(n_sequences=17), dict(q=1.5), dict(kernel_copy_ratio=0.0), dict(shard=2, n_shards=2)):
+        with pytest.raises(rt.RtError):
+            rt.plan_sequences(W, 4320, **bad)
