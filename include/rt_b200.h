@@ -19,6 +19,10 @@
  *   rt_render                Render(): launch + read   OpenCLRaytracer.cpp:80-105
  *   rt_render_aov / rt_trace (no equivalent: hit ids / t are not exported by the reference;
  *                             added so that parity of the nearest-hit search can be tested)
+ *   rt_trace_static          (no equivalent: rt_trace without device allocation)
+ *   rt_quantize_rgb8         PPM quantisation          PPMExporter.cpp:19-21
+ *   rt_plan_sequences / rt_plan_bands / rt_host_build_bvh   (no equivalent: host-only views of the render plan and the scene
+ *                             builder, for tests on machines without a GPU)
  */
 #ifndef RT_B200_H
 #define RT_B200_H
