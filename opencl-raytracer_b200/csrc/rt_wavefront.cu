@@ -212,6 +212,8 @@ __device__ __forceinline__ void exact_pair_call(const Scene& sc, const float4 s,
     btype = b.type;
 }
 
+// (Requesting a survivor's inverse matrix -- the first thing its exact test loads -- with a prefetch when the survivor is queued
+// was measured on the 8K cfg5 frame and dropped: 23.5 ms against 23.2 without.)
 // Persistent warps.  Every lane owns one ray of the queue and is in one of four states:
 //   T  traversing (stands on an inner node)           S  traversing, but its candidate buffer is nearly full
 //   F  traversal finished, candidates still queued    I  idle (no ray)
@@ -1082,6 +1084,15 @@ cudaError_t launch_filter(const Scene& sc, const TaskQueue& qin, const uint32_t*
 #define RT_ADV_MINB 4  // resident CTAs per SM the advance kernel is compiled for (64 registers; latency bound: 3 -> 4 is 24.9 -> 24.0 ms per
                        // frame in round 2, 5 the same as 4)
 #endif
+#ifndef RT_ADV_PREFETCH
+#define RT_ADV_PREFETCH 1  // 0 off, 1 into L1, 2 into L2.  8K cfg5 frame: 23.50 / 23.21 / 23.19 ms of kernels, Render() 26.4 / 26.0 / 26.1
+#endif
+#if RT_ADV_PREFETCH == 1
+__device__ __forceinline__ void prefetch_state(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+#elif RT_ADV_PREFETCH == 2
+__device__ __forceinline__ void prefetch_state(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+#endif
+
 template <bool COUNT>
 __global__ void __launch_bounds__(kBlock, RT_ADV_MINB) wave_advance(const Scene sc, const WaveParams wp, const PathArrays pa, const TaskQueue qin,
                                                        const TaskQueue qout, const uint32_t* __restrict__ n_in, uint32_t* __restrict__ n_out,
@@ -1114,6 +1125,29 @@ __global__ void __launch_bounds__(kBlock, RT_ADV_MINB) wave_advance(const Scene 
             Hit res;
             res.t = res_t[at];
             res.id = res_id[at];
+#if RT_ADV_PREFETCH
+            // the state machine walks a chain of dependent gathers (ctrl word -> path state -> object records); what the path
+            // word and the hit already tell is requested now, so that the chain finds it on its way in
+            if (!first) {
+#define RT_PF prefetch_state
+                if (pw & RT_TASK_ANYHIT) {
+                    RT_PF(pa.P + p);
+                    RT_PF(pa.Nm + p);
+                    RT_PF(pa.acc + p);
+                    RT_PF(pa.refl + p);
+                } else if (res.id < 0) {
+                    RT_PF(pa.acc + p);
+                    RT_PF(pa.refl + p);
+                } else {
+                    RT_PF(sc.minv + 4 * (size_t)res.id);
+                    RT_PF(sc.minv + 4 * (size_t)res.id + 2);
+                    RT_PF(sc.mv + 4 * (size_t)res.id);
+                    RT_PF(sc.mv + 4 * (size_t)res.id + 2);
+                    RT_PF(sc.mat + 3 * (size_t)res.id);
+                }
+#undef RT_PF
+            }
+#endif
             if (first && aov_id) {
                 const uint32_t oi = pa.out[p];
                 aov_id[oi] = res.id;
