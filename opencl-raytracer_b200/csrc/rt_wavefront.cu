@@ -89,8 +89,9 @@ __device__ __forceinline__ uint32_t block_append(bool emit, uint32_t* counter, u
 // The same for the two ends of a queue at once (class B: front, class A: back): both per-warp counts travel through the
 // scan packed into one word (a block emits at most 256 of each), lanes 0 and 1 of warp 0 do the two atomics.  Returns the
 // slot in the queue end the thread emits to (emit_a wins if both are set).  sh holds 2 * kBlock/32 words.
+template <int BLOCK = kBlock>
 __device__ __forceinline__ uint32_t block_append2(bool emit_b, bool emit_a, uint32_t* count_b, uint32_t* count_a, uint32_t* sh) {
-    constexpr unsigned kWarps = kBlock / 32;
+    constexpr unsigned kWarps = BLOCK / 32;
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const unsigned ma = __ballot_sync(kFull, emit_a), mb = __ballot_sync(kFull, emit_b && !emit_a);
     if (lane == 0) sh[warp] = (uint32_t)__popc(mb) | ((uint32_t)__popc(ma) << 16);
@@ -1084,6 +1085,13 @@ cudaError_t launch_filter(const Scene& sc, const TaskQueue& qin, const uint32_t*
 #define RT_ADV_MINB 4  // resident CTAs per SM the advance kernel is compiled for (64 registers; latency bound: 3 -> 4 is 24.9 -> 24.0 ms per
                        // frame in round 2, 5 the same as 4)
 #endif
+#ifndef RT_ADV_BLOCK
+#define RT_ADV_BLOCK 256  // threads per block of wave_advance.  Every loop iteration ends in a block-wide scan behind two barriers (ncu:
+                          // `stalled_barrier` 3.5-5 per issue beside `long_scoreboard` 9-14) and two atomics on the queue counters:
+                          // smaller blocks wait less and hammer the counters more.  8K cfg5 frame, 64 / 128 / 256 / 512 / 1024
+                          // threads: 24.25 / 23.45 / 23.17 / 23.31 / 23.65 ms
+#endif
+constexpr int kAdvBlock = RT_ADV_BLOCK;
 #ifndef RT_ADV_PREFETCH
 #define RT_ADV_PREFETCH 1  // 0 off, 1 into L1, 2 into L2.  8K cfg5 frame: 23.50 / 23.21 / 23.19 ms of kernels, Render() 26.4 / 26.0 / 26.1
 #endif
@@ -1094,7 +1102,7 @@ __device__ __forceinline__ void prefetch_state(const void* p) { asm volatile("pr
 #endif
 
 template <bool COUNT>
-__global__ void __launch_bounds__(kBlock, RT_ADV_MINB) wave_advance(const Scene sc, const WaveParams wp, const PathArrays pa, const TaskQueue qin,
+__global__ void __launch_bounds__(kAdvBlock, (RT_ADV_MINB * kBlock / kAdvBlock) > 0 ? (RT_ADV_MINB * kBlock / kAdvBlock) : 1) wave_advance(const Scene sc, const WaveParams wp, const PathArrays pa, const TaskQueue qin,
                                                        const TaskQueue qout, const uint32_t* __restrict__ n_in, uint32_t* __restrict__ n_out,
                                                        const float* __restrict__ res_t, const int32_t* __restrict__ res_id,
                                                        const int first, float4* __restrict__ fb, int32_t* __restrict__ aov_id,
@@ -1103,10 +1111,10 @@ __global__ void __launch_bounds__(kBlock, RT_ADV_MINB) wave_advance(const Scene 
     const uint32_t n = nb + na;
     if (n == 0u) return;
     LocalCounters lc;
-    __shared__ uint32_t sh_append[2 * kBlock / 32];
+    __shared__ uint32_t sh_append[2 * kAdvBlock / 32];
     const uint32_t back = wp.qcap - 1u;
-    const uint64_t n_round = ((uint64_t)n + kBlock - 1u) / kBlock * kBlock;  // whole blocks take part in the append
-    for (uint64_t i = (uint64_t)blockIdx.x * kBlock + threadIdx.x; i < n_round; i += (uint64_t)gridDim.x * kBlock) {
+    const uint64_t n_round = ((uint64_t)n + kAdvBlock - 1u) / kAdvBlock * kAdvBlock;  // whole blocks take part in the append
+    for (uint64_t i = (uint64_t)blockIdx.x * kAdvBlock + threadIdx.x; i < n_round; i += (uint64_t)gridDim.x * kAdvBlock) {
         StepOut o;
         o.emit = o.write = o.anyhit = false;
         o.light = RT_TASK_NO_GRID;
@@ -1162,7 +1170,7 @@ __global__ void __launch_bounds__(kBlock, RT_ADV_MINB) wave_advance(const Scene 
             const float chk = o.ray.s.x + o.ray.s.y + o.ray.s.z + o.ray.d.x + o.ray.d.y + o.ray.d.z;
             to_a = fabsf(chk) < __int_as_float(0x7f800000);
         }
-        const uint32_t slot = block_append2(o.emit, to_a, n_out, n_out + 1, sh_append);
+        const uint32_t slot = block_append2<kAdvBlock>(o.emit, to_a, n_out, n_out + 1, sh_append);
         if (o.emit) {
             const uint32_t at = to_a ? back - slot : slot;
             qout.s[at] = o.ray.s;
@@ -1305,7 +1313,7 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
     static const int d_min_t = env_int("RT_DDA_MIN_T", 12), d_drain_t = env_int("RT_DDA_DRAIN", 4), d_refill_t = env_int("RT_DDA_REFILL", 16);
     const unsigned sgrid = (unsigned)sm_count * 8u;    // grid-stride kernels
     static const int adv_mult = env_int("RT_ADV_GRID", RT_ADV_MINB);  // = resident CTAs per SM; 3..32 measured within 1 %
-    const unsigned agrid = (unsigned)sm_count * (unsigned)adv_mult;  // wave_advance
+    const unsigned agrid = std::max(1u, (unsigned)sm_count * (unsigned)adv_mult * kBlock / kAdvBlock);  // wave_advance
     const bool count = fr.counters != nullptr;
     for (uint32_t g = 0; g < gens; ++g) {
         const TaskQueue& qin = wb.q[g & 1u];
@@ -1359,10 +1367,10 @@ cudaError_t wave_render(const Scene& sc, const Frame& fr, const WaveBuffers& wb,
             ++nl;
         }
         if (count)
-            wave_advance<true><<<agrid, kBlock, 0, stream>>>(sc, wp, wb.pa, qin, qout, nq, nq + 2, wb.res_t, wb.res_id,
+            wave_advance<true><<<agrid, kAdvBlock, 0, stream>>>(sc, wp, wb.pa, qin, qout, nq, nq + 2, wb.res_t, wb.res_id,
                                                              g == 0 ? 1 : 0, fr.out, fr.hit_id, fr.hit_t, fr.counters);
         else
-            wave_advance<false><<<agrid, kBlock, 0, stream>>>(sc, wp, wb.pa, qin, qout, nq, nq + 2, wb.res_t, wb.res_id,
+            wave_advance<false><<<agrid, kAdvBlock, 0, stream>>>(sc, wp, wb.pa, qin, qout, nq, nq + 2, wb.res_t, wb.res_id,
                                                               g == 0 ? 1 : 0, fr.out, fr.hit_id, fr.hit_t, fr.counters);
         ++nl;
     }
