@@ -79,3 +79,27 @@ def test_shard_rows_partition():
         assert sorted(allrows.tolist()) == list(range(H))
     with pytest.raises(ValueError):
         shard.shard_rows(10, 0, 0, 1)
+
+
+def test_every_ranks_launch_sequences_cover_the_frame_once(rt):
+    """The readback plan of a sharded rt_render (rt_plan_sequences, host logic of the C-ABI library): over all ranks and all of a
+    rank's launch sequences every row of the frame is rendered and copied exactly once, whatever the copy : kernel ratio says."""
+    from pyrt import shard
+
+    W = 7680
+    for H, br, n in ((4320, 16, 8), (4320, 16, 4), (2160, 16, 2), (37, 4, 2), (100, 32, 3)):
+        for ratio in (0.5, 1.25, 3.0):
+            seen = np.zeros(H, dtype=np.int32)
+            for s in range(n):
+                rows = shard.shard_rows(H, br, s, n)
+                b = rt.plan_sequences(W, H, br, s, n, 0, 0.0, ratio).astype(np.int64)
+                blocks = list(range(s, -(-H // br), n))
+                assert b[-1] == len(blocks)
+                mine = []
+                for k in range(len(b) - 1):
+                    for u in range(b[k], b[k + 1]):
+                        r0 = blocks[u] * br
+                        mine.extend(range(r0, min(r0 + br, H)))
+                assert mine == rows.tolist()
+                seen[mine] += 1
+            assert np.all(seen == 1)
