@@ -826,3 +826,28 @@ def test_clustered_scene_keeps_the_bvh(rt, ctx, oracle_mod):
     ctx.render(3, 2, 3)
     s2 = ctx.stats()
     assert s2.node_visits / max(s2.traced_reflect, 1) < visits_clustered  # the uniform scene takes the grid: cells, not node steps
+
+
+@pytest.mark.parametrize("size", [(1001, 777), (2561, 1439), (64, 3)])
+def test_readback_plans_on_odd_frames(rt, ctx, size):
+    """rt_render's readback plan (launch sequences of shrinking size on three streams, two copy streams) on frames whose sizes
+    divide by nothing: the default plan into a pageable and into a pinned buffer, and explicit sequence counts, all give the
+    frame that rt_render_device + rt_readback give."""
+    W, H = size
+    objs, lights = S.synthetic_scene(20000, 1000)
+    ctx.upload_scene(objs, lights)
+    ctx.set_camera(W, H, T.camera_zdir(H))
+    a = ctx.render(4, 2, -1).copy()
+    ctx.render_device(4, 2, -1)
+    b = np.empty((W * H, 4), np.float32)
+    ctx.readback(b)
+    assert np.array_equal(a, b)
+    pinned = rt.PinnedBuffer((W * H, 4))
+    try:
+        ctx.render(4, 2, -1, out=pinned.array)
+        assert np.array_equal(pinned.array, b)
+    finally:
+        pinned.close()
+    for k in (1, 3, 7, 16):
+        ctx.set_option(rt.OPT_READBACK_BANDS, k)
+        assert np.array_equal(ctx.render(4, 2, -1), b), k
