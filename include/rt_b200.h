@@ -115,7 +115,8 @@ typedef struct rt_stats {
     uint64_t node_visits;    /* BVH inner nodes visited                                      */
     uint64_t pixels;         /* pixels rendered by this context (its shard)                  */
     uint64_t hit_pixels;
-    float kernel_ms;         /* device time of all kernels of the last render (CUDA events)  */
+    float kernel_ms;         /* device time from the start of the last render to the end of its last kernel (CUDA events;
+                                rt_render: copies of finished bands run underneath)           */
     float total_ms;          /* kernels + device->host copy of the last render               */
     uint32_t kernel_launches;
     uint32_t accel_used;     /* rt_accel actually used                                       */
